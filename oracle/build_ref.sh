@@ -1,0 +1,30 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE ONLY (see oracle/README.md).
+# Compiles the UNMODIFIED reference programs hw1..hw8 straight from /root/reference
+# with g++ (no cmake, no source edits, no copies) into oracle/_ref/hwN.
+# Flags follow the reference's CMake "Release" build (hwN/CMakeLists.txt): -O3 -DNDEBUG -std=c++17,
+# OpenMP for hw5..hw8.  `-include array` works around color.h using std::array without the
+# include (hw5..hw8 fail on GCC 13 otherwise).
+set -euo pipefail
+REF=${B200RT_REFERENCE:-/root/reference}
+HERE="$(cd "$(dirname "$0")" && pwd)"
+OUT="$HERE/_ref"
+if [ ! -d "$REF/hw8/src" ]; then
+  echo "build_ref: $REF not present; keeping prebuilt oracle/_ref as is" >&2
+  exit 0
+fi
+mkdir -p "$OUT"
+CXX=${B200RT_CXX:-/usr/bin/g++}   # NOT $CXX: the image exports CXX=/opt/gcc/bin/g++, which has no libgomp.spec
+for n in 1 2 3 4 5 6 7 8; do
+  src="$REF/hw$n/src"
+  flags="-O3 -DNDEBUG -std=c++17 -I$src/include"
+  [ "$n" -eq 1 ] && flags="-O2 $flags -fopenmp"
+  [ "$n" -ge 5 ] && flags="$flags -fopenmp -include array"
+  [ "$n" -ge 6 ] && flags="$flags -I$REF/rapidjson/include"
+  [ "$n" -ge 8 ] && flags="$flags -I$REF/stb"
+  if [ ! -x "$OUT/hw$n" ] || [ "$0" -nt "$OUT/hw$n" ]; then
+    echo "build_ref: hw$n" >&2
+    $CXX $flags "$src"/*.cpp -o "$OUT/hw$n" 2> "$OUT/hw$n.log" || { tail -5 "$OUT/hw$n.log" >&2; exit 1; }
+  fi
+done
+echo "build_ref: ok -> $OUT" >&2
