@@ -1,0 +1,218 @@
+/*
+ * b200rt.h -- C ABI of the B200 (sm_100a) render core.
+ *
+ * This is the drop-in boundary for ONE hot path of volivan239/raytracing-course-hw: the
+ * per-pixel, per-sample ray-scene intersection and shading loop.  In the reference that
+ * path is the body of the pixel loop in sceneio::renderScene
+ *     hw8/src/sceneio.cpp:386-396  (OpenMP loop: rng(i), Scene::getPixel, tonemap, gamma, quantise)
+ *     hw4/src/sceneio.cpp:114-122, hw2/src/sceneio.cpp:156-163, hw1/src/sceneio.cpp:103-108 (serial)
+ * and everything below Scene::getPixel (hw8/src/scene.cpp:167-177, hw4/src/scene.cpp:110-118,
+ * hw2/src/scene.cpp:87-89, hw1/src/scene.cpp:7-20).  The reference has no FFI; a maintainer
+ * would replace that loop with:  b200rt_upload_scene(once) ; b200rt_render ; b200rt_resolve.
+ * INTEGRATION.md shows that binding.
+ *
+ * Conventions: plain C structs, plain pointers and sizes.  The caller owns every host buffer
+ * (they are copied during the call); the library owns all device memory.  Every entry point
+ * returns 0 (B200RT_OK) or a negative error code, never throws, never exits.  A context is
+ * driven by one host thread.  There is NO CPU fallback: without a CUDA device every compute
+ * entry point returns B200RT_ERR_NO_DEVICE.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes ------------------------------------------------------------------- */
+#define B200RT_OK                0
+#define B200RT_ERR_INVALID      -1  /* bad argument / malformed scene description          */
+#define B200RT_ERR_NO_DEVICE    -2  /* no CUDA device (there is no CPU fallback)            */
+#define B200RT_ERR_CUDA         -3  /* a CUDA runtime call failed; see b200rt_last_error    */
+#define B200RT_ERR_NO_SCENE     -4  /* render/resolve before upload_scene                   */
+#define B200RT_ERR_UNSUPPORTED  -5  /* mode / feature not implemented on the device path    */
+#define B200RT_ERR_STACK        -6  /* BVH deeper than the traversal stack                  */
+
+/* ---- scene semantics: which homework's integrator is reproduced -- */
+#define B200RT_MODE_HW1 1  /* flat-colour primary cast          hw1/src/scene.cpp:7-20      */
+#define B200RT_MODE_HW2 2  /* Whitted: lights, shadows, branch  hw2/src/scene.cpp:29-85     */
+#define B200RT_MODE_HW3 3  /* MC, uniform hemisphere            hw3/src/scene.cpp:31-87     */
+#define B200RT_MODE_HW4 4  /* MC, cosine + light mixture        hw4/src/scene.cpp:50-108    */
+#define B200RT_MODE_HW5 5  /* hw4 + triangles + BVH (text)      hw5/src/scene.cpp:47-105    */
+#define B200RT_MODE_HW6 6  /* hw5 integrator on glTF triangles  hw6/src/scene.cpp           */
+#define B200RT_MODE_HW7 7  /* GGX metal-rough path tracer       hw7/src/scene.cpp:29-61     */
+#define B200RT_MODE_HW8 8  /* hw7 + textures/normal map/env map hw8/src/scene.cpp:84-165    */
+
+/* analytic primitive types (hw4/src/include/primitives.h FigureType; hw5 adds TRIANGLE) */
+#define B200RT_PRIM_ELLIPSOID 0
+#define B200RT_PRIM_PLANE     1
+#define B200RT_PRIM_BOX       2
+#define B200RT_PRIM_TRIANGLE  3
+
+/* text-scene materials (hw2/src/include/material.h) */
+#define B200RT_MAT_DIFFUSE    0
+#define B200RT_MAT_METALLIC   1
+#define B200RT_MAT_DIELECTRIC 2
+
+/* hw2 lights (hw2/src/include/light_source.h:12-31) */
+#define B200RT_LIGHT_POINT       0
+#define B200RT_LIGHT_DIRECTIONAL 1
+
+/* ---- reference-shaped scene description (what Scene holds after loadScene) ------------ */
+
+/* hw1-hw5 `Figure` (hw4/src/include/primitives.h:33-52): world position + rotation quaternion
+ * (x,y,z,w, never normalised -- SURVEY Q3), shape parameter `data` (ellipsoid radii, plane
+ * normal, box half extents; hw5 triangles also use data2/data3). */
+typedef struct b200rt_primitive {
+    int32_t type;
+    int32_t material;
+    float   data[3];
+    float   data2[3];
+    float   data3[3];
+    float   position[3];
+    float   rotation[4];
+    float   color[3];
+    float   emission[3];
+    float   ior;
+} b200rt_primitive;
+
+/* hw2 light (hw2/src/light_source.cpp:9-23): `v` is the position (point) or direction. */
+typedef struct b200rt_light {
+    int32_t type;
+    float   intensity[3];
+    float   v[3];
+    float   attenuation[3];
+} b200rt_light;
+
+/* hw7/hw8 `Figure` (hw8/src/include/primitives.h:58-75): three `Vertex` in the reference's
+ * member order data, data2, data3 (= glTF p1, p3, p2 after the loader's swizzle,
+ * hw8/src/sceneio.cpp:289); data3 is the barycentric origin.  World space. */
+typedef struct b200rt_triangle {
+    float    p[3][3];    /* coords   of data, data2, data3 */
+    float    uv[3][2];   /* texcoords                       */
+    float    n[3][3];    /* normals (unit)                  */
+    float    tan[3][4];  /* tangents xyz (unit) + w         */
+    uint32_t material;   /* index into materials            */
+} b200rt_triangle;
+
+/* `BvhNode` (hw8/src/include/bvh.h:9-16): left==0 marks a leaf holding [first,last). */
+typedef struct b200rt_bvh_node {
+    float    aabb_min[3];
+    float    aabb_max[3];
+    uint32_t left, right, first, last;
+} b200rt_bvh_node;
+
+/* `GltfMaterial` + `MaterialModel` (hw8/src/include/gltf_structs.h:38-47, material.h:5-9).
+ * Texture fields are IMAGE indices (textureDescs[..].source already applied) or -1. */
+typedef struct b200rt_material {
+    float   base_color[3];
+    float   emission[3];      /* emissiveFactor x KHR emissive strength */
+    float   metallic_factor;
+    float   roughness_factor;
+    int32_t base_color_image;
+    int32_t emissive_image;
+    int32_t metallic_roughness_image;
+    int32_t normal_image;
+} b200rt_material;
+
+/* `Texture` (hw8/src/include/gltf_structs.h:10-13): tightly packed RGB8, row 0 first. */
+typedef struct b200rt_image {
+    int32_t        width, height;
+    const uint8_t *rgb;
+} b200rt_image;
+
+typedef struct b200rt_scene_desc {
+    int32_t mode;                 /* B200RT_MODE_HWn */
+    int32_t width, height;        /* DIMENSIONS / argv */
+    int32_t samples;              /* SAMPLES / argv (1 for hw1, hw2) */
+    int32_t ray_depth;            /* RAY_DEPTH; 6 for glTF modes (hw8/src/include/scene.h:32) */
+    float   bg_color[3];
+    float   ambient[3];           /* hw2 AMBIENT_LIGHT */
+    float   cam_pos[3], cam_right[3], cam_up[3], cam_forward[3];
+    float   cam_fov;              /* CAMERA_FOV_X (text modes) or yfov (glTF modes) */
+
+    const b200rt_primitive *prims;        int32_t n_prims;        /* hw1-hw5 */
+    const b200rt_light     *lights;       int32_t n_lights;       /* hw2     */
+
+    const b200rt_triangle  *tris;         int32_t n_tris;         /* hw6-hw8, in BVH order */
+    const b200rt_bvh_node  *nodes;        int32_t n_nodes;        /* Scene::bvh.nodes      */
+    int32_t                 root;
+    const b200rt_triangle  *light_tris;   int32_t n_light_tris;   /* FiguresMix::figures_  */
+    const b200rt_bvh_node  *light_nodes;  int32_t n_light_nodes;  /* FiguresMix::bvh.nodes */
+    const b200rt_material  *materials;    int32_t n_materials;
+    const b200rt_image     *images;       int32_t n_images;
+    const b200rt_image     *env_map;      /* NULL when absent (hw8 argv[6]) */
+} b200rt_scene_desc;
+
+/* ---- context ------------------------------------------------------------------------ */
+typedef struct b200rt_ctx b200rt_ctx;
+
+typedef struct b200rt_options {
+    int32_t  device;        /* CUDA device ordinal */
+    uint32_t seed;          /* key of the counter-based RNG (0 = default stream) */
+    int32_t  flags;         /* B200RT_FLAG_* */
+} b200rt_options;
+
+#define B200RT_FLAG_COUNTERS 1   /* count rays / node fetches / triangle tests (slower kernel) */
+
+typedef struct b200rt_stats {
+    double   kernel_ms;        /* device time of the last b200rt_render (CUDA events) */
+    uint64_t paths;            /* camera samples started                                */
+    uint64_t rays;             /* closest-hit scene queries (Scene::intersect calls)    */
+    uint64_t light_queries;    /* FiguresMix::pdf traversals                            */
+    uint64_t node_tests;       /* scene-BVH node boxes tested    (COUNTERS flag only)   */
+    uint64_t tri_tests;        /* scene triangles tested          (COUNTERS flag only)   */
+    uint64_t light_node_tests; /* light-BVH node boxes tested     (COUNTERS flag only)   */
+    uint64_t light_tri_tests;  /* light triangles tested          (COUNTERS flag only)   */
+    uint64_t shaded_hits;      /* hits that fetched a shading record (COUNTERS only)    */
+    uint64_t tex_lookups;      /* bilinear texture lookups           (COUNTERS only)    */
+    int32_t  launches;         /* kernels launched by the last render+resolve           */
+} b200rt_stats;
+
+/* Replaces: constructing the render state inside main() (hw8/src/main.cpp:8-15). */
+int b200rt_create(b200rt_ctx **out, const b200rt_options *opt);
+void b200rt_destroy(b200rt_ctx *ctx);
+
+/* Replaces: Scene being resident in host memory for getPixel (hw8/src/include/scene.h:23-41).
+ * Flattens the reference-shaped arrays to the device layout and uploads. */
+int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *scene);
+
+/* Replaces: the pixel loop + Scene::getPixel (hw8/src/sceneio.cpp:387-392, scene.cpp:167-177).
+ * Renders global sample indices [spp_begin, spp_end) of every pixel and ADDS them to the
+ * float accumulation buffer (cleared when spp_begin == 0 or after b200rt_clear).
+ * width/height/ray_depth <= 0 take the scene's values.  Asynchronous on the context stream. */
+int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height,
+                  int32_t spp_begin, int32_t spp_end, int32_t ray_depth);
+int b200rt_clear(b200rt_ctx *ctx);
+
+/* Replaces: `1.0/samples * color`, aces_tonemap, gamma_corrected, toExternColorFormat
+ * (hw8/src/scene.cpp:176, hw8/src/color.cpp:4-31; hw1: round(255 c) only, hw1/src/color.cpp:13-19).
+ * total_spp = number of samples the accumulation buffer holds (all ranks).  Blocks; writes
+ * width*height*3 bytes, top row first (the PPM payload). */
+int b200rt_resolve(b200rt_ctx *ctx, int32_t total_spp, uint8_t *rgb_out);
+
+/* Accumulated radiance SUM, width*height*3 floats (for RMSE tests and multi-GPU reduce). */
+int b200rt_download_accum(b200rt_ctx *ctx, float *rgb_out);
+int b200rt_upload_accum(b200rt_ctx *ctx, const float *rgb_in);
+/* Device pointer + element count of the accumulation buffer (for NCCL reduce by the host). */
+int b200rt_accum_device_ptr(b200rt_ctx *ctx, void **ptr, size_t *n_floats);
+
+/* hw1/hw2 parity aid: primitive index of the primary hit per pixel (-1 = miss), int32 W*H. */
+int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out);
+
+int b200rt_synchronize(b200rt_ctx *ctx);
+int b200rt_get_stats(b200rt_ctx *ctx, b200rt_stats *out);
+/* cudaStream_t of the context as void* (so callers can record events on it). */
+int b200rt_stream(b200rt_ctx *ctx, void **stream_out);
+
+const char *b200rt_strerror(int code);
+const char *b200rt_last_error(b200rt_ctx *ctx);
+int b200rt_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */

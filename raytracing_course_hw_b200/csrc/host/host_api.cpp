@@ -1,0 +1,175 @@
+// C ABI of the host scene library + acceleration-structure hooks + image/PPM I/O.
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <new>
+#include "bvh_build.h"
+#include "host_scene.h"
+
+#if defined(B200RT_HAVE_STB)
+#define STB_IMAGE_IMPLEMENTATION
+#define STBI_NO_HDR
+#define STBI_NO_LINEAR
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Wunused-function"
+#pragma GCC diagnostic ignored "-Wunused-but-set-variable"
+#include "stb_image.h"   // third-party decoder the reference also uses (hw8/src/sceneio.cpp:374-379)
+#pragma GCC diagnostic pop
+#endif
+
+namespace b200rt_host {
+
+double now_ms() {
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+bool decode_png_rgb8(const std::vector<uint8_t> &file, int32_t &w, int32_t &h, std::vector<uint8_t> &rgb);
+
+int load_image_rgb8(const std::string &path, int32_t &w, int32_t &h, std::vector<uint8_t> &rgb) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) return B200RT_HOST_ERR_IO;
+    std::vector<uint8_t> file((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    // Built-in PNG decoder first (lossless => identical texels to stb_image); other formats via stb.
+    if (decode_png_rgb8(file, w, h, rgb)) return B200RT_OK;
+#if defined(B200RT_HAVE_STB)
+    int ww = 0, hh = 0, ch = 0;
+    unsigned char *px = stbi_load_from_memory(file.data(), (int)file.size(), &ww, &hh, &ch, 3);
+    if (!px) return B200RT_HOST_ERR_IMAGE;
+    w = ww; h = hh;
+    rgb.assign(px, px + (size_t)ww * hh * 3);
+    stbi_image_free(px);
+    return B200RT_OK;
+#else
+    return B200RT_HOST_ERR_IMAGE;
+#endif
+}
+
+static BvhItem item_of(const b200rt_triangle &t, uint32_t index) {
+    BvhItem it;
+    for (int a = 0; a < 3; a++) {
+        it.key[a] = t.p[2][a];  // data3.coords (hw8/src/include/bvh.h:63-65)
+        it.mn[a] = std::min(t.p[2][a], std::min(t.p[0][a], t.p[1][a]));
+        it.mx[a] = std::max(t.p[2][a], std::max(t.p[0][a], t.p[1][a]));
+    }
+    it.index = index;
+    return it;
+}
+
+static void build_over(std::vector<b200rt_triangle> &tris, uint32_t n, std::vector<b200rt_bvh_node> &nodes, int32_t *root) {
+    std::vector<BvhItem> items(n);
+    for (uint32_t i = 0; i < n; i++) items[i] = item_of(tris[i], i);
+    BvhBuilder b;
+    b.build(items, n);
+    std::vector<b200rt_triangle> sorted(n);
+    for (uint32_t i = 0; i < n; i++) sorted[i] = tris[items[i].index];
+    std::copy(sorted.begin(), sorted.end(), tris.begin());
+    nodes = std::move(b.nodes);
+    if (root) *root = (int32_t)b.root;
+}
+
+// Scene::initBVH (hw8/src/scene.cpp:76-78) then Scene::initDistribution -> FiguresMix ctor
+// (hw8/src/include/distributions.h:103-115): copy the BVH-ordered figures, std::partition the
+// emissive ones (material emissiveFactor != 0; textures ignored) to the front, build a second
+// BVH over them.
+void build_triangle_accel(b200rt_host_scene &s) {
+    build_over(s.tris, (uint32_t)s.tris.size(), s.nodes, &s.desc.root);
+    std::vector<b200rt_triangle> copy = s.tris;
+    auto emissive = [&](const b200rt_triangle &t) {
+        const float *e = s.materials[t.material].emission;
+        return !(e[0] == 0 && e[1] == 0 && e[2] == 0);
+    };
+    size_t n = (size_t)(std::partition(copy.begin(), copy.end(), emissive) - copy.begin());
+    copy.resize(n);
+    s.light_tris = std::move(copy);
+    s.light_nodes.clear();
+    if (n > 0) build_over(s.light_tris, (uint32_t)n, s.light_nodes, nullptr);
+    // n == 0: the reference still builds a one-node BVH over nothing but never uses it.
+}
+
+}  // namespace b200rt_host
+
+using namespace b200rt_host;
+
+extern "C" {
+
+int b200rt_host_load_text(const char *path, int32_t mode, b200rt_host_scene **out) {
+    if (!path || !out) return B200RT_ERR_INVALID;
+    auto *s = new (std::nothrow) b200rt_host_scene();
+    if (!s) return B200RT_ERR_INVALID;
+    int rc = B200RT_ERR_INVALID;
+    try { rc = load_text_scene(path, mode, *s); } catch (...) { rc = B200RT_HOST_ERR_PARSE; }
+    if (rc) { delete s; return rc; }
+    *out = s;
+    return B200RT_OK;
+}
+
+int b200rt_host_load_gltf(const char *path, int32_t mode, int32_t width, int32_t height, int32_t samples, b200rt_host_scene **out) {
+    if (!path || !out || width <= 0 || height <= 0 || samples <= 0) return B200RT_ERR_INVALID;
+    auto *s = new (std::nothrow) b200rt_host_scene();
+    if (!s) return B200RT_ERR_INVALID;
+    int rc = B200RT_ERR_INVALID;
+    try { rc = load_gltf_scene(path, mode, *s); } catch (...) { rc = B200RT_HOST_ERR_PARSE; }
+    if (rc) { delete s; return rc; }
+    s->desc.width = width; s->desc.height = height; s->desc.samples = samples;
+    *out = s;
+    return B200RT_OK;
+}
+
+int b200rt_host_set_env_map(b200rt_host_scene *s, const char *image_path) {
+    if (!s || !image_path) return B200RT_ERR_INVALID;
+    int32_t w, h;
+    std::vector<uint8_t> rgb;
+    int rc = load_image_rgb8(image_path, w, h, rgb);
+    if (rc) return rc;
+    s->env_data = std::move(rgb);
+    s->env.width = w; s->env.height = h;
+    s->has_env = true;
+    s->sync();
+    return B200RT_OK;
+}
+
+const b200rt_scene_desc *b200rt_host_desc(const b200rt_host_scene *s) { return s ? &s->desc : nullptr; }
+
+int b200rt_host_set_frame(b200rt_host_scene *s, int32_t width, int32_t height, int32_t samples) {
+    if (!s) return B200RT_ERR_INVALID;
+    if (width > 0) s->desc.width = width;
+    if (height > 0) s->desc.height = height;
+    if (samples > 0) s->desc.samples = samples;
+    return B200RT_OK;
+}
+
+void b200rt_host_free(b200rt_host_scene *s) { delete s; }
+
+int b200rt_host_write_ppm(const char *path, int32_t width, int32_t height, const uint8_t *rgb) {
+    if (!path || !rgb || width <= 0 || height <= 0) return B200RT_ERR_INVALID;
+    FILE *f = fopen(path, "wb");
+    if (!f) return B200RT_HOST_ERR_IO;
+    fprintf(f, "P6\n%d %d\n255\n", width, height);  // hw8/src/sceneio.cpp:383-385
+    size_t n = (size_t)width * height * 3;
+    size_t w = fwrite(rgb, 1, n, f);
+    fclose(f);
+    return w == n ? B200RT_OK : B200RT_HOST_ERR_IO;
+}
+
+int b200rt_host_timings(const b200rt_host_scene *s, double *parse_ms, double *bvh_ms) {
+    if (!s) return B200RT_ERR_INVALID;
+    if (parse_ms) *parse_ms = s->parse_ms;
+    if (bvh_ms) *bvh_ms = s->bvh_ms;
+    return B200RT_OK;
+}
+
+const char *b200rt_host_strerror(int code) {
+    switch (code) {
+        case B200RT_OK: return "ok";
+        case B200RT_ERR_INVALID: return "invalid argument";
+        case B200RT_HOST_ERR_IO: return "file missing or unreadable";
+        case B200RT_HOST_ERR_PARSE: return "malformed scene (JSON syntax or missing required member)";
+        case B200RT_HOST_ERR_IMAGE: return "image could not be decoded";
+        default: return "unknown error";
+    }
+}
+
+}  // extern "C"
