@@ -1,0 +1,457 @@
+// K1 (hw1 primary cast), K2 (hw2 Whitted), K3 (hw4 analytic path tracer) for sm_100a.
+// Compiled with -fmad=false: every float operation below is written in the reference's own
+// order and with its float/double promotions, so that the deterministic configs (hw1, hw2)
+// reproduce primary-hit indices and radiance bit for bit (north_star).
+//   hw1: hw1/src/scene.cpp:7-30, hw1/src/primitives.cpp:24-91
+//   hw2: hw2/src/scene.cpp:8-99, hw2/src/primitives.cpp:25-137, hw2/src/light_source.cpp:9-23
+//   hw4: hw4/src/scene.cpp:10-128, hw4/src/include/distributions.h:46-205, hw4/src/primitives.cpp:9-118
+// Primitives and lights live in __constant__ memory (<= 64 + 16 entries, warp-uniform reads).
+#include "analytic_kernels.h"
+#include "rt_math.cuh"
+
+namespace b200rt {
+
+__constant__ DAnalyticScene g_scene;
+
+cudaError_t analytic_upload(const DAnalyticScene &scene, cudaStream_t stream) {
+    return cudaMemcpyToSymbolAsync(g_scene, &scene, sizeof(scene), 0, cudaMemcpyHostToDevice, stream);
+}
+
+namespace {
+
+// ---- reference-order float helpers --------------------------------------------------------
+// Vec3::normalize = float(1.0 / double(len)) * v with len = sqrt(x*x + y*y + z*z) (vec3.h:77-79)
+__device__ __forceinline__ V3 rnorm(V3 a) {
+    const float k = (float)(1.0 / (double)sqrtf(dot(a, a)));
+    return k * a;
+}
+// Vec3::cross of the reference = b x a in standard terms, written out in its own order.
+__device__ __forceinline__ V3 rcross(V3 a, V3 b) { return mk(a.z * b.y - a.y * b.z, a.x * b.z - a.z * b.x, a.y * b.x - a.x * b.y); }
+
+struct Quat { V3 v; float w; };
+__device__ __forceinline__ Quat qmul(const Quat &a, const Quat &b) {
+    Quat r;
+    r.v = (a.w * b.v + b.w * a.v) + rcross(a.v, b.v);
+    r.w = a.w * b.w - dot(a.v, b.v);
+    return r;
+}
+__device__ __forceinline__ Quat qconj(const Quat &q) { return Quat{-1.f * q.v, q.w}; }
+__device__ __forceinline__ V3 qtransform(const Quat &q, V3 p) { return qmul(qmul(q, Quat{p, 0.f}), qconj(q)).v; }
+
+struct AHit { float t; V3 n; bool inside; };
+
+__device__ __forceinline__ bool quadratic(float a, float b, float c, float &t, bool &inside) {
+    const float d = b * b - 4 * a * c;
+    if (d <= 0) return false;
+    float x1 = (-b - sqrtf(d)) / (2 * a);
+    float x2 = (-b + sqrtf(d)) / (2 * a);
+    if (x1 > x2) { const float s = x1; x1 = x2; x2 = s; }
+    if (x2 < 0) return false;
+    if (x1 < 0) { t = x2; inside = true; } else { t = x1; inside = false; }
+    return true;
+}
+
+// std::min(a, b) = (b < a) ? b : a ; std::max(a, b) = (a < b) ? b : a  (NaN behaviour)
+__device__ __forceinline__ float smin(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float smax(float a, float b) { return (a < b) ? b : a; }
+
+__device__ __forceinline__ bool box_slabs(V3 s, V3 o, V3 d, float &t, bool &inside) {
+    const V3 ts1 = (-1.f * s - o) / d;
+    const V3 ts2 = (s - o) / d;
+    const float t1x = smin(ts1.x, ts2.x), t2x = smax(ts1.x, ts2.x);
+    const float t1y = smin(ts1.y, ts2.y), t2y = smax(ts1.y, ts2.y);
+    const float t1z = smin(ts1.z, ts2.z), t2z = smax(ts1.z, ts2.z);
+    const float t1 = smax(smax(t1x, t1y), t1z);
+    const float t2 = smin(smin(t2x, t2y), t2z);
+    if (t1 > t2 || t2 < 0) return false;
+    if (t1 < 0) { inside = true; t = t2; } else { inside = false; t = t1; }
+    return true;
+}
+
+// Figure::intersect of hw1..hw4.  WANT_N = false skips the normal (hw1 / shadow rays).
+template <bool WANT_N>
+__device__ __forceinline__ bool hit_prim(const b200rt_primitive &f, V3 o, V3 d, bool plane_tmax, AHit &h) {
+    const Quat q{ld3(f.rotation), f.rotation[3]};
+    const V3 lo = qtransform(q, o - ld3(f.position));
+    const V3 ld = qtransform(q, d);
+    V3 n = mk(0, 0, 0);
+    if (f.type == B200RT_PRIM_ELLIPSOID) {
+        const V3 r = ld3(f.data);
+        const V3 orr = lo / r, dr = ld / r;
+        const float c = dot(orr, orr) - 1;
+        const float b = 2.f * dot(orr, dr);
+        const float a = dot(dr, dr);
+        if (!quadratic(a, b, c, h.t, h.inside)) return false;
+        if (WANT_N) {
+            const V3 point = lo + h.t * ld;
+            n = point / (r * r);
+            if (h.inside) n = -1.f * n;
+            n = rnorm(n);
+        }
+    } else if (f.type == B200RT_PRIM_PLANE) {
+        const V3 pn = ld3(f.data);
+        const float t = -dot(lo, pn) / dot(ld, pn);
+        if (!(t > 0 && (!plane_tmax || t < 1e4f))) return false;
+        h.t = t;
+        if (dot(ld, pn) > 0) { n = -1.f * pn; h.inside = true; } else { n = pn; h.inside = false; }
+    } else {
+        const V3 s = ld3(f.data);
+        if (!box_slabs(s, lo, ld, h.t, h.inside)) return false;
+        if (WANT_N) {
+            const V3 p = lo + h.t * ld;
+            n = p / s;
+            const float mx = smax(smax(fabsf(n.x), fabsf(n.y)), fabsf(n.z));
+            if (fabsf(n.x) != mx) n.x = 0;
+            if (fabsf(n.y) != mx) n.y = 0;
+            if (fabsf(n.z) != mx) n.z = 0;
+            if (h.inside) n = -1.f * n;
+        }
+    }
+    if (WANT_N) h.n = rnorm(qtransform(qconj(q), n));
+    return true;
+}
+
+// Camera of hw1/hw2 (pixel centre +0.5, evaluated in double: hw1/src/scene.cpp:26-27).
+__device__ __forceinline__ V3 camera_dir_center(const DCamera &c, int x, int y) {
+    const float nx = (float)((double)c.tan_x * (2 * (x + 0.5) / c.width - 1));
+    const float ny = (float)((double)c.tan_y * (2 * (y + 0.5) / c.height - 1));
+    return (nx * ld3(c.right) - ny * ld3(c.up)) + ld3(c.forward);
+}
+
+// ---- K1 ------------------------------------------------------------------------------------
+__global__ void cast_kernel(const DCamera cam, float *__restrict__ out, int32_t *__restrict__ ids) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cam.width * cam.height) return;
+    const int x = i % cam.width, y = i / cam.width;
+    const V3 o = ld3(cam.pos), d = camera_dir_center(cam, x, y);
+    V3 ans = ld3(g_scene.bg);
+    float best = -1;
+    int id = -1;
+    for (int k = 0; k < g_scene.n_prims; k++) {
+        AHit h;
+        // hw1 planes have no T_MAX and the nearest test is `best == -1 || t < best` (scene.cpp:13)
+        if (hit_prim<false>(g_scene.prims[k], o, d, false, h) && (best == -1 || h.t < best)) {
+            best = h.t; id = k; ans = ld3(g_scene.prims[k].color);
+        }
+    }
+    out[3 * i] = ans.x; out[3 * i + 1] = ans.y; out[3 * i + 2] = ans.z;
+    ids[i] = id;
+}
+
+// ---- K2 ------------------------------------------------------------------------------------
+__device__ __forceinline__ int closest_prim(V3 o, V3 d, float tmax, bool plane_tmax, AHit &best) {
+    int pos = -1;
+    for (int k = 0; k < g_scene.n_prims; k++) {
+        AHit h;
+        if (hit_prim<true>(g_scene.prims[k], o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best = h; pos = k; }
+    }
+    return pos;
+}
+__device__ __forceinline__ bool occluded(V3 o, V3 d, float tmax) {
+    for (int k = 0; k < g_scene.n_prims; k++) {
+        AHit h;
+        if (hit_prim<false>(g_scene.prims[k], o, d, false, h) && h.t <= tmax) return true;
+    }
+    return false;
+}
+
+#define B200RT_WHITTED_MAX_DEPTH 16
+struct WFrame {
+    V3 o, d;        // incoming ray
+    V3 aux;         // stage 3: reflected colour
+    V3 n;
+    float t;
+    int prim, depth, stage;
+    bool inside;
+};
+
+// Explicit-stack evaluation of the branching recursion Scene::getColor (hw2/src/scene.cpp:29-85),
+// post-order so every float operation happens in the recursion's order.
+__global__ void whitted_kernel(const DCamera cam, int ray_depth, float *__restrict__ out, int32_t *__restrict__ ids) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cam.width * cam.height) return;
+    const int x = i % cam.width, y = i / cam.width;
+    WFrame st[B200RT_WHITTED_MAX_DEPTH + 1];
+    int sp = 0;
+    st[0].o = ld3(cam.pos); st[0].d = camera_dir_center(cam, x, y); st[0].depth = ray_depth; st[0].stage = 0;
+    V3 ret = mk(0, 0, 0);
+    int primary = -1;
+    while (sp >= 0) {
+        WFrame &f = st[sp];
+        if (f.stage == 0) {
+            if (f.depth == 0) { ret = mk(0.f, 0.f, 0.f); sp--; continue; }
+            AHit h;
+            const int pos = closest_prim(f.o, f.d, INFINITY, false, h);
+            if (sp == 0) primary = pos;
+            if (pos < 0) { ret = ld3(g_scene.bg); sp--; continue; }
+            const b200rt_primitive &fig = g_scene.prims[pos];
+            f.t = h.t; f.n = h.n; f.inside = h.inside; f.prim = pos;
+            if (fig.material == B200RT_MAT_DIFFUSE) {
+                V3 color = ld3(g_scene.ambient);
+                for (int li = 0; li < g_scene.n_lights; li++) {
+                    const b200rt_light &L = g_scene.lights[li];
+                    const V3 p = f.o + h.t * f.d;
+                    V3 l, c; float tmax;
+                    if (L.type == B200RT_LIGHT_POINT) {
+                        const V3 direction = ld3(L.v) - p;
+                        const float r = sqrtf(dot(direction, direction));
+                        const float k = (float)(1.0 / (double)(L.attenuation[0] + L.attenuation[1] * r + L.attenuation[2] * r * r));
+                        c = k * ld3(L.intensity);
+                        l = rnorm(direction);
+                        tmax = r;
+                    } else {
+                        l = rnorm(ld3(L.v)); c = ld3(L.intensity); tmax = INFINITY;
+                    }
+                    const float reflected = dot(l, h.n);
+                    if (reflected >= 0 && !occluded(p + 0.0001f * l, l, tmax)) color = color + reflected * c;
+                }
+                ret = color * ld3(fig.color);
+                sp--;
+                continue;
+            }
+            // METALLIC and DIELECTRIC both start with the mirror direction (scene.cpp:53-56)
+            const V3 dn = rnorm(f.d);
+            const V3 rd = dn - (2.f * dot(h.n, dn)) * h.n;
+            f.stage = fig.material == B200RT_MAT_METALLIC ? 1 : 2;
+            WFrame &c = st[sp + 1];
+            c.o = (f.o + h.t * f.d) + 0.0001f * rd; c.d = rd; c.depth = f.depth - 1; c.stage = 0;
+            sp++;
+            continue;
+        }
+        const b200rt_primitive &fig = g_scene.prims[f.prim];
+        if (f.stage == 1) { ret = ld3(fig.color) * ret; sp--; continue; }
+        if (f.stage == 2) {
+            float eta1 = 1.f, eta2 = fig.ior;
+            if (f.inside) { const float s = eta1; eta1 = eta2; eta2 = s; }
+            const V3 l = -1.f * rnorm(f.d);
+            const float nl = dot(f.n, l);
+            const float sin2 = eta1 / eta2 * sqrtf(1 - nl * nl);
+            if (fabsf(sin2) > 1.f) { sp--; continue; }      // total internal reflection: ret = reflected
+            const float cos2 = sqrtf(1 - sin2 * sin2);
+            const V3 rd = (eta1 / eta2) * (-1.f * l) + (eta1 / eta2 * nl - cos2) * f.n;
+            f.aux = ret;
+            f.stage = 3;
+            WFrame &c = st[sp + 1];
+            c.o = (f.o + f.t * f.d) + 0.0001f * rd; c.d = rd; c.depth = f.depth - 1; c.stage = 0;
+            sp++;
+            continue;
+        }
+        {   // stage 3: Schlick blend (scene.cpp:78-84)
+            V3 refr = ret;
+            if (!f.inside) refr = refr * ld3(fig.color);
+            float eta1 = 1.f, eta2 = fig.ior;
+            if (f.inside) { const float s = eta1; eta1 = eta2; eta2 = s; }
+            const V3 l = -1.f * rnorm(f.d);
+            const float q = (eta1 - eta2) / (eta1 + eta2);
+            const float r0 = q * q;                                  // pow(q, 2.) rounds to the float product
+            const double b1 = (double)(1 - dot(f.n, l));
+            const double b2 = b1 * b1;
+            const float r = (float)((double)r0 + (double)(1 - r0) * (b2 * b2 * b1));   // pow(b, 5.) in double
+            ret = r * f.aux + (1 - r) * refr;
+            sp--;
+        }
+    }
+    out[3 * i] = ret.x; out[3 * i + 1] = ret.y; out[3 * i + 2] = ret.z;
+    ids[i] = primary;
+}
+
+// ---- K3: hw4 Monte-Carlo path tracer over analytic primitives ---------------------------------
+// Iterative form of Scene::getColor (hw4/src/scene.cpp:50-108): L += T * emission per hit,
+// T *= bounce weight.  Sampling = Mix{Cosine, Mix{BoxLight | EllipsoidLight ...}}
+// (hw4/src/scene.cpp:10-28, distributions.h:46-205).  Statistical parity only (counter RNG);
+// the stream layout equals oracle/port_mc.cpp's Philox policy draw for draw.
+#define B200RT_PI_F 3.14159274f          /* const float PI = acos(-1) */
+#define B200RT_MAX_REJECTION 8           /* the reference loops unbounded */
+
+__device__ __forceinline__ float light_pdf_one(const b200rt_primitive &f, V3 x, V3 d, V3 y, V3 yn) {
+    const V3 xy = x - y;
+    if (f.type == B200RT_PRIM_BOX) {
+        const float sx = f.data[0], sy = f.data[1], sz = f.data[2];
+        const float s_total = 8 * (sy * sz + sx * sz + sx * sy);
+        return dot(xy, xy) / (s_total * fabsf(dot(d, yn)));
+    }
+    const V3 r = ld3(f.data);
+    const Quat q{ld3(f.rotation), f.rotation[3]};
+    const V3 n = qtransform(q, y - ld3(f.position)) / r;
+    const V3 g = mk(n.x * r.y * r.z, r.x * n.y * r.z, r.x * r.y * n.z);
+    const float point_prob = 1.f / (4 * B200RT_PI_F * sqrtf(dot(g, g)));
+    return point_prob * dot(xy, xy) / fabsf(dot(d, yn));
+}
+// FigureLight::pdf (distributions.h:85-106): first hit plus the second hit from just behind it.
+__device__ __forceinline__ float light_pdf(const b200rt_primitive &f, V3 x, V3 d) {
+    AHit h1;
+    if (!hit_prim<true>(f, x, d, true, h1)) return 0.f;
+    if (isnan(h1.t)) return INFINITY;
+    float ans = light_pdf_one(f, x, d, x + h1.t * d, h1.n);
+    AHit h2;
+    if (!hit_prim<true>(f, x + (h1.t + 0.0001f) * d, d, true, h2)) return ans;
+    return ans + light_pdf_one(f, x, d, x + (h1.t + 0.0001f + h2.t) * d, h2.n);
+}
+
+__device__ __forceinline__ V3 light_sample(const b200rt_primitive &f, V3 x, Rng &rng) {
+    const Quat q{ld3(f.rotation), f.rotation[3]};
+    V3 dir = mk(0, 0, 1);
+    for (int iter = 0; iter < B200RT_MAX_REJECTION; iter++) {
+        V3 point;
+        if (f.type == B200RT_PRIM_BOX) {
+            const float sx = f.data[0], sy = f.data[1], sz = f.data[2];
+            const float wx = sy * sz, wy = sx * sz, wz = sx * sy;
+            const float u = rng.u() * (wx + wy + wz);
+            const float flip = rng.u() > 0.5f ? 1.f : -1.f;
+            const float a = rng.u(), b = rng.u();
+            if (u < wx) point = mk(flip * sx, (2 * a - 1) * sy, (2 * b - 1) * sz);
+            else if (u < wx + wy) point = mk((2 * a - 1) * sx, flip * sy, (2 * b - 1) * sz);
+            else point = mk((2 * a - 1) * sx, (2 * b - 1) * sy, flip * sz);
+        } else {
+            const float u1 = rng.u(), u2 = rng.u();
+            point = ld3(f.data) * sphere_dir(u1, u2);
+        }
+        const V3 actual = qtransform(qconj(q), point) + ld3(f.position);
+        dir = rnorm(actual - x);
+        AHit h;
+        if (hit_prim<false>(f, x, dir, true, h)) break;
+    }
+    return dir;
+}
+
+__global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp) {
+    const int W = rp.cam.width, H = rp.cam.height;
+    const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
+    const long long n_tiles = (long long)tiles_x * tiles_y;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    unsigned paths = 0, rays = 0;
+    if (warp_id < n_tiles * rp.n_chunks) {
+        const int chunk = (int)(warp_id / n_tiles);
+        const long long tile = warp_id % n_tiles;
+        const int px = (int)(tile % tiles_x) * 8 + (lane & 7);
+        const int py = (int)(tile / tiles_x) * 4 + (lane >> 3);
+        if (px < W && py < H) {
+            const int total = rp.spp_end - rp.spp_begin;
+            const int per = (total + rp.n_chunks - 1) / rp.n_chunks;
+            const int s0 = rp.spp_begin + chunk * per;
+            const int s1 = min(rp.spp_end, s0 + per);
+            Rng rng;
+            rng.pixel = (uint32_t)(py * W + px); rng.seed = rp.seed;
+            const int n_lights = g_scene.n_light_prims;
+            V3 sum = mk(0, 0, 0);
+            for (int s = s0; s < s1; s++) {
+                rng.begin_sample((uint32_t)s);
+                // hw4 camera: jitter only, no +0.5, fovX based, NOT normalised (scene.cpp:113-128)
+                const float fx = (float)px + rng.u();
+                const float fy = (float)py + rng.u();
+                const float nx = rp.cam.tan_x * (2 * fx / W - 1);
+                const float ny = rp.cam.tan_y * (2 * fy / H - 1);
+                V3 o = ld3(rp.cam.pos);
+                V3 d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
+                V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
+                paths++;
+                for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
+                    AHit h;
+                    rays++;
+                    const int pos = closest_prim(o, d, INFINITY, true, h);
+                    if (pos < 0) { L = L + T * ld3(g_scene.bg); break; }
+                    rng.begin_bounce((uint32_t)bounce);
+                    const b200rt_primitive &f = g_scene.prims[pos];
+                    const V3 x = o + h.t * d;
+                    L = L + T * ld3(f.emission);
+                    if (f.material == B200RT_MAT_DIFFUSE) {
+                        const V3 xs = x + 0.0001f * h.n;
+                        // Mix::sample: uniform choice between Cosine and the light mixture
+                        const int k = n_lights > 0 ? 2 : 1;
+                        const int which = (int)(rng.u() * k);
+                        V3 nd;
+                        if (which == 0) {
+                            const float u1 = rng.u(), u2 = rng.u();
+                            V3 c = sphere_dir(u1, u2) + h.n;
+                            const float l = sqrtf(dot(c, c));
+                            nd = (l <= 1e-9f || dot(c, h.n) <= 1e-9f || isnan(l)) ? h.n : (1.f / l) * c;
+                        } else {
+                            const int li = min((int)(rng.u() * n_lights), n_lights - 1);
+                            nd = light_sample(g_scene.prims[g_scene.light_prims[li]], xs, rng);
+                        }
+                        if (dot(nd, h.n) < 0) break;
+                        float pdf = smax(0.f, dot(nd, h.n) / B200RT_PI_F);
+                        if (n_lights > 0) {
+                            float inner = 0;
+                            for (int li = 0; li < n_lights; li++) inner += light_pdf(g_scene.prims[g_scene.light_prims[li]], xs, nd);
+                            pdf = (pdf + inner / n_lights) / 2;
+                        }
+                        const float w = (1.f / (B200RT_PI_F * pdf)) * dot(nd, h.n);
+                        T = T * (w * ld3(f.color));
+                        o = x + 0.0001f * nd; d = nd;
+                    } else {
+                        const V3 dn = rnorm(d);
+                        const V3 rd = dn - (2.f * dot(h.n, dn)) * h.n;
+                        bool reflect = true;
+                        V3 nd = rd;
+                        if (f.material == B200RT_MAT_METALLIC) {
+                            T = T * ld3(f.color);
+                        } else {
+                            // Fresnel coin first (counter RNG: same estimator as tracing the reflected
+                            // branch before the coin)
+                            const float coin = rng.u();
+                            float eta1 = 1.f, eta2 = f.ior;
+                            if (h.inside) { const float sw = eta1; eta1 = eta2; eta2 = sw; }
+                            const V3 l = -1.f * dn;
+                            const float nl = dot(h.n, l);
+                            const float sin2 = eta1 / eta2 * sqrtf(1 - nl * nl);
+                            if (!(fabsf(sin2) > 1.f)) {
+                                const float q = (eta1 - eta2) / (eta1 + eta2);
+                                const float r0 = q * q;
+                                const float b1 = 1 - nl, b2 = b1 * b1;
+                                const float r = r0 + (1 - r0) * (b2 * b2 * b1);
+                                if (!(coin < r)) {
+                                    const float cos2 = sqrtf(1 - sin2 * sin2);
+                                    nd = (eta1 / eta2) * (-1.f * l) + (eta1 / eta2 * nl - cos2) * h.n;
+                                    reflect = false;
+                                    if (!h.inside) T = T * ld3(f.color);
+                                }
+                            }
+                        }
+                        (void)reflect;
+                        o = x + 0.0001f * nd; d = nd;
+                    }
+                }
+                sum = sum + L;
+            }
+            float *dst = rp.accum + ((size_t)chunk * W * H + (size_t)(py * W + px)) * 3;
+            dst[0] = sum.x; dst[1] = sum.y; dst[2] = sum.z;
+        }
+    }
+    // per-warp counter flush
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        paths += __shfl_down_sync(0xffffffffu, paths, off);
+        rays += __shfl_down_sync(0xffffffffu, rays, off);
+    }
+    if (lane == 0 && paths) {
+        atomicAdd(&rp.counters->paths, (unsigned long long)paths);
+        atomicAdd(&rp.counters->rays, (unsigned long long)rays);
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_cast(const DCamera &cam, float *out, int32_t *ids, cudaStream_t stream) {
+    const int n = cam.width * cam.height;
+    cast_kernel<<<(n + 127) / 128, 128, 0, stream>>>(cam, out, ids);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_whitted(const DCamera &cam, int ray_depth, float *out, int32_t *ids, cudaStream_t stream) {
+    if (ray_depth > B200RT_WHITTED_MAX_DEPTH) return cudaErrorInvalidValue;
+    const int n = cam.width * cam.height;
+    whitted_kernel<<<(n + 63) / 64, 64, 0, stream>>>(cam, ray_depth, out, ids);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pt_analytic(const DRenderParams &rp, cudaStream_t stream) {
+    const long long tiles = (long long)((rp.cam.width + 7) / 8) * ((rp.cam.height + 3) / 4);
+    const long long warps = tiles * rp.n_chunks;
+    const long long blocks = (warps * 32 + 127) / 128;
+    pt_analytic_kernel<<<(unsigned)blocks, 128, 0, stream>>>(rp);
+    return cudaGetLastError();
+}
+
+}  // namespace b200rt

@@ -1,0 +1,611 @@
+// C ABI of the B200 render core: context, scene flattening + upload, launches, resolve.
+// See include/b200rt.h for the contract and the reference call sites each entry replaces.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "analytic_kernels.h"
+#include "b200rt.h"
+#include "device_scene.h"
+#include "gltf_kernel.cuh"
+
+using namespace b200rt;
+
+struct b200rt_ctx {
+    int device = 0;
+    uint32_t seed = 0;
+    int flags = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string last_error;
+
+    bool has_scene = false;
+    b200rt_scene_desc desc{};     // scalar fields only (pointers are not retained)
+    DGltfScene gs{};
+    std::vector<void *> allocations;
+    std::vector<cudaArray_t> arrays;
+    std::vector<cudaTextureObject_t> textures;
+    float *lut_srgb = nullptr;
+
+    int acc_w = 0, acc_h = 0, n_slabs = 0;
+    float *total = nullptr, *slabs = nullptr;
+    uint8_t *rgb8 = nullptr;
+    int32_t *ids = nullptr;
+    DCounters *counters = nullptr;
+    b200rt_stats stats{};
+    bool timing_pending = false;
+};
+
+namespace {
+
+int fail(b200rt_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (c) {
+        c->last_error = what;
+        if (e != cudaSuccess) { c->last_error += ": "; c->last_error += cudaGetErrorString(e); }
+    }
+    return code;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, B200RT_ERR_CUDA, #call, e_); } while (0)
+
+template <class T>
+int dev_upload(b200rt_ctx *ctx, const std::vector<T> &host, const T **out) {
+    *out = nullptr;
+    size_t bytes = std::max<size_t>(host.size(), 1) * sizeof(T);
+    void *p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    ctx->allocations.push_back(p);
+    if (!host.empty()) CK(cudaMemcpyAsync(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *out = static_cast<const T *>(p);
+    return B200RT_OK;
+}
+
+void release_scene(b200rt_ctx *c) {
+    for (auto t : c->textures) cudaDestroyTextureObject(t);
+    for (auto a : c->arrays) cudaFreeArray(a);
+    for (auto p : c->allocations) cudaFree(p);
+    c->textures.clear(); c->arrays.clear(); c->allocations.clear();
+    c->has_scene = false;
+}
+
+// ---- BVH flattening: reference-shaped 40-byte nodes -> 32-byte sibling-pair layout ------------
+struct Flattener {
+    const b200rt_bvh_node *ref;
+    const b200rt_triangle *tris;
+    std::vector<DNode> out;
+    int max_depth = 0;
+
+    static void tri_box(const b200rt_triangle &t, float *mn, float *mx) {
+        for (int a = 0; a < 3; a++) {
+            mn[a] = std::min(t.p[0][a], std::min(t.p[1][a], t.p[2][a]));
+            mx[a] = std::max(t.p[0][a], std::max(t.p[1][a], t.p[2][a]));
+        }
+    }
+    void range_box(uint32_t first, uint32_t last, DNode &n) const {
+        float mn[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
+        for (uint32_t i = first; i < last; i++) {
+            float a[3], b[3];
+            tri_box(tris[i], a, b);
+            for (int k = 0; k < 3; k++) {
+                mn[k] = i == first ? a[k] : std::min(mn[k], a[k]);
+                mx[k] = i == first ? b[k] : std::max(mx[k], b[k]);
+            }
+        }
+        n.mnx = mn[0]; n.mny = mn[1]; n.mnz = mn[2]; n.mxx = mx[0]; n.mxy = mx[1]; n.mxz = mx[2];
+    }
+    void ref_box(uint32_t r, DNode &n) const {
+        n.mnx = ref[r].aabb_min[0]; n.mny = ref[r].aabb_min[1]; n.mnz = ref[r].aabb_min[2];
+        n.mxx = ref[r].aabb_max[0]; n.mxy = ref[r].aabb_max[1]; n.mxz = ref[r].aabb_max[2];
+    }
+    // A node is either a reference node (r >= 0) or a virtual range produced by splitting a
+    // leaf with more than 15 triangles (closest-hit results are tree-independent).
+    uint32_t emit(long r, uint32_t first, uint32_t last, int depth) {
+        max_depth = std::max(max_depth, depth);
+        bool leaf = r < 0 || ref[r].left == 0;
+        if (r >= 0) { first = ref[r].first; last = ref[r].last; }
+        if (leaf && last - first <= 15) return B200RT_LEAF | ((last - first) << 27) | first;
+        uint32_t pair = (uint32_t)out.size();
+        out.resize(out.size() + 2);
+        DNode l{}, rr{};
+        if (leaf) {
+            uint32_t mid = first + (last - first) / 2;
+            range_box(first, mid, l); range_box(mid, last, rr);
+            uint32_t ml = emit(-1, first, mid, depth + 1), mr = emit(-1, mid, last, depth + 1);
+            l.a = ml; rr.a = mr;
+        } else {
+            ref_box(ref[r].left, l); ref_box(ref[r].right, rr);
+            uint32_t ml = emit(ref[r].left, 0, 0, depth + 1), mr = emit(ref[r].right, 0, 0, depth + 1);
+            l.a = ml; rr.a = mr;
+        }
+        l.b = (l.a & B200RT_LEAF) ? ((l.a >> 27) & 15u) : 0;
+        rr.b = (rr.a & B200RT_LEAF) ? ((rr.a >> 27) & 15u) : 0;
+        out[pair] = l; out[pair + 1] = rr;
+        return pair;
+    }
+    void run(const b200rt_bvh_node *nodes, int n_nodes, int root, const b200rt_triangle *t, int n_tris) {
+        ref = nodes; tris = t;
+        out.assign(2, DNode{});
+        if (n_nodes <= 0 || n_tris <= 0) { out[0].a = B200RT_LEAF; return; }
+        ref_box((uint32_t)root, out[0]);
+        uint32_t meta = emit(root, 0, 0, 1);
+        out[0].a = meta;
+        out[0].b = (meta & B200RT_LEAF) ? ((meta >> 27) & 15u) : 0;
+    }
+};
+
+float __int_as_float_host(int v) { float f; memcpy(&f, &v, 4); return f; }
+
+DTri make_tri(const b200rt_triangle &t) {
+    DTri d;
+    d.v0 = make_float4(t.p[2][0], t.p[2][1], t.p[2][2], 0.f);
+    d.e1 = make_float4(t.p[0][0] - t.p[2][0], t.p[0][1] - t.p[2][1], t.p[0][2] - t.p[2][2], t.tan[0][3]);
+    d.e2 = make_float4(t.p[1][0] - t.p[2][0], t.p[1][1] - t.p[2][1], t.p[1][2] - t.p[2][2], 0.f);
+    return d;
+}
+
+bool validate_tree(const b200rt_bvh_node *nodes, int n_nodes, int root, int n_tris) {
+    if (n_tris == 0) return true;
+    if (!nodes || root < 0 || root >= n_nodes) return false;
+    for (int i = 0; i < n_nodes; i++) {
+        const auto &n = nodes[i];
+        if (n.left == 0) { if (n.first > n.last || n.last > (uint32_t)n_tris) return false; }
+        else if (n.left >= (uint32_t)n_nodes || n.right >= (uint32_t)n_nodes || n.left <= (uint32_t)i || n.right <= (uint32_t)i) return false;
+    }
+    return true;
+}
+
+}  // namespace
+
+// ---- small kernels ---------------------------------------------------------------------------
+// Adds the per-chunk slabs to the running total in a fixed order (deterministic sum).
+__global__ void fold_slabs_kernel(float *__restrict__ total, const float *__restrict__ slabs, int n_slabs, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float acc = total[i];
+    for (int s = 0; s < n_slabs; s++) acc += slabs[(size_t)s * n + i];
+    total[i] = acc;
+}
+
+// K5 resolve: mean, ACES fit, clamp, gamma 1/2.2, round to RGB8 (hw8/src/color.cpp:4-31,
+// hw8/src/scene.cpp:176).  hw1 quantises the raw colour (hw1/src/color.cpp:13-19).
+// The gamma pow is evaluated in double: the reference calls double pow() in hw4-hw8 and powf in
+// hw2; rounding the double result to float reproduces both except on exact rounding ties.
+__global__ void resolve_kernel(const float *__restrict__ total, uint8_t *__restrict__ rgb, size_t n_px, float inv_spp, int tonemap) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_px) return;
+    const float gamma = (float)(1. / 2.2);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        float x = inv_spp * total[3 * i + c];
+        if (tonemap) {
+            const float a = 2.51f, b = 0.03f, cc = 2.43f, d = 0.59f, e = 0.14f;
+            float num = __fmul_rn(x, __fadd_rn(__fmul_rn(a, x), b));
+            float den = __fadd_rn(__fmul_rn(x, __fadd_rn(__fmul_rn(cc, x), d)), e);
+            float y = __fdiv_rn(num, den);
+            y = fminf(1.f, fmaxf(0.f, y));
+            x = (float)pow((double)y, (double)gamma);
+        }
+        float q = roundf(__fmul_rn(255.f, x));
+        rgb[3 * i + c] = (uint8_t)q;
+    }
+}
+
+namespace {
+
+int make_texture(b200rt_ctx *ctx, const b200rt_image &img, cudaTextureObject_t *out) {
+    *out = 0;
+    if (!img.rgb || img.width <= 0 || img.height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
+    std::vector<uchar4> rgba((size_t)img.width * img.height);
+    for (size_t i = 0; i < rgba.size(); i++) rgba[i] = make_uchar4(img.rgb[3 * i], img.rgb[3 * i + 1], img.rgb[3 * i + 2], 255);
+    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+    cudaArray_t arr = nullptr;
+    CK(cudaMallocArray(&arr, &fmt, (size_t)img.width, (size_t)img.height));
+    ctx->arrays.push_back(arr);
+    CK(cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)img.width * 4, (size_t)img.width * 4, (size_t)img.height, cudaMemcpyHostToDevice));
+    cudaResourceDesc rd{};
+    rd.resType = cudaResourceTypeArray;
+    rd.res.array.array = arr;
+    cudaTextureDesc td{};
+    td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint;          // the bilinear blend is done in the kernel
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    cudaTextureObject_t tex = 0;
+    CK(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
+    ctx->textures.push_back(tex);
+    *out = tex;
+    return B200RT_OK;
+}
+
+int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
+    if (s->n_tris < 0 || s->n_tris >= (1 << 27)) return fail(ctx, B200RT_ERR_INVALID, "triangle count out of range");
+    if (s->n_tris > 0 && (!s->tris || !s->materials)) return fail(ctx, B200RT_ERR_INVALID, "missing triangle/material arrays");
+    if (!validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
+    if (s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
+    for (int i = 0; i < s->n_tris; i++) if (s->tris[i].material >= (uint32_t)s->n_materials) return fail(ctx, B200RT_ERR_INVALID, "material index out of range");
+
+    DGltfScene g{};
+    g.hw8 = s->mode == B200RT_MODE_HW8;
+    for (int k = 0; k < 3; k++) g.bg[k] = s->bg_color[k];
+    int rc;
+
+    Flattener fl;
+    fl.run(s->nodes, s->n_nodes, s->root, s->tris, s->n_tris);
+    if (fl.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "scene BVH deeper than the traversal stack");
+    if ((rc = dev_upload(ctx, fl.out, &g.nodes))) return rc;
+
+    std::vector<DTri> tris((size_t)s->n_tris);
+    std::vector<DShade> shade((size_t)s->n_tris);
+    for (int i = 0; i < s->n_tris; i++) {
+        const b200rt_triangle &t = s->tris[i];
+        tris[i] = make_tri(t);
+        tris[i].v0.w = __int_as_float_host((int)t.material);
+        DShade &q = shade[i];
+        q.q[0] = make_float4(t.n[0][0], t.n[0][1], t.n[0][2], t.uv[0][0]);
+        q.q[1] = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], t.uv[0][1]);
+        q.q[2] = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], t.uv[1][0]);
+        q.q[3] = make_float4(t.tan[0][0], t.tan[0][1], t.tan[0][2], t.uv[1][1]);
+        q.q[4] = make_float4(t.tan[1][0], t.tan[1][1], t.tan[1][2], t.uv[2][0]);
+        q.q[5] = make_float4(t.tan[2][0], t.tan[2][1], t.tan[2][2], t.uv[2][1]);
+    }
+    if ((rc = dev_upload(ctx, tris, &g.tris))) return rc;
+    if ((rc = dev_upload(ctx, shade, &g.shade))) return rc;
+
+    // lights: FiguresMix::figures_ + its BVH (hw8/src/include/distributions.h:99-115)
+    g.n_light_tris = s->n_light_tris;
+    Flattener ll;
+    ll.run(s->light_nodes, s->n_light_nodes, 0, s->light_tris, s->n_light_tris);
+    if (ll.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "light BVH deeper than the traversal stack");
+    if ((rc = dev_upload(ctx, ll.out, &g.light_nodes))) return rc;
+    std::vector<DTri> ltris((size_t)s->n_light_tris);
+    std::vector<DLightNormals> lnorm((size_t)s->n_light_tris);
+    for (int i = 0; i < s->n_light_tris; i++) {
+        const b200rt_triangle &t = s->light_tris[i];
+        ltris[i] = make_tri(t);
+        // pointProb = 1.0 / (0.5 * |b.cross(c)|) in the reference's float/double mix (distributions.h:71-76)
+        float bx = ltris[i].e1.x, by = ltris[i].e1.y, bz = ltris[i].e1.z, cx = ltris[i].e2.x, cy = ltris[i].e2.y, cz = ltris[i].e2.z;
+        float nx = bz * cy - by * cz, ny = bx * cz - bz * cx, nz = by * cx - bx * cy;
+        float len = (float)std::sqrt((double)(nx * nx + ny * ny + nz * nz));
+        ltris[i].v0.w = (float)(1.0 / (0.5 * len));
+        lnorm[i].n0 = make_float4(t.n[0][0], t.n[0][1], t.n[0][2], 0);
+        lnorm[i].n1 = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], 0);
+        lnorm[i].n2 = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], 0);
+    }
+    if ((rc = dev_upload(ctx, ltris, &g.light_tris))) return rc;
+    if ((rc = dev_upload(ctx, lnorm, &g.light_normals))) return rc;
+
+    // textures: one point-sampled RGBA8 texture object per image (hw8 only)
+    std::vector<cudaTextureObject_t> tex((size_t)std::max(0, s->n_images), 0);
+    if (g.hw8)
+        for (int i = 0; i < s->n_images; i++)
+            if ((rc = make_texture(ctx, s->images[i], &tex[i]))) return rc;
+    std::vector<DMaterial> mats((size_t)s->n_materials);
+    for (int i = 0; i < s->n_materials; i++) {
+        const b200rt_material &m = s->materials[i];
+        DMaterial &d = mats[i];
+        memset(&d, 0, sizeof(d));
+        for (int k = 0; k < 3; k++) { d.base_color[k] = m.base_color[k]; d.emission[k] = m.emission[k]; }
+        d.metallic_factor = m.metallic_factor; d.roughness_factor = m.roughness_factor;
+        auto bind = [&](int32_t idx, cudaTextureObject_t &t, int32_t &w, int32_t &h) -> bool {
+            if (!g.hw8 || idx < 0) return true;
+            if (idx >= s->n_images) return false;
+            t = tex[idx]; w = s->images[idx].width; h = s->images[idx].height;
+            return true;
+        };
+        if (!bind(m.base_color_image, d.tex_base, d.w_base, d.h_base) || !bind(m.emissive_image, d.tex_emissive, d.w_emissive, d.h_emissive) ||
+            !bind(m.metallic_roughness_image, d.tex_mr, d.w_mr, d.h_mr) || !bind(m.normal_image, d.tex_normal, d.w_normal, d.h_normal))
+            return fail(ctx, B200RT_ERR_INVALID, "image index out of range");
+    }
+    if ((rc = dev_upload(ctx, mats, &g.materials))) return rc;
+    if (g.hw8 && s->env_map) {
+        if ((rc = make_texture(ctx, *s->env_map, &g.env))) return rc;
+        g.env_w = s->env_map->width; g.env_h = s->env_map->height;
+    }
+    // sRGB decode table with the reference's own arithmetic: powf(float(1./255) * c, 2.2f) (scene.cpp:11-13)
+    std::vector<float> lut(256);
+    for (int c = 0; c < 256; c++) lut[c] = std::pow((float)(1. / 255) * (1.f * (float)c), 2.2f);
+    const float *lp = nullptr;
+    if ((rc = dev_upload(ctx, lut, &lp))) return rc;
+    ctx->lut_srgb = const_cast<float *>(lp);
+    ctx->gs = g;
+    return B200RT_OK;
+}
+
+int ensure_buffers(b200rt_ctx *ctx, int w, int h, int n_slabs) {
+    size_t n = (size_t)w * h * 3;
+    if (w != ctx->acc_w || h != ctx->acc_h) {
+        cudaFree(ctx->total); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->slabs);
+        ctx->total = nullptr; ctx->rgb8 = nullptr; ctx->ids = nullptr; ctx->slabs = nullptr; ctx->n_slabs = 0;
+        CK(cudaMalloc(&ctx->total, n * sizeof(float)));
+        CK(cudaMalloc(&ctx->rgb8, n));
+        CK(cudaMalloc(&ctx->ids, (size_t)w * h * sizeof(int32_t)));
+        CK(cudaMemsetAsync(ctx->total, 0, n * sizeof(float), ctx->stream));
+        ctx->acc_w = w; ctx->acc_h = h;
+    }
+    if (n_slabs > ctx->n_slabs) {
+        cudaFree(ctx->slabs); ctx->slabs = nullptr;
+        CK(cudaMalloc(&ctx->slabs, n * sizeof(float) * (size_t)n_slabs));
+        ctx->n_slabs = n_slabs;
+    }
+    return B200RT_OK;
+}
+
+// tan of the half field of view with the libm call the reference's TU binds to (hw1/hw2 include
+// <math.h> => tanf; hw3..hw8 include only <cmath> => double tan rounded to float).
+void camera_of(const b200rt_scene_desc &d, int w, int h, DCamera &c) {
+    for (int k = 0; k < 3; k++) { c.pos[k] = d.cam_pos[k]; c.right[k] = d.cam_right[k]; c.up[k] = d.cam_up[k]; c.forward[k] = d.cam_forward[k]; }
+    float half = d.cam_fov / 2;
+    float t = d.mode <= B200RT_MODE_HW2 ? tanf(half) : (float)std::tan((double)half);
+    if (d.mode <= B200RT_MODE_HW5) { c.tan_x = t; c.tan_y = t * h / w; }   // fovX based (hw4/src/scene.cpp:121-122)
+    else { c.tan_y = t; c.tan_x = t * w / h; }                             // fovY based (hw8/src/scene.cpp:180-181)
+    c.width = w; c.height = h;
+}
+
+}  // namespace
+
+// ================================== C ABI =====================================================
+extern "C" {
+
+int b200rt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
+    if (!out) return B200RT_ERR_INVALID;
+    *out = nullptr;
+    int n = b200rt_device_count();
+    if (n <= 0) return B200RT_ERR_NO_DEVICE;       // no CPU fallback
+    int dev = opt ? opt->device : 0;
+    if (dev < 0 || dev >= n) return B200RT_ERR_INVALID;
+    b200rt_ctx *ctx = new (std::nothrow) b200rt_ctx();
+    if (!ctx) return B200RT_ERR_INVALID;
+    ctx->device = dev;
+    ctx->seed = opt ? opt->seed : 0;
+    ctx->flags = opt ? opt->flags : 0;
+    cudaError_t e;
+    if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->counters, sizeof(DCounters))) != cudaSuccess) {
+        delete ctx;
+        return B200RT_ERR_CUDA;
+    }
+    *out = ctx;
+    return B200RT_OK;
+}
+
+void b200rt_destroy(b200rt_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    release_scene(ctx);
+    cudaFree(ctx->total); cudaFree(ctx->slabs); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->counters);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
+    if (!ctx || !s) return B200RT_ERR_INVALID;
+    if (s->width <= 0 || s->height <= 0 || s->samples <= 0) return fail(ctx, B200RT_ERR_INVALID, "bad frame size / sample count");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    release_scene(ctx);
+    int rc = B200RT_OK;
+    switch (s->mode) {
+        case B200RT_MODE_HW1: case B200RT_MODE_HW2: case B200RT_MODE_HW4: {
+            if (s->n_prims < 0 || s->n_prims > B200RT_MAX_PRIMS || s->n_lights < 0 || s->n_lights > B200RT_MAX_LIGHTS)
+                return fail(ctx, B200RT_ERR_UNSUPPORTED, "too many primitives/lights for the analytic kernels");
+            if ((s->n_prims && !s->prims) || (s->n_lights && !s->lights)) return fail(ctx, B200RT_ERR_INVALID, "missing primitive/light arrays");
+            static DAnalyticScene a;   // 9 KB: keep off the stack; a ctx is driven by one thread
+            memset(&a, 0, sizeof(a));
+            for (int i = 0; i < s->n_prims; i++) {
+                a.prims[i] = s->prims[i];
+                if (a.prims[i].type == B200RT_PRIM_TRIANGLE) return fail(ctx, B200RT_ERR_UNSUPPORTED, "TRIANGLE primitives (hw5) not implemented");
+                // hw4 light set: emissive BOX / ELLIPSOID (hw4/src/scene.cpp:12-19)
+                const float *e = s->prims[i].emission;
+                if ((e[0] > 0 || e[1] > 0 || e[2] > 0) && (s->prims[i].type == B200RT_PRIM_BOX || s->prims[i].type == B200RT_PRIM_ELLIPSOID))
+                    a.light_prims[a.n_light_prims++] = i;
+            }
+            for (int i = 0; i < s->n_lights; i++) a.lights[i] = s->lights[i];
+            a.n_prims = s->n_prims; a.n_lights = s->n_lights; a.mode = s->mode;
+            for (int k = 0; k < 3; k++) { a.bg[k] = s->bg_color[k]; a.ambient[k] = s->ambient[k]; }
+            CK(analytic_upload(a, ctx->stream));
+            break;
+        }
+        case B200RT_MODE_HW7: case B200RT_MODE_HW8:
+            rc = upload_gltf(ctx, s);
+            break;
+        default:
+            return fail(ctx, B200RT_ERR_UNSUPPORTED, "scene mode not implemented on the device path (hw3, hw5, hw6)");
+    }
+    if (rc) { release_scene(ctx); return rc; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->desc = *s;
+    ctx->desc.prims = nullptr; ctx->desc.lights = nullptr; ctx->desc.tris = nullptr; ctx->desc.nodes = nullptr;
+    ctx->desc.light_tris = nullptr; ctx->desc.light_nodes = nullptr; ctx->desc.materials = nullptr; ctx->desc.images = nullptr; ctx->desc.env_map = nullptr;
+    ctx->has_scene = true;
+    return b200rt_clear(ctx);
+}
+
+int b200rt_clear(b200rt_ctx *ctx) {
+    if (!ctx) return B200RT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->total) CK(cudaMemsetAsync(ctx->total, 0, (size_t)ctx->acc_w * ctx->acc_h * 3 * sizeof(float), ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_begin, int32_t spp_end, int32_t ray_depth) {
+    if (!ctx) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "render before upload_scene");
+    const b200rt_scene_desc &d = ctx->desc;
+    if (width <= 0) width = d.width;
+    if (height <= 0) height = d.height;
+    if (ray_depth <= 0) ray_depth = d.ray_depth;
+    const bool deterministic = d.mode == B200RT_MODE_HW1 || d.mode == B200RT_MODE_HW2;
+    if (deterministic) { spp_begin = 0; spp_end = 1; }
+    if (spp_begin < 0 || spp_end <= spp_begin) return fail(ctx, B200RT_ERR_INVALID, "empty sample range");
+    if ((long long)width * height > (1ll << 30)) return fail(ctx, B200RT_ERR_INVALID, "frame too large");
+    CK(cudaSetDevice(ctx->device));
+
+    // enough warps to fill 148 SMs several times over even for small frames
+    const long long n_px = (long long)width * height;
+    int n_chunks = 1;
+    if (!deterministic) {
+        const long long want = 148ll * 2048 * 4;
+        n_chunks = (int)std::min<long long>({(want + n_px - 1) / n_px, (long long)(spp_end - spp_begin), 256ll});
+        n_chunks = std::max(n_chunks, 1);
+    }
+    int rc = ensure_buffers(ctx, width, height, n_chunks);
+    if (rc) return rc;
+
+    DRenderParams rp{};
+    camera_of(d, width, height, rp.cam);
+    rp.spp_begin = spp_begin; rp.spp_end = spp_end; rp.n_chunks = n_chunks; rp.ray_depth = ray_depth;
+    rp.seed = ctx->seed; rp.accum = ctx->slabs; rp.counters = ctx->counters;
+
+    CK(cudaMemsetAsync(ctx->counters, 0, sizeof(DCounters), ctx->stream));
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    int launches = 0;
+    if (d.mode == B200RT_MODE_HW1) { CK(launch_cast(rp.cam, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
+    else if (d.mode == B200RT_MODE_HW2) { CK(launch_whitted(rp.cam, ray_depth, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
+    else if (d.mode == B200RT_MODE_HW4) { CK(launch_pt_analytic(rp, ctx->stream)); launches++; }
+    else {
+        const int tiles = ((width + 7) / 8) * ((height + 3) / 4);
+        const long long warps = (long long)tiles * n_chunks;
+        const int block = 128;
+        const long long blocks = (warps * 32 + block - 1) / block;
+        if (blocks > 0x7fffffffll) return fail(ctx, B200RT_ERR_INVALID, "grid too large");
+        const bool count = ctx->flags & B200RT_FLAG_COUNTERS;
+        dim3 g((unsigned)blocks), b(block);
+        if (ctx->gs.hw8) {
+            if (count) gltf_path_kernel<true, true><<<g, b, 0, ctx->stream>>>(ctx->gs, rp, ctx->lut_srgb);
+            else gltf_path_kernel<true, false><<<g, b, 0, ctx->stream>>>(ctx->gs, rp, ctx->lut_srgb);
+        } else {
+            if (count) gltf_path_kernel<false, true><<<g, b, 0, ctx->stream>>>(ctx->gs, rp, ctx->lut_srgb);
+            else gltf_path_kernel<false, false><<<g, b, 0, ctx->stream>>>(ctx->gs, rp, ctx->lut_srgb);
+        }
+        CK(cudaGetLastError());
+        launches++;
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    {
+        const size_t n = (size_t)n_px * 3;
+        fold_slabs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->total, ctx->slabs, n_chunks, n);
+        CK(cudaGetLastError());
+        launches++;
+    }
+    ctx->stats.launches = launches;
+    ctx->timing_pending = true;
+    return B200RT_OK;
+}
+
+int b200rt_synchronize(b200rt_ctx *ctx) {
+    if (!ctx) return B200RT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_resolve(b200rt_ctx *ctx, int32_t total_spp, uint8_t *rgb_out) {
+    if (!ctx || !rgb_out) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene || !ctx->total) return fail(ctx, B200RT_ERR_NO_SCENE, "resolve before render");
+    if (total_spp <= 0) return fail(ctx, B200RT_ERR_INVALID, "total_spp must be positive");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n_px = (size_t)ctx->acc_w * ctx->acc_h;
+    const bool hw1 = ctx->desc.mode == B200RT_MODE_HW1;
+    const float inv = (ctx->desc.mode <= B200RT_MODE_HW2) ? 1.f : (float)(1.0 / total_spp);   // `1.0 / samples * color`
+    resolve_kernel<<<(unsigned)((n_px + 255) / 256), 256, 0, ctx->stream>>>(ctx->total, ctx->rgb8, n_px, inv, hw1 ? 0 : 1);
+    CK(cudaGetLastError());
+    ctx->stats.launches += 1;
+    CK(cudaMemcpyAsync(rgb_out, ctx->rgb8, n_px * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_download_accum(b200rt_ctx *ctx, float *rgb_out) {
+    if (!ctx || !rgb_out) return B200RT_ERR_INVALID;
+    if (!ctx->total) return fail(ctx, B200RT_ERR_NO_SCENE, "no accumulation buffer yet");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(rgb_out, ctx->total, (size_t)ctx->acc_w * ctx->acc_h * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_upload_accum(b200rt_ctx *ctx, const float *rgb_in) {
+    if (!ctx || !rgb_in) return B200RT_ERR_INVALID;
+    if (!ctx->total) return fail(ctx, B200RT_ERR_NO_SCENE, "no accumulation buffer yet");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(ctx->total, rgb_in, (size_t)ctx->acc_w * ctx->acc_h * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_accum_device_ptr(b200rt_ctx *ctx, void **ptr, size_t *n_floats) {
+    if (!ctx || !ptr || !n_floats) return B200RT_ERR_INVALID;
+    if (!ctx->total) return fail(ctx, B200RT_ERR_NO_SCENE, "no accumulation buffer yet");
+    *ptr = ctx->total;
+    *n_floats = (size_t)ctx->acc_w * ctx->acc_h * 3;
+    return B200RT_OK;
+}
+
+int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out) {
+    if (!ctx || !ids_out) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "primary_ids before upload_scene");
+    if (ctx->desc.mode != B200RT_MODE_HW1 && ctx->desc.mode != B200RT_MODE_HW2) return fail(ctx, B200RT_ERR_UNSUPPORTED, "primary ids exist for hw1/hw2 only");
+    if (!ctx->ids || (width > 0 && width != ctx->acc_w) || (height > 0 && height != ctx->acc_h)) return fail(ctx, B200RT_ERR_INVALID, "render the frame first");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(ids_out, ctx->ids, (size_t)ctx->acc_w * ctx->acc_h * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
+int b200rt_get_stats(b200rt_ctx *ctx, b200rt_stats *out) {
+    if (!ctx || !out) return B200RT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->timing_pending) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        DCounters c;
+        CK(cudaMemcpy(&c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost));
+        int launches = ctx->stats.launches;
+        ctx->stats = b200rt_stats{};
+        ctx->stats.launches = launches;
+        ctx->stats.kernel_ms = ms;
+        ctx->stats.paths = c.paths; ctx->stats.rays = c.rays; ctx->stats.light_queries = c.light_queries;
+        ctx->stats.node_tests = c.node_tests; ctx->stats.tri_tests = c.tri_tests;
+        ctx->stats.light_node_tests = c.light_node_tests; ctx->stats.light_tri_tests = c.light_tri_tests;
+        ctx->stats.shaded_hits = c.shaded_hits; ctx->stats.tex_lookups = c.tex_lookups;
+        ctx->timing_pending = false;
+        if (c.stack_overflow) return fail(ctx, B200RT_ERR_STACK, "traversal stack overflow during render");
+    }
+    *out = ctx->stats;
+    return B200RT_OK;
+}
+
+int b200rt_stream(b200rt_ctx *ctx, void **stream_out) {
+    if (!ctx || !stream_out) return B200RT_ERR_INVALID;
+    *stream_out = (void *)ctx->stream;
+    return B200RT_OK;
+}
+
+const char *b200rt_strerror(int code) {
+    switch (code) {
+        case B200RT_OK: return "ok";
+        case B200RT_ERR_INVALID: return "invalid argument";
+        case B200RT_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+        case B200RT_ERR_CUDA: return "CUDA runtime error";
+        case B200RT_ERR_NO_SCENE: return "no scene uploaded / nothing rendered";
+        case B200RT_ERR_UNSUPPORTED: return "not implemented on the device path";
+        case B200RT_ERR_STACK: return "BVH deeper than the traversal stack";
+        default: return "unknown error";
+    }
+}
+
+const char *b200rt_last_error(b200rt_ctx *ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+}  // extern "C"

@@ -1,0 +1,101 @@
+// Device-side scene layout and launch parameters.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "b200rt.h"
+
+namespace b200rt {
+
+// 32-byte BVH node, fetched as two float4.  Siblings are stored ADJACENT (left = 2p, right = 2p+1,
+// 64-byte aligned), so one traversal step reads both child boxes with four float4 __ldg.
+//   internal: a = index of the left child (even), b = 0
+//   leaf    : a = first triangle,               b = triangle count (> 0)
+struct DNode {
+    float mnx, mny, mnz; uint32_t a;
+    float mxx, mxy, mxz; uint32_t b;
+};
+static_assert(sizeof(DNode) == 32, "DNode must be 32 bytes");
+
+// 48-byte Moeller-Trumbore record: v0 = data3 (barycentric origin), e1 = data - data3 (weight u),
+// e2 = data2 - data3 (weight v)  (hw8/src/primitives.cpp:86-88).
+//   scene triangles: v0.w = material id (int bits), e1.w = tangent w of `data` (Q14), e2.w = 0
+//   light triangles: v0.w = pointProb = 1 / (0.5 |e1 x e2|) (distributions.h:76)
+struct DTri {
+    float4 v0, e1, e2;
+};
+static_assert(sizeof(DTri) == 48, "DTri must be 48 bytes");
+
+// 96-byte shading record of a triangle, six float4:
+//   q[0] = n(data).xyz,  uv(data).x     q[3] = tan(data).xyz,  uv(data2).y
+//   q[1] = n(data2).xyz, uv(data).y     q[4] = tan(data2).xyz, uv(data3).x
+//   q[2] = n(data3).xyz, uv(data2).x    q[5] = tan(data3).xyz, uv(data3).y
+struct DShade {
+    float4 q[6];
+};
+static_assert(sizeof(DShade) == 96, "DShade must be 96 bytes");
+
+// Light triangles carry their three vertex normals for the hw8 pdf (distributions.h:140-145).
+struct DLightNormals {
+    float4 n0, n1, n2;  // data, data2, data3
+};
+
+struct DMaterial {
+    float base_color[3];
+    float emission[3];
+    float metallic_factor;
+    float roughness_factor;
+    cudaTextureObject_t tex_base, tex_emissive, tex_mr, tex_normal;  // 0 = absent
+    int32_t w_base, h_base, w_emissive, h_emissive, w_mr, h_mr, w_normal, h_normal;
+};
+
+struct DCamera {
+    float pos[3], right[3], up[3], forward[3];
+    float tan_x, tan_y;   // computed on the host with the reference's own libm call
+    int32_t width, height;
+};
+
+struct DGltfScene {
+    const DNode *nodes;
+    const DTri *tris;
+    const DShade *shade;
+    const DNode *light_nodes;
+    const DTri *light_tris;
+    const DLightNormals *light_normals;
+    const DMaterial *materials;
+    int32_t n_light_tris;
+    int32_t root_is_leaf, light_root_is_leaf;
+    int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
+    float bg[3];
+    cudaTextureObject_t env;     // 0 = absent
+    int32_t env_w, env_h;
+};
+
+struct DCounters {
+    unsigned long long paths, rays, light_queries, node_tests, tri_tests, light_node_tests, light_tri_tests,
+        shaded_hits, tex_lookups, stack_overflow;
+};
+
+struct DRenderParams {
+    DCamera cam;
+    int32_t spp_begin, spp_end;   // global sample indices rendered by this launch
+    int32_t n_chunks;             // the sample range is cut into n_chunks slabs of accum
+    int32_t ray_depth;
+    uint32_t seed;
+    float *accum;                 // [n_chunks][H*W*3] partial sums (slab 0 is the running total)
+    DCounters *counters;
+};
+
+// analytic scenes (hw1, hw2, hw4): primitives + lights live in __constant__ memory
+#define B200RT_MAX_PRIMS 64
+#define B200RT_MAX_LIGHTS 16
+struct DAnalyticScene {
+    b200rt_primitive prims[B200RT_MAX_PRIMS];
+    b200rt_light lights[B200RT_MAX_LIGHTS];
+    int32_t n_prims, n_lights;
+    int32_t light_prims[B200RT_MAX_PRIMS];  // hw4: indices of emissive BOX/ELLIPSOID figures
+    int32_t n_light_prims;
+    float bg[3], ambient[3];
+    int32_t mode;
+};
+
+}  // namespace b200rt

@@ -1,0 +1,468 @@
+// K4: glTF path-tracing megakernel (hw7 / hw8 semantics) for sm_100a.
+// Replaces Scene::getPixel / getColor / intersect and everything below them:
+//   hw8/src/scene.cpp:84-187, hw8/src/include/bvh.h:111-142, hw8/src/primitives.cpp:18-125,
+//   hw8/src/include/distributions.h:35-280, hw8/src/include/material.h:11-65
+//   (hw7 deltas: hw7/src/scene.cpp:29-61, hw7/src/include/material.h:44-59, distributions.h:140-145).
+// Not a port: iterative path loop instead of recursion, while-while stack traversal over 32-byte
+// sibling-pair nodes with near-child-first ordering and distance pruning, Moeller-Trumbore
+// triangle records, Philox counter RNG, texels through point-sampled texture objects with a
+// shared-memory sRGB decode table.
+#pragma once
+#include "device_scene.h"
+#include "rt_math.cuh"
+
+namespace b200rt {
+
+#define B200RT_STACK 64
+#define B200RT_TMAX 1e4f
+#define B200RT_EPS 1e-4f
+#define B200RT_LEAF 0x80000000u
+
+struct TraceHit {
+    float t, u, v;
+    int tri;
+    float det;
+};
+
+struct ThreadCounters {
+    unsigned paths, rays, light_queries, node_tests, tri_tests, light_node_tests, light_tri_tests, shaded, tex, overflow;
+};
+
+__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const V3 o, const V3 inv, float tbest, float &tnear) {
+    float x0 = (lo.x - o.x) * inv.x, x1 = (hi.x - o.x) * inv.x;
+    float y0 = (lo.y - o.y) * inv.y, y1 = (hi.y - o.y) * inv.y;
+    float z0 = (lo.z - o.z) * inv.z, z1 = (hi.z - o.z) * inv.z;
+    float tmin = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+    float tmax = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    tnear = tmin;
+    // AABB::intersect accepts t1 <= t2 && t2 >= 0 (hw8/src/primitives.cpp:38); tbest adds the
+    // distance prune of BVH::intersect_ (bvh.h:118) -- conservative (<=) so ties still descend.
+    return tmin <= tmax && tmax >= 0.f && tmin <= tbest;
+}
+
+// Closest hit over the scene BVH.  t in (0, 1e4) like intersectPlaneAndRay (primitives.cpp:20).
+template <bool COUNT>
+__device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, const V3 d, TraceHit &h, ThreadCounters &tc) {
+    h.t = B200RT_TMAX; h.tri = -1; h.u = h.v = 0.f; h.det = 0.f;
+    const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    uint32_t stack[B200RT_STACK];
+    int sp = 0;
+    uint32_t cur = __ldg(&sc.nodes[0].a);   // root meta: its box is not tested (always the scene)
+    while (true) {
+        if (!(cur & B200RT_LEAF)) {
+            const float4 *p = reinterpret_cast<const float4 *>(sc.nodes + cur);
+            const float4 l0 = __ldg(p), l1 = __ldg(p + 1), r0 = __ldg(p + 2), r1 = __ldg(p + 3);
+            float tl, tr;
+            const bool hl = slab(l0, l1, o, inv, h.t, tl);
+            const bool hr = slab(r0, r1, o, inv, h.t, tr);
+            if (COUNT) tc.node_tests += 2;
+            const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
+            if (hl && hr) {
+                const bool left_first = tl <= tr;
+                if (sp < B200RT_STACK) stack[sp++] = left_first ? mr : ml; else tc.overflow = 1;
+                cur = left_first ? ml : mr;
+                continue;
+            }
+            if (hl) { cur = ml; continue; }
+            if (hr) { cur = mr; continue; }
+        } else {
+            const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
+            for (uint32_t i = first; i < first + count; i++) {
+                const float4 *q = reinterpret_cast<const float4 *>(sc.tris + i);
+                const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+                if (COUNT) tc.tri_tests++;
+                const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+                const V3 pv = cross(d, E2);
+                const float det = dot(E1, pv);
+                const float idet = 1.f / det;
+                const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
+                const float u = dot(tv, pv) * idet;
+                const V3 qv = cross(tv, E1);
+                const float v = dot(d, qv) * idet;
+                const float t = dot(E2, qv) * idet;
+                if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < h.t) { h.t = t; h.u = u; h.v = v; h.tri = (int)i; h.det = det; }
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+}
+
+// FiguresMix::getTotalPdf (distributions.h:122-165): every emissive triangle whose box the ray
+// (x, d) pierces contributes pointProb * |x-y|^2 / |d . n_y|; NO distance pruning.
+template <bool COUNT>
+__device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o, const V3 d, ThreadCounters &tc) {
+    const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    uint32_t stack[B200RT_STACK];
+    int sp = 0;
+    float total = 0.f;
+    {   // unlike the scene root, the light root's box IS a real filter
+        const float4 *p = reinterpret_cast<const float4 *>(sc.light_nodes);
+        float tn;
+        if (COUNT) tc.light_node_tests++;
+        if (!slab(__ldg(p), __ldg(p + 1), o, inv, INFINITY, tn)) return 0.f;
+    }
+    uint32_t cur = __ldg(&sc.light_nodes[0].a);
+    while (true) {
+        if (!(cur & B200RT_LEAF)) {
+            const float4 *p = reinterpret_cast<const float4 *>(sc.light_nodes + cur);
+            const float4 l0 = __ldg(p), l1 = __ldg(p + 1), r0 = __ldg(p + 2), r1 = __ldg(p + 3);
+            float tl, tr;
+            const bool hl = slab(l0, l1, o, inv, INFINITY, tl);
+            const bool hr = slab(r0, r1, o, inv, INFINITY, tr);
+            if (COUNT) tc.light_node_tests += 2;
+            const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
+            if (hl && hr) {
+                if (sp < B200RT_STACK) stack[sp++] = mr; else tc.overflow = 1;
+                cur = ml;
+                continue;
+            }
+            if (hl) { cur = ml; continue; }
+            if (hr) { cur = mr; continue; }
+        } else {
+            const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
+            for (uint32_t i = first; i < first + count; i++) {
+                const float4 *q = reinterpret_cast<const float4 *>(sc.light_tris + i);
+                const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+                if (COUNT) tc.light_tri_tests++;
+                const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+                const V3 pv = cross(d, E2);
+                const float det = dot(E1, pv);
+                const float idet = 1.f / det;
+                const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
+                const float u = dot(tv, pv) * idet;
+                const V3 qv = cross(tv, E1);
+                const float v = dot(d, qv) * idet;
+                const float t = dot(E2, qv) * idet;
+                if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < B200RT_TMAX) {
+                    V3 yn;
+                    if (sc.hw8) {   // interpolated shading normal of the emitter (hw8 distributions.h:140-145)
+                        const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);
+                        const float4 n0 = __ldg(nq), n1 = __ldg(nq + 1), n2 = __ldg(nq + 2);
+                        yn = normalize(mk(n2.x + u * (n0.x - n2.x) + v * (n1.x - n2.x),
+                                          n2.y + u * (n0.y - n2.y) + v * (n1.y - n2.y),
+                                          n2.z + u * (n0.z - n2.z) + v * (n1.z - n2.z)));
+                    } else {        // geometric normal (hw7 distributions.h:145)
+                        yn = normalize(cross(E2, E1));
+                    }
+                    // |x - y|^2 with y = x + t d
+                    const V3 td = t * d;
+                    total += v0.w * len2(td) / fabsf(dot(d, yn));
+                }
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    return total;
+}
+
+// ---- textures (hw8/src/scene.cpp:9-35): wrap, bilinear on the integer texel grid, sRGB decode
+// per texel BEFORE blending.  Texels are RGBA8 in a point-sampled texture object; decode goes
+// through a 256-entry table (host-computed with the reference's powf) in shared memory.
+__device__ __forceinline__ V3 texel(cudaTextureObject_t tex, int ix, int iy, const float *lut) {
+    const uchar4 c = tex2D<uchar4>(tex, (float)ix + 0.5f, (float)iy + 0.5f);
+    return mk(lut[c.x], lut[c.y], lut[c.z]);
+}
+__device__ __forceinline__ V3 sample_texture(cudaTextureObject_t tex, int w, int h, float tx, float ty, const float *lut) {
+    tx -= floorf(tx);
+    ty -= floorf(ty);
+    tx *= (float)w;
+    ty *= (float)h;
+    int ix1 = (int)floorf(tx), iy1 = (int)floorf(ty);
+    const int ix2 = (ix1 + 1) % w, iy2 = (iy1 + 1) % h;
+    ix1 = min(ix1, w - 1); iy1 = min(iy1, h - 1);
+    const float dx = tx - (float)ix1, dy = ty - (float)iy1;
+    const V3 p11 = texel(tex, ix1, iy1, lut), p12 = texel(tex, ix1, iy2, lut);
+    const V3 p21 = texel(tex, ix2, iy1, lut), p22 = texel(tex, ix2, iy2, lut);
+    return (1.f - dx) * ((1.f - dy) * p11 + dy * p12) + dx * ((1.f - dy) * p21 + dy * p22);
+}
+
+// ---- BRDF (hw8/src/include/material.h:11-65) ----
+__device__ __forceinline__ float ggx_d(float hn, float a2) {
+    if (hn <= 0.f) return 0.f;
+    const float k = fmaxf(0.f, (a2 - 1.f) * hn * hn + 1.f);
+    return a2 / (3.14159265358979f * k * k);
+}
+__device__ __forceinline__ float smith_v1(float nx, float a2) {
+    return 1.f / (fabsf(nx) + sqrtf(fmaxf(0.f, a2 + (1.f - a2) * nx * nx)));
+}
+__device__ __forceinline__ float pow5(float x) { const float x2 = x * x; return x2 * x2 * x; }
+
+template <bool HW8>
+__device__ __forceinline__ V3 eval_brdf(const V3 base, float metallic_factor, const V3 l, const V3 v, const V3 n,
+                                        const V3 color, float metallic, float alpha) {
+    const V3 h = normalize(l + v);
+    const float a2 = alpha * alpha;
+    float specular = 0.f;
+    if (!(dot(h, l) < 1e-4f || dot(h, v) < 1e-4f)) specular = ggx_d(dot(h, n), a2) * smith_v1(dot(n, l), a2) * smith_v1(dot(n, v), a2);
+    const float fw = pow5(fmaxf(0.f, 1.f - fabsf(dot(v, h))));
+    V3 metal = mk(0, 0, 0), diel = mk(0, 0, 0);
+    const V3 albedo = HW8 ? base * color : base;
+    metallic = HW8 ? metallic * metallic_factor : metallic_factor;
+    const float ln = dot(l, n), vn = dot(v, n);
+    if (metallic > 0.f && (!HW8 || (vn >= 0.f && ln >= 0.f))) {
+        const V3 ft = albedo + fw * (mk(1, 1, 1) - albedo);
+        metal = specular * ft;
+    }
+    if (metallic < 1.f) {
+        V3 diffuse = mk(0, 0, 0);
+        if (!HW8 || ln >= 0.f) diffuse = 0.318309886183791f * albedo;
+        const float f = 0.04f + fw * 0.96f;
+        diel = (1.f - f) * diffuse + mk(specular * f, specular * f, specular * f);
+    }
+    return (1.f - metallic) * diel + metallic * metal;
+}
+
+// ---- VNDF (Heitz 2018) in the frame that maps the shading normal to +z
+// (hw8/src/include/distributions.h:168-246).  The reference builds the frame with a quaternion
+// (getQ); any rotation taking n to +z gives the same distribution, but the port comparison wants
+// the same frame, so the same half-angle quaternion is used here.
+struct Frame {
+    float qx, qy, qz, qw;   // Hamilton quaternion q such that rotate(q, n) = +z
+};
+__device__ __forceinline__ Frame frame_of(const V3 n) {
+    Frame f;
+    if (n.z > 0.9999f) { f.qx = f.qy = f.qz = 0.f; f.qw = 1.f; return f; }
+    if (n.z < -0.9999f) { f.qx = f.qy = f.qz = 0.f; f.qw = -1.f; return f; }
+    // reference: a = n.cross(newN) (= newN x n in standard terms), w = |n| + n.z, normalised;
+    // its transform() is the inverse rotation of the Hamilton convention => conjugate axis.
+    const V3 a = cross(mk(0, 0, 1), n);
+    const float w = sqrtf(len2(n)) + n.z;
+    const float il = rsqrtf(len2(a) + w * w);
+    f.qx = -a.x * il; f.qy = -a.y * il; f.qz = -a.z * il; f.qw = w * il;
+    return f;
+}
+__device__ __forceinline__ V3 rotate(float qx, float qy, float qz, float qw, const V3 p) {
+    // p' = p + 2 w (q x p) + 2 q x (q x p)
+    const V3 q = mk(qx, qy, qz);
+    const V3 t = 2.f * cross(q, p);
+    return p + qw * t + cross(q, t);
+}
+__device__ __forceinline__ V3 to_local(const Frame &f, const V3 p) { return rotate(f.qx, f.qy, f.qz, f.qw, p); }
+__device__ __forceinline__ V3 to_world(const Frame &f, const V3 p) { return rotate(-f.qx, -f.qy, -f.qz, f.qw, p); }
+
+__device__ __forceinline__ V3 vndf_sample_local(const V3 v, float a, float u1, float u2) {
+    const V3 vh = normalize(mk(a * v.x, a * v.y, v.z));
+    const float lensq = vh.x * vh.x + vh.y * vh.y;
+    const V3 T1 = lensq > 0.f ? rsqrtf(lensq) * mk(-vh.y, vh.x, 0.f) : mk(1, 0, 0);
+    const V3 T2 = cross(vh, T1);   // reference: T1.cross(vh) with the negated cross
+    const float r = sqrtf(u1);
+    float sn, cs;
+    sincosf(6.283185307179586f * u2, &sn, &cs);
+    const float t1 = r * cs;
+    float t2 = r * sn;
+    const float s = 0.5f * (1.f + vh.z);
+    t2 = (1.f - s) * sqrtf(1.f - t1 * t1) + s * t2;
+    const V3 nh = t1 * T1 + t2 * T2 + sqrtf(fmaxf(0.f, 1.f - t1 * t1 - t2 * t2)) * vh;
+    const V3 ne = normalize(mk(a * nh.x, a * nh.y, fmaxf(0.f, nh.z)));
+    return 2.f * dot(ne, v) * ne - v;
+}
+__device__ __forceinline__ float vndf_pdf_local(const V3 d, const V3 v, float a) {
+    const V3 ni = normalize(v + d);
+    const float a2 = a * a;
+    const float k = ni.x * ni.x / a2 + ni.y * ni.y / a2 + ni.z * ni.z;
+    const float D = 1.f / (3.14159265358979f * a2 * k * k);
+    const float lambda = 0.5f * (-1.f + sqrtf(1.f + (a2 * v.x * v.x + a2 * v.y * v.y) / (v.z * v.z)));
+    const float G1 = 1.f / (1.f + lambda);
+    const float vni = dot(v, ni);
+    const float dv = G1 * fmaxf(0.f, vni) * D / fabsf(v.z);
+    return dv / (4.f * vni);
+}
+
+}  // namespace b200rt
+
+namespace b200rt {
+
+// One bounce of Scene::getColor (hw8/src/scene.cpp:84-165).  Returns false when the path ends.
+// L accumulates throughput-weighted emission; T is the path throughput (product of `mult`).
+template <bool HW8, bool COUNT>
+__device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *lut_srgb, const float *lut_lin,
+                                             const TraceHit &hit, V3 &o, V3 &d, V3 &L, V3 &T,
+                                             const uint4 rnd, ThreadCounters &tc) {
+    const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + hit.tri);
+    const float4 tv0 = __ldg(tq), te1 = __ldg(tq + 1), te2 = __ldg(tq + 2);
+    const bool inside = hit.det > 0.f;   // ray.d . n > 0 with n = b.cross(c) (primitives.cpp:21)
+    const float u = hit.u, v = hit.v;
+    if (COUNT) tc.shaded++;
+
+    const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + hit.tri);
+    const float4 s0 = __ldg(sq), s1 = __ldg(sq + 1), s2 = __ldg(sq + 2);
+    V3 ns = normalize(mk(s2.x + u * (s0.x - s2.x) + v * (s1.x - s2.x),
+                         s2.y + u * (s0.y - s2.y) + v * (s1.y - s2.y),
+                         s2.z + u * (s0.z - s2.z) + v * (s1.z - s2.z)));
+    if (inside) ns = -ns;
+    V3 ng = normalize(cross(mk(te2.x, te2.y, te2.z), mk(te1.x, te1.y, te1.z)));
+    if (inside) ng = -ng;
+
+    const DMaterial *m = sc.materials + __float_as_int(tv0.w);
+    V3 emission = mk(__ldg(&m->emission[0]), __ldg(&m->emission[1]), __ldg(&m->emission[2]));
+    const V3 base = mk(__ldg(&m->base_color[0]), __ldg(&m->base_color[1]), __ldg(&m->base_color[2]));
+    const float metallic_factor = __ldg(&m->metallic_factor);
+    const float roughness_factor = __ldg(&m->roughness_factor);
+    V3 color = mk(1, 1, 1);
+    float alpha, metallic = 1.f;
+    if (HW8) {
+        const float4 s3 = __ldg(sq + 3), s4 = __ldg(sq + 4), s5 = __ldg(sq + 5);
+        // uv: data = (s0.w, s1.w), data2 = (s2.w, s3.w), data3 = (s4.w, s5.w)
+        const float tx = s4.w + u * (s0.w - s4.w) + v * (s2.w - s4.w);
+        const float ty = s5.w + u * (s1.w - s5.w) + v * (s3.w - s5.w);
+        const cudaTextureObject_t tb = m->tex_base, te = m->tex_emissive, tm = m->tex_mr, tn = m->tex_normal;
+        if (tb) { color = sample_texture(tb, m->w_base, m->h_base, tx, ty, lut_srgb); if (COUNT) tc.tex++; }
+        if (te) { emission = emission * sample_texture(te, m->w_emissive, m->h_emissive, tx, ty, lut_srgb); if (COUNT) tc.tex++; }
+        V3 mr = mk(1, 1, 1);
+        if (tm) { mr = sample_texture(tm, m->w_mr, m->h_mr, tx, ty, lut_lin); if (COUNT) tc.tex++; }
+        if (tn) {
+            // applyNormalMaps (scene.cpp:37-52): X = tangent, Z = shading normal, Y = w * X.cross(Z) = w * (Z x X)
+            const V3 smp = sample_texture(tn, m->w_normal, m->h_normal, tx, ty, lut_lin);
+            if (COUNT) tc.tex++;
+            const V3 X = normalize(mk(s5.x + u * (s3.x - s5.x) + v * (s4.x - s5.x),
+                                      s5.y + u * (s3.y - s5.y) + v * (s4.y - s5.y),
+                                      s5.z + u * (s3.z - s5.z) + v * (s4.z - s5.z)));
+            const V3 Y = te1.w * cross(ns, X);
+            const V3 ln = mk(2.f * smp.x - 1.f, 2.f * smp.y - 1.f, 2.f * smp.z - 1.f);
+            ns = normalize(ln.x * X + ln.y * Y + ln.z * ns);
+        }
+        const float rgh = fmaxf(0.08f, roughness_factor * mr.y);
+        alpha = rgh * rgh;
+        metallic = mr.z;
+    } else {
+        alpha = roughness_factor * roughness_factor;
+    }
+
+    const V3 x = o + hit.t * d;
+    const V3 xo = x + B200RT_EPS * ng;     // origin offset along the GEOMETRIC normal (scene.cpp:151-152)
+    const V3 vdir = -d;                    // towards the viewer
+
+    // Mix::sample (distributions.h:256-265): uniform choice among {Cosine, Vndf, [lights]}
+    const int k = sc.n_light_tris > 0 ? 3 : 2;
+    const int which = (int)(u01(rnd.x) * (float)k);
+    const float r1 = u01(rnd.y), r2 = u01(rnd.z), r3 = u01(rnd.w);
+    const Frame fr = frame_of(ns);
+    const V3 vloc = to_local(fr, vdir);
+    V3 nd;
+    if (which == 0) {
+        V3 c = sphere_dir(r1, r2) + ns;
+        const float l = sqrtf(len2(c));
+        nd = (l <= 1e-9f || dot(c, ns) <= 1e-9f || isnan(l)) ? ns : (1.f / l) * c;
+    } else if (which == 2) {
+        // FiguresMix::sample (:117-120) + TriangleLight::sample (:81-94): draws = index, u, v
+        const int li = min((int)(r1 * (float)sc.n_light_tris), sc.n_light_tris - 1);
+        const float4 *lq = reinterpret_cast<const float4 *>(sc.light_tris + li);
+        const float4 a = __ldg(lq), b = __ldg(lq + 1), c = __ldg(lq + 2);
+        float lu = r2, lv = r3;
+        if (lu + lv > 1.f) { lu = 1.f - lu; lv = 1.f - lv; }
+        const V3 point = mk(a.x + lu * b.x + lv * c.x, a.y + lu * b.y + lv * c.y, a.z + lu * b.z + lv * c.z);
+        nd = normalize(point - xo);
+    } else {
+        nd = to_world(fr, vndf_sample_local(vloc, alpha, r1, r2));
+    }
+
+    L = L + T * emission;
+    const V3 brdf = eval_brdf<HW8>(base, metallic_factor, nd, vdir, ns, color, metallic, alpha);
+    if (brdf.x < B200RT_EPS && brdf.y < B200RT_EPS && brdf.z < B200RT_EPS) return false;
+
+    // Mix::pdf (:267-279) = mean of all component pdfs
+    float pdf = fmaxf(0.f, dot(nd, ns) * 0.318309886183791f);
+    pdf += vndf_pdf_local(to_local(fr, nd), vloc, alpha);
+    if (k == 3) {
+        tc.light_queries++;
+        pdf += light_pdf_sum<COUNT>(sc, xo, nd, tc) / (float)sc.n_light_tris;
+    }
+    pdf /= (float)k;
+    const float w = (1.f / pdf) * fabsf(dot(nd, ns));
+    const V3 mult = w * brdf;
+    // firefly clamp (scene.cpp:161): any channel > 6 or NaN ends the path
+    if (!(mult.x <= 6.f) || !(mult.y <= 6.f) || !(mult.z <= 6.f)) return false;
+    T = T * mult;
+    o = xo;
+    d = nd;
+    return true;
+}
+
+__device__ __forceinline__ void flush_counters(DCounters *g, const ThreadCounters &tc) {
+    unsigned vals[10] = {tc.paths, tc.rays, tc.light_queries, tc.node_tests, tc.tri_tests,
+                         tc.light_node_tests, tc.light_tri_tests, tc.shaded, tc.tex, tc.overflow};
+    unsigned long long *dst = reinterpret_cast<unsigned long long *>(g);
+#pragma unroll
+    for (int i = 0; i < 10; i++) {
+        unsigned v = vals[i];
+        // 32-bit per-thread counts: at most ~1e5 per thread, the warp sum fits in 32 bits
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst + i, (unsigned long long)v);
+    }
+}
+
+// Work decomposition: the image is cut into 8x4-pixel tiles, one warp per (tile, sample chunk),
+// so the 32 primary rays of a warp are coherent.  A thread renders samples [s0, s1) of its pixel
+// into slab `chunk` of the accumulation buffer; fold_slabs() adds the slabs in a fixed order
+// (deterministic, no float atomics).
+template <bool HW8, bool COUNT>
+__global__ void __launch_bounds__(128) gltf_path_kernel(const DGltfScene sc, const DRenderParams rp,
+                                                        const float *__restrict__ lut_srgb_g) {
+    __shared__ float lut_srgb[256];
+    __shared__ float lut_lin[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        lut_srgb[i] = lut_srgb_g[i];
+        lut_lin[i] = 0.00392156862745098f * (float)i;   // (1./255) * c as float (scene.cpp:11)
+    }
+    __syncthreads();
+
+    const int W = rp.cam.width, H = rp.cam.height;
+    const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
+    const long long n_tiles = (long long)tiles_x * tiles_y;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    ThreadCounters tc = {};
+    if (warp_id < n_tiles * rp.n_chunks) {
+        const int chunk = (int)(warp_id / n_tiles);
+        const long long tile = warp_id % n_tiles;
+        const int px = (int)(tile % tiles_x) * 8 + (lane & 7);
+        const int py = (int)(tile / tiles_x) * 4 + (lane >> 3);
+        if (px < W && py < H) {
+            const int total = rp.spp_end - rp.spp_begin;
+            const int per = (total + rp.n_chunks - 1) / rp.n_chunks;
+            const int s0 = rp.spp_begin + chunk * per;
+            const int s1 = min(rp.spp_end, s0 + per);
+            const uint32_t pixel = (uint32_t)(py * W + px);
+            const V3 cpos = ld3(rp.cam.pos), cright = ld3(rp.cam.right), cup = ld3(rp.cam.up), cfwd = ld3(rp.cam.forward);
+            V3 sum = mk(0, 0, 0);
+            for (int s = s0; s < s1; s++) {
+                // camera sample (scene.cpp:172-173, 179-187): jitter in [0,1)^2, fovY-based, normalised
+                const uint4 j = philox4x32_10((uint32_t)s, 0u, pixel, rp.seed);
+                const float fx = (float)px + u01(j.x), fy = (float)py + u01(j.y);
+                const float nx = rp.cam.tan_x * (2.f * fx / (float)W - 1.f);
+                const float ny = rp.cam.tan_y * (2.f * fy / (float)H - 1.f);
+                V3 o = cpos;
+                V3 d = normalize(nx * cright - ny * cup + cfwd);
+                V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
+                tc.paths++;
+                for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
+                    TraceHit hit;
+                    tc.rays++;
+                    trace_closest<COUNT>(sc, o, d, hit, tc);
+                    if (hit.tri < 0) {
+                        V3 bg = ld3(sc.bg);
+                        if (HW8 && sc.env) {
+                            // equirect lookup (scene.cpp:94-96), decoded as sRGB
+                            const float tx = 0.5f + 0.5f * atan2f(d.z, d.x) * 0.318309886183791f;
+                            const float ty = 0.5f - asinf(d.y) * 0.318309886183791f;
+                            bg = sample_texture(sc.env, sc.env_w, sc.env_h, tx, ty, lut_srgb);
+                        }
+                        L = L + T * bg;
+                        break;
+                    }
+                    const uint4 rnd = philox4x32_10((uint32_t)s, 16u * (uint32_t)(bounce + 1), pixel, rp.seed);
+                    if (!shade_bounce<HW8, COUNT>(sc, lut_srgb, lut_lin, hit, o, d, L, T, rnd, tc)) break;
+                }
+                sum = sum + L;
+            }
+            float *dst = rp.accum + ((size_t)chunk * W * H + pixel) * 3;
+            dst[0] = sum.x; dst[1] = sum.y; dst[2] = sum.z;
+        }
+    }
+    flush_counters(rp.counters, tc);
+}
+
+}  // namespace b200rt

@@ -1,0 +1,55 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/* by running the UNMODIFIED reference binaries (oracle/_ref/hwN, built by
+oracle/build_ref.sh from /root/reference).  Run in the build container only; the fixtures are
+committed because neither /root/reference nor (necessarily) oracle/_ref exist on the GPU box.
+
+Fixtures:
+  hw1_sample.ppm.gz, hw2_sample.ppm.gz            deterministic configs, full size
+  hw4_p3_{k}.txt + hw4_p3_{k}_spp4.ppm.gz         hw4 scenes shrunk to 160x120, SAMPLES 4 (minstd stream)
+  hw4_p3_{k}_spp4096.ppm.gz                       ground truth for the RMSE tests (160x120, SAMPLES 4096)
+  hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
+  hw8_sphere_emissive_128x96_spp4.ppm.gz / _spp4096
+"""
+import gzip, os, re, subprocess, sys, tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+GOLD = os.path.join(ROOT, "tests", "golden")
+SC = os.path.join(ROOT, "tests", "scenes")
+
+
+def run(binary, args, out_name):
+    dst = os.path.join(GOLD, out_name + ".ppm.gz")
+    if os.path.exists(dst) and "--force" not in sys.argv:
+        return
+    with tempfile.TemporaryDirectory() as td:
+        tmp = os.path.join(td, "o.ppm")
+        cmd = ["bash", "-c", 'ulimit -s unlimited; exec "$0" "$@"', os.path.join(REF, binary)] + [a if a != "@OUT" else tmp for a in args]
+        subprocess.run(cmd, check=True, stderr=subprocess.DEVNULL)
+        with open(tmp, "rb") as f, gzip.GzipFile(dst, "wb", mtime=0) as g:
+            g.write(f.read())
+    print("wrote", dst, flush=True)
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    run("hw1", [os.path.join(SC, "hw1/sample.txt"), "@OUT"], "hw1_sample")
+    run("hw2", [os.path.join(SC, "hw2/sample.txt"), "@OUT"], "hw2_sample")
+    for k in (1, 3, 4):
+        src = open(os.path.join(SC, f"hw4/practice3_{k}.txt")).read()
+        src = re.sub(r"DIMENSIONS \d+ \d+", "DIMENSIONS 160 120", src)
+        for spp in (4, 4096):
+            txt = os.path.join(GOLD, f"hw4_p3_{k}_spp{spp}.txt")
+            open(txt, "w").write(re.sub(r"SAMPLES \d+", f"SAMPLES {spp}", src))
+        run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4.txt"), "@OUT"], f"hw4_p3_{k}_spp4")
+    for name, path, binary in (("hw7_practice7_1", "hw7/practice7_1.gltf", "hw7"),
+                               ("hw7_practice7_4", "hw7/practice7_4.gltf", "hw7"),
+                               ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf", "hw8")):
+        for spp in (4, 4096):
+            run(binary, [os.path.join(SC, path), "128", "96", str(spp), "@OUT"], f"{name}_128x96_spp{spp}")
+    for k in (1, 3, 4):  # slow (single-threaded reference): last
+        run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw4_p3_{k}_spp4096")
+
+
+if __name__ == "__main__":
+    main()
