@@ -1,0 +1,277 @@
+"""raytracing_course_hw_b200 -- Python harness over the two C-ABI libraries.
+
+The product is C++/CUDA (csrc/); this module only binds it with ctypes so that tests, bench.py
+and scripts can drive the same entry points the CLI uses.  Names mirror the reference's
+`sceneio` namespace: load_scene(...) / render_scene(...)  (hw8/src/include/sceneio.h:7-11).
+
+There is NO CPU fallback: if libb200rt.so is missing, or no CUDA device is visible, Renderer()
+raises.  Nothing here imports or touches oracle/.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_DIR = os.path.join(_PKG, "lib")
+
+MODE_HW1, MODE_HW2, MODE_HW3, MODE_HW4, MODE_HW5, MODE_HW6, MODE_HW7, MODE_HW8 = range(1, 9)
+FLAG_COUNTERS = 1
+
+
+class B200rtError(RuntimeError):
+    def __init__(self, code, what):
+        super().__init__(f"b200rt error {code}: {what}")
+        self.code = code
+
+
+class Options(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int32), ("seed", ctypes.c_uint32), ("flags", ctypes.c_int32)]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("kernel_ms", ctypes.c_double), ("paths", ctypes.c_uint64), ("rays", ctypes.c_uint64),
+                ("light_queries", ctypes.c_uint64), ("node_tests", ctypes.c_uint64), ("tri_tests", ctypes.c_uint64),
+                ("light_node_tests", ctypes.c_uint64), ("light_tri_tests", ctypes.c_uint64),
+                ("shaded_hits", ctypes.c_uint64), ("tex_lookups", ctypes.c_uint64), ("launches", ctypes.c_int32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class SceneHeader(ctypes.Structure):
+    """Leading scalar fields of b200rt_scene_desc (include/b200rt.h); pointers are not bound here."""
+    _fields_ = [("mode", ctypes.c_int32), ("width", ctypes.c_int32), ("height", ctypes.c_int32),
+                ("samples", ctypes.c_int32), ("ray_depth", ctypes.c_int32)]
+
+
+_host = None
+_dev = None
+
+
+def host_lib():
+    global _host
+    if _host is None:
+        path = os.path.join(LIB_DIR, "libb200rt_host.so")
+        if not os.path.exists(path):
+            raise ImportError(f"{path} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = ctypes.CDLL(path)
+        L.b200rt_host_desc.restype = ctypes.c_void_p
+        L.b200rt_host_desc.argtypes = [ctypes.c_void_p]
+        L.b200rt_host_strerror.restype = ctypes.c_char_p
+        L.b200rt_host_free.argtypes = [ctypes.c_void_p]
+        L.b200rt_host_free.restype = None
+        L.b200rt_host_set_frame.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]
+        L.b200rt_host_set_env_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.b200rt_host_timings.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+        L.b200rt_host_write_ppm.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        _host = L
+    return _host
+
+
+def device_lib():
+    """The CUDA library.  Fails loudly when it was not built (no fallback of any kind)."""
+    global _dev
+    if _dev is None:
+        path = os.path.join(LIB_DIR, "libb200rt.so")
+        if not os.path.exists(path):
+            raise ImportError(f"{path} missing: the CUDA extension is required (no CPU fallback); "
+                              "run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = ctypes.CDLL(path)
+        L.b200rt_strerror.restype = ctypes.c_char_p
+        L.b200rt_last_error.restype = ctypes.c_char_p
+        L.b200rt_last_error.argtypes = [ctypes.c_void_p]
+        L.b200rt_destroy.argtypes = [ctypes.c_void_p]
+        L.b200rt_destroy.restype = None
+        L.b200rt_upload_scene.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_render.argtypes = [ctypes.c_void_p] + [ctypes.c_int32] * 5
+        L.b200rt_clear.argtypes = [ctypes.c_void_p]
+        L.b200rt_resolve.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_download_accum.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_upload_accum.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_accum_device_ptr.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
+        L.b200rt_primary_ids.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
+        L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
+        L.b200rt_stream.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        _dev = L
+    return _dev
+
+
+DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b200rt_render", "b200rt_clear",
+                  "b200rt_resolve", "b200rt_download_accum", "b200rt_upload_accum", "b200rt_accum_device_ptr",
+                  "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
+                  "b200rt_strerror", "b200rt_last_error", "b200rt_device_count"]
+HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_set_env_map", "b200rt_host_desc",
+                "b200rt_host_set_frame", "b200rt_host_free", "b200rt_host_write_ppm", "b200rt_host_timings",
+                "b200rt_host_strerror"]
+
+
+class Scene:
+    """A loaded scene (host arrays + reference-shaped b200rt_scene_desc)."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    @property
+    def desc_ptr(self):
+        return host_lib().b200rt_host_desc(self._h)
+
+    @property
+    def header(self):
+        return SceneHeader.from_address(self.desc_ptr)
+
+    mode = property(lambda s: s.header.mode)
+    width = property(lambda s: s.header.width)
+    height = property(lambda s: s.header.height)
+    samples = property(lambda s: s.header.samples)
+    ray_depth = property(lambda s: s.header.ray_depth)
+
+    def set_frame(self, width=0, height=0, samples=0):
+        host_lib().b200rt_host_set_frame(self._h, width, height, samples)
+
+    def set_env_map(self, path):
+        rc = host_lib().b200rt_host_set_env_map(self._h, os.fsencode(path))
+        if rc:
+            raise B200rtError(rc, host_lib().b200rt_host_strerror(rc).decode())
+
+    def timings(self):
+        a, b = ctypes.c_double(), ctypes.c_double()
+        host_lib().b200rt_host_timings(self._h, ctypes.byref(a), ctypes.byref(b))
+        return {"parse_ms": a.value, "bvh_ms": b.value}
+
+    def close(self):
+        if self._h:
+            host_lib().b200rt_host_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def load_scene(path, width=None, height=None, samples=None, mode=0, env_map=None):
+    """sceneio::loadScene: text scenes take everything from the file; glTF scenes take
+    width/height/samples from the caller (argv in the reference, hw8/src/main.cpp:9-11)."""
+    L = host_lib()
+    h = ctypes.c_void_p()
+    p = os.fsencode(path)
+    if str(path).lower().endswith((".gltf",)):
+        if not (width and height and samples):
+            raise ValueError("glTF scenes need width, height and samples")
+        rc = L.b200rt_host_load_gltf(p, mode, width, height, samples, ctypes.byref(h))
+    else:
+        rc = L.b200rt_host_load_text(p, mode, ctypes.byref(h))
+    if rc:
+        raise B200rtError(rc, L.b200rt_host_strerror(rc).decode())
+    sc = Scene(h)
+    if not str(path).lower().endswith(".gltf") and (width or height or samples):
+        sc.set_frame(width or 0, height or 0, samples or 0)
+    if env_map:
+        sc.set_env_map(env_map)
+    return sc
+
+
+class Renderer:
+    """One b200rt context = one GPU."""
+
+    def __init__(self, device=0, seed=0, flags=0):
+        self._L = device_lib()
+        self._ctx = ctypes.c_void_p()
+        opt = Options(device, seed, flags)
+        rc = self._L.b200rt_create(ctypes.byref(self._ctx), ctypes.byref(opt))
+        if rc:
+            raise B200rtError(rc, self._L.b200rt_strerror(rc).decode())
+        self.width = self.height = 0
+
+    def _ck(self, rc):
+        if rc:
+            raise B200rtError(rc, self._L.b200rt_strerror(rc).decode() + " / " + self._L.b200rt_last_error(self._ctx).decode())
+
+    def upload(self, scene):
+        self._ck(self._L.b200rt_upload_scene(self._ctx, scene.desc_ptr))
+        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
+
+    def render(self, spp_begin=0, spp_end=None, width=0, height=0, ray_depth=0):
+        if spp_end is None:
+            spp_end = self.samples
+        if width > 0:
+            self.width = width
+        if height > 0:
+            self.height = height
+        self._ck(self._L.b200rt_render(self._ctx, width, height, spp_begin, spp_end, ray_depth))
+
+    def clear(self):
+        self._ck(self._L.b200rt_clear(self._ctx))
+
+    def synchronize(self):
+        self._ck(self._L.b200rt_synchronize(self._ctx))
+
+    def resolve(self, total_spp=None, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 3), np.uint8)
+        self._ck(self._L.b200rt_resolve(self._ctx, total_spp or self.samples, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def download_accum(self):
+        out = np.empty((self.height, self.width, 3), np.float32)
+        self._ck(self._L.b200rt_download_accum(self._ctx, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def upload_accum(self, arr):
+        arr = np.ascontiguousarray(arr, np.float32)
+        self._ck(self._L.b200rt_upload_accum(self._ctx, arr.ctypes.data_as(ctypes.c_void_p)))
+
+    def accum_device_ptr(self):
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        self._ck(self._L.b200rt_accum_device_ptr(self._ctx, ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def primary_ids(self):
+        out = np.empty((self.height, self.width), np.int32)
+        self._ck(self._L.b200rt_primary_ids(self._ctx, self.width, self.height, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def stats(self):
+        s = Stats()
+        self._ck(self._L.b200rt_get_stats(self._ctx, ctypes.byref(s)))
+        return s.as_dict()
+
+    def stream(self):
+        p = ctypes.c_void_p()
+        self._ck(self._L.b200rt_stream(self._ctx, ctypes.byref(p)))
+        return p.value or 0
+
+    def close(self):
+        if self._ctx:
+            self._L.b200rt_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def write_ppm(path, rgb):
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    rc = host_lib().b200rt_host_write_ppm(os.fsencode(path), rgb.shape[1], rgb.shape[0], rgb.ctypes.data_as(ctypes.c_void_p))
+    if rc:
+        raise B200rtError(rc, host_lib().b200rt_host_strerror(rc).decode())
+
+
+def render_scene(scene, out_path=None, device=0, seed=0):
+    """sceneio::renderScene (hw8/src/sceneio.cpp:381-402): render all samples, tonemap, write the PPM."""
+    r = Renderer(device=device, seed=seed)
+    try:
+        r.upload(scene)
+        r.render(0, scene.samples)
+        img = r.resolve(scene.samples)
+    finally:
+        r.close()
+    if out_path:
+        write_ppm(out_path, img)
+    return img
