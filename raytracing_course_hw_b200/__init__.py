@@ -45,6 +45,28 @@ class SceneHeader(ctypes.Structure):
                 ("samples", ctypes.c_int32), ("ray_depth", ctypes.c_int32)]
 
 
+class Image(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_int32), ("height", ctypes.c_int32), ("rgb", ctypes.POINTER(ctypes.c_uint8))]
+
+
+class SceneDesc(ctypes.Structure):
+    """Full b200rt_scene_desc (include/b200rt.h), for tests and tools that inspect loaded scenes."""
+    _fields_ = [("mode", ctypes.c_int32), ("width", ctypes.c_int32), ("height", ctypes.c_int32),
+                ("samples", ctypes.c_int32), ("ray_depth", ctypes.c_int32),
+                ("bg_color", ctypes.c_float * 3), ("ambient", ctypes.c_float * 3),
+                ("cam_pos", ctypes.c_float * 3), ("cam_right", ctypes.c_float * 3),
+                ("cam_up", ctypes.c_float * 3), ("cam_forward", ctypes.c_float * 3), ("cam_fov", ctypes.c_float),
+                ("prims", ctypes.c_void_p), ("n_prims", ctypes.c_int32),
+                ("lights", ctypes.c_void_p), ("n_lights", ctypes.c_int32),
+                ("tris", ctypes.c_void_p), ("n_tris", ctypes.c_int32),
+                ("nodes", ctypes.c_void_p), ("n_nodes", ctypes.c_int32), ("root", ctypes.c_int32),
+                ("light_tris", ctypes.c_void_p), ("n_light_tris", ctypes.c_int32),
+                ("light_nodes", ctypes.c_void_p), ("n_light_nodes", ctypes.c_int32),
+                ("materials", ctypes.c_void_p), ("n_materials", ctypes.c_int32),
+                ("images", ctypes.POINTER(Image)), ("n_images", ctypes.c_int32),
+                ("env_map", ctypes.POINTER(Image))]
+
+
 _host = None
 _dev = None
 
@@ -120,6 +142,10 @@ class Scene:
     @property
     def header(self):
         return SceneHeader.from_address(self.desc_ptr)
+
+    @property
+    def desc(self):
+        return SceneDesc.from_address(self.desc_ptr)
 
     mode = property(lambda s: s.header.mode)
     width = property(lambda s: s.header.width)

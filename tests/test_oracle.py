@@ -1,0 +1,77 @@
+"""Pins the oracle: the CPU port (oracle/port_*.cpp) run with the REFERENCE's own minstd stream must
+reproduce the PPM bytes of the unmodified reference binaries (committed under tests/golden/, made by
+tools/make_golden.py).  This also pins the host loaders and the SAH BVH build, because the port
+consumes the scene description they produce (triangle order decides light sampling)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+import raytracing_course_hw_b200 as rt
+
+S, G = ou.SCENES, ou.GOLDEN
+
+
+def test_port_hw1_bytes_equal_reference():
+    sc = rt.load_scene(os.path.join(S, "hw1/sample.txt"))
+    assert (sc.mode, sc.width, sc.height) == (rt.MODE_HW1, 640, 480)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden("hw1_sample"))
+    # flat colours => colour <-> primitive id is 1:1 in this scene: ids are pinned too
+    ids = o["ids"]
+    assert set(np.unique(ids)) == {-1, 0, 1, 2}
+    ref = ou.golden("hw1_sample")
+    for pid, colour in ((-1, (0, 0, 128)), (0, (255, 0, 0)), (1, (0, 255, 0)), (2, (255, 255, 0))):
+        assert (ref[ids == pid] == np.array(colour, np.uint8)).all()
+
+
+def test_port_hw2_bytes_equal_reference():
+    sc = rt.load_scene(os.path.join(S, "hw2/sample.txt"))
+    assert (sc.mode, sc.width, sc.height, sc.ray_depth) == (rt.MODE_HW2, 664, 510, 5)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden("hw2_sample"))
+
+
+@pytest.mark.parametrize("k", [1, 3, 4])
+def test_port_hw4_bytes_equal_reference(k):
+    sc = rt.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"))
+    assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW4, 160, 120, 4, 6)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden(f"hw4_p3_{k}_spp4"))
+
+
+@pytest.mark.parametrize("name,path", [("hw7_practice7_1", "hw7/practice7_1.gltf"),
+                                       ("hw7_practice7_4", "hw7/practice7_4.gltf"),
+                                       ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf")])
+def test_port_gltf_bytes_equal_reference(name, path):
+    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=4)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
+
+
+def test_port_philox_is_statistically_the_same_estimator():
+    """The Philox policy changes only the random numbers: at equal spp its error against the
+    4096-spp reference render must be comparable to the minstd policy's, and the mean must agree."""
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=32)
+    truth = ou.inv_display(ou.golden("hw8_sphere_emissive_128x96_spp4096"))
+    a = ou.inv_display(ou.port_render(sc, 0)["rgb"])
+    b = ou.inv_display(ou.port_render(sc, 1)["rgb"])
+    rmse_a = np.sqrt(((a - truth) ** 2).mean())
+    rmse_b = np.sqrt(((b - truth) ** 2).mean())
+    assert rmse_b <= 1.15 * rmse_a
+    assert abs(b.mean() - truth.mean()) <= 0.02 * truth.mean()
+
+
+def test_port_sample_ranges_add_up():
+    """Counter-based stream: rendering [0,4) and [4,8) separately equals [0,8) up to float order."""
+    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=64, height=48, samples=8)
+    full = ou.port_render(sc, 1, spp_begin=0, spp_end=8)["accum"]
+    parts = ou.port_render(sc, 1, spp_begin=0, spp_end=4)["accum"] + ou.port_render(sc, 1, spp_begin=4, spp_end=8)["accum"]
+    assert np.allclose(full, parts, rtol=1e-5, atol=1e-6)
+
+
+def test_port_resolve_matches_port_render():
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=64, height=48, samples=4)
+    o = ou.port_render(sc, 1)
+    assert np.array_equal(ou.port_resolve(o["accum"], 4), o["rgb"])
