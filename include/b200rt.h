@@ -156,7 +156,8 @@ typedef struct b200rt_options {
     int32_t  flags;         /* B200RT_FLAG_* */
 } b200rt_options;
 
-#define B200RT_FLAG_COUNTERS 1   /* count rays / node fetches / triangle tests (slower kernel) */
+#define B200RT_FLAG_COUNTERS   1  /* also count node fetches / triangle tests / texture lookups */
+#define B200RT_FLAG_MEGAKERNEL 2  /* glTF modes: one-kernel-per-path variant instead of the wavefront pipeline */
 
 typedef struct b200rt_stats {
     double   kernel_ms;        /* device time of the last b200rt_render (CUDA events) */
@@ -182,7 +183,7 @@ int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *scene);
 
 /* Replaces: the pixel loop + Scene::getPixel (hw8/src/sceneio.cpp:387-392, scene.cpp:167-177).
  * Renders global sample indices [spp_begin, spp_end) of every pixel and ADDS them to the
- * float accumulation buffer (cleared when spp_begin == 0 or after b200rt_clear).
+ * float accumulation buffer (zeroed by b200rt_upload_scene, b200rt_clear or a frame-size change).
  * width/height/ray_depth <= 0 take the scene's values.  Asynchronous on the context stream. */
 int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height,
                   int32_t spp_begin, int32_t spp_end, int32_t ray_depth);

@@ -11,6 +11,7 @@
 #include "b200rt.h"
 #include "device_scene.h"
 #include "gltf_kernel.cuh"
+#include "wavefront.cuh"
 
 using namespace b200rt;
 
@@ -35,6 +36,11 @@ struct b200rt_ctx {
     uint8_t *rgb8 = nullptr;
     int32_t *ids = nullptr;
     DCounters *counters = nullptr;
+    // wavefront pipeline state (glTF modes)
+    WaveBuffers wave{};
+    size_t wave_capacity = 0;
+    int num_sms = 0;
+    int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0};
     b200rt_stats stats{};
     bool timing_pending = false;
 };
@@ -332,6 +338,88 @@ int ensure_buffers(b200rt_ctx *ctx, int w, int h, int n_slabs) {
     return B200RT_OK;
 }
 
+void free_wave(b200rt_ctx *c) {
+    cudaFree(c->wave.ray_o); cudaFree(c->wave.ray_d); cudaFree(c->wave.thr); cudaFree(c->wave.rad);
+    cudaFree(c->wave.bsdf); cudaFree(c->wave.hit); cudaFree(c->wave.ctr);
+    for (int i = 0; i < 3; i++) cudaFree(c->wave.queue[i]);
+    c->wave = WaveBuffers{};
+    c->wave_capacity = 0;
+}
+
+#define B200RT_MAX_DEPTH 64
+int ensure_wave(b200rt_ctx *ctx, size_t slots) {
+    if (slots <= ctx->wave_capacity) return B200RT_OK;
+    free_wave(ctx);
+    WaveBuffers &w = ctx->wave;
+    CK(cudaMalloc(&w.ray_o, slots * sizeof(float4)));
+    CK(cudaMalloc(&w.ray_d, slots * sizeof(float4)));
+    CK(cudaMalloc(&w.thr, slots * sizeof(float4)));
+    CK(cudaMalloc(&w.rad, slots * sizeof(float4)));
+    CK(cudaMalloc(&w.bsdf, slots * sizeof(float4)));
+    CK(cudaMalloc(&w.hit, slots * sizeof(float4)));
+    for (int i = 0; i < 3; i++) CK(cudaMalloc(&w.queue[i], slots * sizeof(int)));
+    CK(cudaMalloc(&w.ctr, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int)));
+    ctx->wave_capacity = slots;
+    return B200RT_OK;
+}
+
+// Wavefront render of sample indices [spp_begin, spp_end): waves of (all pixels) x S_w samples.
+template <bool HW8, bool COUNT>
+int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
+    const int W = rp.cam.width, H = rp.cam.height;
+    WaveParams wp{};
+    wp.cam = rp.cam;
+    wp.tiles_x = (W + 7) / 8;
+    wp.n_tiles = wp.tiles_x * ((H + 3) / 4);
+    wp.seed = rp.seed;
+    const long long per = (long long)wp.n_tiles * 32;
+    const int total = rp.spp_end - rp.spp_begin;
+    long long s_w = std::max<long long>(1, (4ll << 20) / per);           // aim at >= 4 M paths per wave
+    s_w = std::min<long long>({s_w, (long long)total, std::max<long long>(1, (16ll << 20) / per)});
+    int rc = ensure_wave(ctx, (size_t)(per * s_w));
+    if (rc) return rc;
+    if (rp.ray_depth > B200RT_MAX_DEPTH) return fail(ctx, B200RT_ERR_UNSUPPORTED, "ray depth above 64");
+    if (!ctx->blocks_extend[COUNT]) {
+        int dev = ctx->device, nb = 0;
+        CK(cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, dev));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_extend<COUNT>, 128, 0));
+        ctx->blocks_extend[COUNT] = std::max(1, nb) * ctx->num_sms;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_light<COUNT>, 128, 0));
+        ctx->blocks_light[COUNT] = std::max(1, nb) * ctx->num_sms;
+    }
+    const WaveBuffers &wb = ctx->wave;
+    const bool lights = ctx->gs.n_light_tris > 0;
+    const int flat_blocks = ctx->num_sms * 16;
+    cudaStream_t st = ctx->stream;
+    for (int s0 = rp.spp_begin; s0 < rp.spp_end; s0 += (int)s_w) {
+        wp.s_begin = s0;
+        wp.s_count = std::min<int>((int)s_w, rp.spp_end - s0);
+        CK(cudaMemsetAsync(wb.ctr, 0, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int), st));
+        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters);
+        (*launches)++;
+        int *qa = wb.queue[0], *qb = wb.queue[2];
+        for (int b = 0; b < rp.ray_depth; b++) {
+            int *c = wb.ctr + 4 * b;
+            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters);
+            const bool last = b == rp.ray_depth - 1;
+            if (lights && !last) {
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters);
+                (*launches) += 3;
+            } else {
+                // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, b, ctx->lut_srgb, ctx->counters);
+                (*launches) += 2;
+            }
+            std::swap(qa, qb);
+        }
+        wf_accumulate<<<(unsigned)((per + 255) / 256), 256, 0, st>>>(wp, wb, ctx->total);
+        (*launches)++;
+        CK(cudaGetLastError());
+    }
+    return B200RT_OK;
+}
+
 // tan of the half field of view with the libm call the reference's TU binds to (hw1/hw2 include
 // <math.h> => tanf; hw3..hw8 include only <cmath> => double tan rounded to float).
 void camera_of(const b200rt_scene_desc &d, int w, int h, DCamera &c) {
@@ -382,6 +470,7 @@ void b200rt_destroy(b200rt_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     release_scene(ctx);
+    free_wave(ctx);
     cudaFree(ctx->total); cudaFree(ctx->slabs); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->counters);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -473,6 +562,14 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
     if (d.mode == B200RT_MODE_HW1) { CK(launch_cast(rp.cam, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
     else if (d.mode == B200RT_MODE_HW2) { CK(launch_whitted(rp.cam, ray_depth, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
     else if (d.mode == B200RT_MODE_HW4) { CK(launch_pt_analytic(rp, ctx->stream)); launches++; }
+    else if (!(ctx->flags & B200RT_FLAG_MEGAKERNEL)) {
+        const bool count = ctx->flags & B200RT_FLAG_COUNTERS;
+        int wrc;
+        if (ctx->gs.hw8) wrc = count ? render_wavefront<true, true>(ctx, rp, &launches) : render_wavefront<true, false>(ctx, rp, &launches);
+        else wrc = count ? render_wavefront<false, true>(ctx, rp, &launches) : render_wavefront<false, false>(ctx, rp, &launches);
+        if (wrc) return wrc;
+        n_chunks = 0;   // the wavefront accumulates into `total` itself
+    }
     else {
         const int tiles = ((width + 7) / 8) * ((height + 3) / 4);
         const long long warps = (long long)tiles * n_chunks;
@@ -492,7 +589,7 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
         launches++;
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    {
+    if (n_chunks > 0) {
         const size_t n = (size_t)n_px * 3;
         fold_slabs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->total, ctx->slabs, n_chunks, n);
         CK(cudaGetLastError());

@@ -274,19 +274,26 @@ __device__ __forceinline__ float vndf_pdf_local(const V3 d, const V3 v, float a)
 
 namespace b200rt {
 
-// One bounce of Scene::getColor (hw8/src/scene.cpp:84-165).  Returns false when the path ends.
-// L accumulates throughput-weighted emission; T is the path throughput (product of `mult`).
+// One bounce of Scene::getColor (hw8/src/scene.cpp:84-165), split in two so that the light-BVH
+// query between them can run either inline (megakernel) or as its own wavefront stage.
+struct BounceOut {
+    V3 xo, nd, brdf;        // next ray origin / direction, BRDF value
+    float pdf_partial;      // cosine pdf + VNDF pdf
+    float absdot;           // |nd . n_shading|
+};
+
+// Surface part: fetch the shading record, material and textures, add the emission to L, draw the
+// next direction from Mix{Cosine, Vndf, [lights]} and evaluate the BRDF.  Returns false when the
+// path ends here (BRDF below 1e-4 in every channel, scene.cpp:154-156).
 template <bool HW8, bool COUNT>
-__device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *lut_srgb, const float *lut_lin,
-                                             const TraceHit &hit, V3 &o, V3 &d, V3 &L, V3 &T,
-                                             const uint4 rnd, ThreadCounters &tc) {
-    const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + hit.tri);
+__device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float *lut_srgb, const float *lut_lin,
+                                              const V3 o, const V3 d, float t, float u, float v, int tri, bool inside,
+                                              V3 &L, const V3 T, const uint4 rnd, ThreadCounters &tc, BounceOut &out) {
+    const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + tri);
     const float4 tv0 = __ldg(tq), te1 = __ldg(tq + 1), te2 = __ldg(tq + 2);
-    const bool inside = hit.det > 0.f;   // ray.d . n > 0 with n = b.cross(c) (primitives.cpp:21)
-    const float u = hit.u, v = hit.v;
     if (COUNT) tc.shaded++;
 
-    const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + hit.tri);
+    const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
     const float4 s0 = __ldg(sq), s1 = __ldg(sq + 1), s2 = __ldg(sq + 2);
     V3 ns = normalize(mk(s2.x + u * (s0.x - s2.x) + v * (s1.x - s2.x),
                          s2.y + u * (s0.y - s2.y) + v * (s1.y - s2.y),
@@ -330,7 +337,7 @@ __device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *
         alpha = roughness_factor * roughness_factor;
     }
 
-    const V3 x = o + hit.t * d;
+    const V3 x = o + t * d;
     const V3 xo = x + B200RT_EPS * ng;     // origin offset along the GEOMETRIC normal (scene.cpp:151-152)
     const V3 vdir = -d;                    // towards the viewer
 
@@ -362,21 +369,43 @@ __device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *
     const V3 brdf = eval_brdf<HW8>(base, metallic_factor, nd, vdir, ns, color, metallic, alpha);
     if (brdf.x < B200RT_EPS && brdf.y < B200RT_EPS && brdf.z < B200RT_EPS) return false;
 
-    // Mix::pdf (:267-279) = mean of all component pdfs
+    // first two terms of Mix::pdf (:267-279)
     float pdf = fmaxf(0.f, dot(nd, ns) * 0.318309886183791f);
     pdf += vndf_pdf_local(to_local(fr, nd), vloc, alpha);
-    if (k == 3) {
-        tc.light_queries++;
-        pdf += light_pdf_sum<COUNT>(sc, xo, nd, tc) / (float)sc.n_light_tris;
-    }
-    pdf /= (float)k;
-    const float w = (1.f / pdf) * fabsf(dot(nd, ns));
+    out.xo = xo; out.nd = nd; out.brdf = brdf; out.pdf_partial = pdf; out.absdot = fabsf(dot(nd, ns));
+    return true;
+}
+
+// Second part: mean of the component pdfs, path weight, firefly clamp (scene.cpp:158-163).
+// light_sum = FiguresMix::getTotalPdf for the ray (xo, nd); ignored when there are no emitters.
+__device__ __forceinline__ bool finish_bounce(const V3 brdf, float pdf_partial, float absdot, float light_sum,
+                                              int n_light_tris, V3 &T) {
+    float pdf = pdf_partial;
+    float k = 2.f;
+    if (n_light_tris > 0) { pdf += light_sum / (float)n_light_tris; k = 3.f; }
+    pdf /= k;
+    const float w = (1.f / pdf) * absdot;
     const V3 mult = w * brdf;
-    // firefly clamp (scene.cpp:161): any channel > 6 or NaN ends the path
+    // any channel > 6 or NaN ends the path
     if (!(mult.x <= 6.f) || !(mult.y <= 6.f) || !(mult.z <= 6.f)) return false;
     T = T * mult;
-    o = xo;
-    d = nd;
+    return true;
+}
+
+template <bool HW8, bool COUNT>
+__device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *lut_srgb, const float *lut_lin,
+                                             const TraceHit &hit, V3 &o, V3 &d, V3 &L, V3 &T,
+                                             const uint4 rnd, ThreadCounters &tc) {
+    BounceOut bo;
+    if (!shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, hit.t, hit.u, hit.v, hit.tri, hit.det > 0.f, L, T, rnd, tc, bo)) return false;
+    float ls = 0.f;
+    if (sc.n_light_tris > 0) {
+        tc.light_queries++;
+        ls = light_pdf_sum<COUNT>(sc, bo.xo, bo.nd, tc);
+    }
+    if (!finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, ls, sc.n_light_tris, T)) return false;
+    o = bo.xo;
+    d = bo.nd;
     return true;
 }
 

@@ -1,0 +1,424 @@
+// K4w: wavefront form of the glTF path tracer (same arithmetic as gltf_kernel.cuh, different
+// scheduling).  ncu on the megakernel showed 7.5 of 32 lanes active on average (profiles/
+// r01_megakernel_*): incoherent rays make per-warp lockstep traversal idle most lanes.  Here every
+// bounce is split into stages that exchange path indices through device queues:
+//
+//   generate  : camera rays of one wave (all pixels x S_w sample indices)           -> queue A
+//   extend    : closest hit, PERSISTENT warps that refill idle lanes from the queue -> hit[]
+//   shade     : material/textures/BRDF/sampling; emission into rad[]               -> queue M
+//   light     : FiguresMix::getTotalPdf query, persistent like extend; then the pdf mean, weight
+//               and firefly clamp                                                  -> queue B (next bounce)
+//   accumulate: total[pixel] += sum over the wave's samples of rad[] (fixed order, no float atomics)
+//
+// Inside the persistent kernels a warp alternates between an "inner node" phase and a "leaf"
+// phase chosen by ballot, so the two code paths are never both executed for one step, and lanes
+// whose query finished are refilled every B200RT_WF_BATCH steps.
+// Reference code replaced: same as gltf_kernel.cuh (hw8/src/scene.cpp:84-187, bvh.h:111-142,
+// distributions.h:122-165).
+#pragma once
+#include "gltf_kernel.cuh"
+
+namespace b200rt {
+
+#define B200RT_WF_BATCH 8        /* traversal steps between refills */
+#define B200RT_WF_LEAF_T 6       /* lanes waiting at a leaf that trigger a leaf phase */
+#define B200RT_WF_MISS 0x7FFFFFFFu
+#define B200RT_FULL 0xffffffffu
+
+struct WaveBuffers {
+    float4 *ray_o;   // o.xyz, -
+    float4 *ray_d;   // d.xyz, |nd . n_s| of the bounce that produced this ray
+    float4 *thr;     // throughput T.xyz, partial pdf (cosine + vndf)
+    float4 *rad;     // radiance L.xyz, -
+    float4 *bsdf;    // BRDF value of the pending bounce
+    float4 *hit;     // t, u, v, bits: triangle index | inside << 31 (B200RT_WF_MISS = no hit)
+    int *queue[3];
+    // per bounce b: ctr[4b] = rays entering bounce b, ctr[4b+1] = extend cursor,
+    //               ctr[4b+2] = light queries of bounce b, ctr[4b+3] = light cursor
+    int *ctr;
+};
+
+struct WaveParams {
+    DCamera cam;
+    int32_t tiles_x, n_tiles;     // 8x4 pixel tiles
+    int32_t s_begin, s_count;     // global sample indices [s_begin, s_begin + s_count) in this wave
+    uint32_t seed;
+};
+
+__device__ __forceinline__ bool slot_to_pixel(const WaveParams &wp, int slot, int &px, int &py, int &s_local) {
+    const int per = wp.n_tiles * 32;
+    s_local = slot / per;
+    const int r = slot - s_local * per;
+    const int tile = r >> 5, lane = r & 31;
+    px = (tile % wp.tiles_x) * 8 + (lane & 7);
+    py = (tile / wp.tiles_x) * 4 + (lane >> 3);
+    return px < wp.cam.width && py < wp.cam.height;
+}
+
+// Warp-aggregated append; every lane of the warp must call it (converged).
+__device__ __forceinline__ void queue_push(int *queue, int *counter, bool want, int value) {
+    const unsigned m = __ballot_sync(B200RT_FULL, want);
+    if (m == 0) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(B200RT_FULL, base, leader);
+    if (want) queue[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+
+__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters) {
+    const int n_slots = wp.n_tiles * 32 * wp.s_count;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const V3 cpos = ld3(wp.cam.pos), cright = ld3(wp.cam.right), cup = ld3(wp.cam.up), cfwd = ld3(wp.cam.forward);
+    unsigned made = 0;
+    for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n_slots; base += warps * 32) {
+        const int slot = base + lane;
+        int px, py, sl;
+        const bool ok = slot_to_pixel(wp, slot, px, py, sl);
+        if (ok) {
+            const uint32_t pixel = (uint32_t)(py * wp.cam.width + px);
+            const uint4 j = philox4x32_10((uint32_t)(wp.s_begin + sl), 0u, pixel, wp.seed);
+            const float fx = (float)px + u01(j.x), fy = (float)py + u01(j.y);
+            const float nx = wp.cam.tan_x * (2.f * fx / (float)wp.cam.width - 1.f);
+            const float ny = wp.cam.tan_y * (2.f * fy / (float)wp.cam.height - 1.f);
+            const V3 d = normalize(nx * cright - ny * cup + cfwd);
+            wb.ray_o[slot] = make_float4(cpos.x, cpos.y, cpos.z, 0.f);
+            wb.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.f);
+            wb.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+            wb.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            made++;
+        }
+        queue_push(wb.queue[0], wb.ctr + 0, ok, slot);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) made += __shfl_down_sync(B200RT_FULL, made, off);
+    if (lane == 0 && made) atomicAdd(&counters->paths, (unsigned long long)made);
+}
+
+// ---- persistent closest-hit traversal ------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
+                                                 const int *__restrict__ n_in, int *cursor, DCounters *counters) {
+    const int n = *n_in;
+    const int lane = threadIdx.x & 31;
+    uint2 stack[B200RT_STACK];
+    int sp = 0;
+    bool active = false, exhausted = false;
+    int p = 0;
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 0);
+    float tbest = 0.f, hu = 0.f, hv = 0.f, hdet = 0.f;
+    uint32_t htri = B200RT_WF_MISS, cur = 0;
+    unsigned node_tests = 0, tri_tests = 0;
+    bool overflow = false;
+
+    while (true) {
+        const unsigned idle = __ballot_sync(B200RT_FULL, !active);
+        if (!exhausted && idle) {
+            const int n_idle = __popc(idle), leader = __ffs(idle) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(cursor, n_idle);
+            base = __shfl_sync(B200RT_FULL, base, leader);
+            if (!active) {
+                const int idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < n) {
+                    p = q_in[idx];
+                    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+                    o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
+                    inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+                    tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
+                    sp = 0;
+                    cur = __ldg(&sc.nodes[0].a);
+                    active = true;
+                }
+            }
+            if (base + n_idle >= n) exhausted = true;
+        }
+        if (__ballot_sync(B200RT_FULL, active) == 0) break;
+
+        for (int it = 0; it < B200RT_WF_BATCH; it++) {
+            const bool at_leaf = active && (cur & B200RT_LEAF);
+            const bool at_inner = active && !(cur & B200RT_LEAF);
+            const unsigned leaf_mask = __ballot_sync(B200RT_FULL, at_leaf);
+            const unsigned inner_mask = __ballot_sync(B200RT_FULL, at_inner);
+            if ((leaf_mask | inner_mask) == 0) break;
+            bool pop = false;
+            if (inner_mask == 0 || __popc(leaf_mask) >= B200RT_WF_LEAF_T) {
+                if (at_leaf) {
+                    const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
+                    for (uint32_t i = first; i < first + count; i++) {
+                        const float4 *q = reinterpret_cast<const float4 *>(sc.tris + i);
+                        const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+                        if (COUNT) tri_tests++;
+                        const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+                        const V3 pv = cross(d, E2);
+                        const float det = dot(E1, pv);
+                        const float idet = 1.f / det;
+                        const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
+                        const float u = dot(tv, pv) * idet;
+                        const V3 qv = cross(tv, E1);
+                        const float v = dot(d, qv) * idet;
+                        const float t = dot(E2, qv) * idet;
+                        if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < tbest) { tbest = t; hu = u; hv = v; htri = i; hdet = det; }
+                    }
+                    pop = true;
+                }
+            } else if (at_inner) {
+                const float4 *pn = reinterpret_cast<const float4 *>(sc.nodes + cur);
+                const float4 l0 = __ldg(pn), l1 = __ldg(pn + 1), r0 = __ldg(pn + 2), r1 = __ldg(pn + 3);
+                float tl, tr;
+                const bool hl = slab(l0, l1, o, inv, tbest, tl);
+                const bool hr = slab(r0, r1, o, inv, tbest, tr);
+                if (COUNT) node_tests += 2;
+                const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
+                if (hl && hr) {
+                    const bool left_first = tl <= tr;
+                    if (sp < B200RT_STACK) stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
+                    else overflow = true;
+                    cur = left_first ? ml : mr;
+                } else if (hl) cur = ml;
+                else if (hr) cur = mr;
+                else pop = true;
+            }
+            if (pop) {
+                // skip stacked subtrees that a closer hit has made irrelevant
+                bool got = false;
+                while (sp > 0) {
+                    const uint2 e = stack[--sp];
+                    if (__uint_as_float(e.y) <= tbest) { cur = e.x; got = true; break; }
+                }
+                if (!got) {
+                    const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
+                    wb.hit[p] = make_float4(tbest, hu, hv, __uint_as_float(bits));
+                    active = false;
+                }
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&counters->rays, (unsigned long long)n);
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            node_tests += __shfl_down_sync(B200RT_FULL, node_tests, off);
+            tri_tests += __shfl_down_sync(B200RT_FULL, tri_tests, off);
+        }
+        if (lane == 0) {
+            atomicAdd(&counters->node_tests, (unsigned long long)node_tests);
+            atomicAdd(&counters->tri_tests, (unsigned long long)tri_tests);
+        }
+    }
+    if (overflow) atomicAdd(&counters->stack_overflow, 1ull);
+}
+
+// ---- shade --------------------------------------------------------------------------------------
+template <bool HW8, bool COUNT>
+__global__ void __launch_bounds__(128) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
+                                                const int *__restrict__ n_in, int *q_out, int *n_out, int bounce,
+                                                const float *__restrict__ lut_srgb_g, DCounters *counters) {
+    __shared__ float lut_srgb[256];
+    __shared__ float lut_lin[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        lut_srgb[i] = lut_srgb_g[i];
+        lut_lin[i] = 0.00392156862745098f * (float)i;
+    }
+    __syncthreads();
+    const int n = *n_in;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const bool has_lights = sc.n_light_tris > 0;
+    ThreadCounters tc = {};
+    for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n; base += warps * 32) {
+        const int i = base + lane;
+        bool cont = false;
+        int p = 0;
+        if (i < n) {
+            p = q_in[i];
+            const float4 h = wb.hit[p];
+            const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+            const float4 th = wb.thr[p];
+            float4 ra = wb.rad[p];
+            const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
+            V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
+            const uint32_t bits = __float_as_uint(h.w);
+            if (bits == B200RT_WF_MISS) {
+                V3 bg = ld3(sc.bg);
+                if (HW8 && sc.env) {
+                    const float tx = 0.5f + 0.5f * atan2f(d.z, d.x) * 0.318309886183791f;
+                    const float ty = 0.5f - asinf(d.y) * 0.318309886183791f;
+                    bg = sample_texture(sc.env, sc.env_w, sc.env_h, tx, ty, lut_srgb);
+                }
+                L = L + T * bg;
+            } else {
+                int px, py, sl;
+                slot_to_pixel(wp, p, px, py, sl);
+                const uint4 rnd = philox4x32_10((uint32_t)(wp.s_begin + sl), 16u * (uint32_t)(bounce + 1), (uint32_t)(py * wp.cam.width + px), wp.seed);
+                BounceOut bo;
+                cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, (int)(bits & 0x7FFFFFFFu), (bits >> 31) != 0, L, T, rnd, tc, bo);
+                if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
+                if (cont) {
+                    wb.ray_o[p] = make_float4(bo.xo.x, bo.xo.y, bo.xo.z, 0.f);
+                    wb.ray_d[p] = make_float4(bo.nd.x, bo.nd.y, bo.nd.z, bo.absdot);
+                    wb.thr[p] = make_float4(T.x, T.y, T.z, bo.pdf_partial);
+                    if (has_lights) wb.bsdf[p] = make_float4(bo.brdf.x, bo.brdf.y, bo.brdf.z, 0.f);
+                }
+            }
+            wb.rad[p] = make_float4(L.x, L.y, L.z, 0.f);
+        }
+        queue_push(q_out, n_out, cont, p);
+    }
+    if (COUNT) flush_counters(counters, tc);
+}
+
+// ---- persistent light-pdf traversal + end of the bounce ---------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
+                                                const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters) {
+    const int n = *n_in;
+    const int lane = threadIdx.x & 31;
+    uint32_t stack[B200RT_STACK];
+    int sp = 0;
+    bool active = false, exhausted = false;
+    int p = 0;
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 0);
+    float total = 0.f;
+    uint32_t cur = 0;
+    unsigned node_tests = 0, tri_tests = 0;
+    bool overflow = false;
+    bool push_pending = false;
+    int push_p = 0;
+
+    while (true) {
+        // converged point: publish the paths that finished during the last batch
+        queue_push(q_out, n_out, push_pending, push_p);
+        push_pending = false;
+        const unsigned idle = __ballot_sync(B200RT_FULL, !active);
+        if (!exhausted && idle) {
+            const int n_idle = __popc(idle), leader = __ffs(idle) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(cursor, n_idle);
+            base = __shfl_sync(B200RT_FULL, base, leader);
+            if (!active) {
+                const int idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < n) {
+                    p = q_in[idx];
+                    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+                    o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
+                    inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+                    total = 0.f; sp = 0;
+                    active = true;
+                    // the light root's box is a real filter (unlike the scene root)
+                    const float4 *pr = reinterpret_cast<const float4 *>(sc.light_nodes);
+                    float tn;
+                    if (COUNT) node_tests++;
+                    if (slab(__ldg(pr), __ldg(pr + 1), o, inv, INFINITY, tn)) cur = __ldg(&sc.light_nodes[0].a);
+                    else cur = B200RT_LEAF;      // empty leaf: finishes on the next leaf phase
+                }
+            }
+            if (base + n_idle >= n) exhausted = true;
+        }
+        if (__ballot_sync(B200RT_FULL, active) == 0) break;
+
+        for (int it = 0; it < B200RT_WF_BATCH; it++) {
+            const bool at_leaf = active && (cur & B200RT_LEAF);
+            const bool at_inner = active && !(cur & B200RT_LEAF);
+            const unsigned leaf_mask = __ballot_sync(B200RT_FULL, at_leaf);
+            const unsigned inner_mask = __ballot_sync(B200RT_FULL, at_inner);
+            if ((leaf_mask | inner_mask) == 0) break;
+            bool pop = false;
+            if (inner_mask == 0 || __popc(leaf_mask) >= B200RT_WF_LEAF_T) {
+                if (at_leaf) {
+                    const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
+                    for (uint32_t i = first; i < first + count; i++) {
+                        const float4 *q = reinterpret_cast<const float4 *>(sc.light_tris + i);
+                        const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+                        if (COUNT) tri_tests++;
+                        const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+                        const V3 pv = cross(d, E2);
+                        const float det = dot(E1, pv);
+                        const float idet = 1.f / det;
+                        const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
+                        const float u = dot(tv, pv) * idet;
+                        const V3 qv = cross(tv, E1);
+                        const float v = dot(d, qv) * idet;
+                        const float t = dot(E2, qv) * idet;
+                        if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < B200RT_TMAX) {
+                            V3 yn;
+                            if (sc.hw8) {
+                                const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);
+                                const float4 n0 = __ldg(nq), n1 = __ldg(nq + 1), n2 = __ldg(nq + 2);
+                                yn = normalize(mk(n2.x + u * (n0.x - n2.x) + v * (n1.x - n2.x),
+                                                  n2.y + u * (n0.y - n2.y) + v * (n1.y - n2.y),
+                                                  n2.z + u * (n0.z - n2.z) + v * (n1.z - n2.z)));
+                            } else {
+                                yn = normalize(cross(E2, E1));
+                            }
+                            const V3 td = t * d;
+                            total += v0.w * len2(td) / fabsf(dot(d, yn));
+                        }
+                    }
+                    pop = true;
+                }
+            } else if (at_inner) {
+                const float4 *pn = reinterpret_cast<const float4 *>(sc.light_nodes + cur);
+                const float4 l0 = __ldg(pn), l1 = __ldg(pn + 1), r0 = __ldg(pn + 2), r1 = __ldg(pn + 3);
+                float tl, tr;
+                const bool hl = slab(l0, l1, o, inv, INFINITY, tl);
+                const bool hr = slab(r0, r1, o, inv, INFINITY, tr);
+                if (COUNT) node_tests += 2;
+                const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
+                if (hl && hr) {
+                    if (sp < B200RT_STACK) stack[sp++] = mr; else overflow = true;
+                    cur = ml;
+                } else if (hl) cur = ml;
+                else if (hr) cur = mr;
+                else pop = true;
+            }
+            if (pop) {
+                if (sp > 0) cur = stack[--sp];
+                else {
+                    // end of the bounce: mean pdf, weight, firefly clamp (scene.cpp:158-163)
+                    const float4 th = wb.thr[p], bs = wb.bsdf[p];
+                    V3 T = mk(th.x, th.y, th.z);
+                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, wb.ray_d[p].w, total, sc.n_light_tris, T)) {
+                        wb.thr[p] = make_float4(T.x, T.y, T.z, 0.f);
+                        push_pending = true;
+                        push_p = p;
+                    }
+                    active = false;
+                }
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&counters->light_queries, (unsigned long long)n);
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            node_tests += __shfl_down_sync(B200RT_FULL, node_tests, off);
+            tri_tests += __shfl_down_sync(B200RT_FULL, tri_tests, off);
+        }
+        if (lane == 0) {
+            atomicAdd(&counters->light_node_tests, (unsigned long long)node_tests);
+            atomicAdd(&counters->light_tri_tests, (unsigned long long)tri_tests);
+        }
+    }
+    if (overflow) atomicAdd(&counters->stack_overflow, 1ull);
+}
+
+// total[pixel] += sum of the wave's samples, in sample order (deterministic)
+__global__ void wf_accumulate(const WaveParams wp, const WaveBuffers wb, float *__restrict__ total) {
+    const int per = wp.n_tiles * 32;
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= per) return;
+    int px, py, sl;
+    if (!slot_to_pixel(wp, r, px, py, sl)) return;
+    float3 acc = make_float3(0.f, 0.f, 0.f);
+    for (int s = 0; s < wp.s_count; s++) {
+        const float4 v = wb.rad[(size_t)s * per + r];
+        acc.x += v.x; acc.y += v.y; acc.z += v.z;
+    }
+    float *dst = total + ((size_t)py * wp.cam.width + px) * 3;
+    dst[0] += acc.x; dst[1] += acc.y; dst[2] += acc.z;
+}
+
+}  // namespace b200rt

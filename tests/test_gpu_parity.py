@@ -22,9 +22,12 @@ pytestmark = pytest.mark.gpu
 S, G = ou.SCENES, ou.GOLDEN
 
 
-@pytest.fixture(scope="module")
-def renderer():
-    r = rt.Renderer(flags=rt.FLAG_COUNTERS)
+@pytest.fixture(scope="module", params=["wavefront", "megakernel"])
+def renderer(request):
+    """Both schedulings of the glTF path tracer (K4w wavefront = default, K4 megakernel) run the
+    whole suite; the analytic kernels K1-K3 are the same under either flag."""
+    flags = rt.FLAG_COUNTERS | (rt.FLAG_MEGAKERNEL if request.param == "megakernel" else 0)
+    r = rt.Renderer(flags=flags)
     yield r
     r.close()
 

@@ -15,10 +15,11 @@ ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--tris", type=int, default=270000)
 ap.add_argument("--scene", default=None)
 ap.add_argument("--counters", action="store_true")
+ap.add_argument("--megakernel", action="store_true")
 a = ap.parse_args()
 path = a.scene or bench.scene_path(a.tris)
 sc = rt.load_scene(path, width=a.width, height=a.height, samples=a.spp)
-r = rt.Renderer(flags=rt.FLAG_COUNTERS if a.counters else 0)
+r = rt.Renderer(flags=(rt.FLAG_COUNTERS if a.counters else 0) | (rt.FLAG_MEGAKERNEL if a.megakernel else 0))
 r.upload(sc)
 for i in range(a.steps):
     r.render(i * a.spp, (i + 1) * a.spp)
