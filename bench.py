@@ -252,12 +252,7 @@ def main():
     r.upload(scene)
     ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", local))
 
-    def accum_tensor():
-        p, n = r.accum_device_ptr()
-
-        class _W:
-            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (p, False), "version": 3, "strides": None}
-        return torch.as_tensor(_W(), device=torch.device("cuda", local))
+    from raytracing_course_hw_b200.dist import accum_tensor, reduce_to_rank0
 
     def step(i):
         # global sample indices: step i, rank `rank` (disjoint across ranks and steps)
@@ -286,8 +281,7 @@ def main():
     if dist:
         # ONE reduce of the radiance buffers per frame (north_star), on the render stream
         with torch.cuda.stream(ext):
-            t = accum_tensor()
-            dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
+            reduce_to_rank0(accum_tensor(r, torch.device("cuda", local)))
     e1.record(ext)
     r.synchronize()
     torch.cuda.synchronize()

@@ -56,6 +56,7 @@ def build_cuda(force=False, verbose=False):
         return out
     common = [NVCC] + ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INC, "-I", cu,
                               "-ccbin", GXX, "-diag-suppress", "550"]
+    common += os.environ.get("B200RT_NVCC_DEFS", "").split()      # development sweeps only
     if verbose:
         common += ["-Xptxas", "-v"]
     objs = []

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -41,6 +42,7 @@ struct b200rt_ctx {
     size_t wave_capacity = 0;
     int num_sms = 0;
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0};
+    int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T, wf_blocks_cap = 0;
     b200rt_stats stats{};
     bool timing_pending = false;
 };
@@ -383,8 +385,10 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         int dev = ctx->device, nb = 0;
         CK(cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, dev));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_extend<COUNT>, 128, 0));
+        if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
         ctx->blocks_extend[COUNT] = std::max(1, nb) * ctx->num_sms;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_light<COUNT>, 128, 0));
+        if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
         ctx->blocks_light[COUNT] = std::max(1, nb) * ctx->num_sms;
     }
     const WaveBuffers &wb = ctx->wave;
@@ -400,11 +404,11 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
             int *c = wb.ctr + 4 * b;
-            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters);
+            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
             const bool last = b == rp.ray_depth - 1;
             if (lights && !last) {
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t_light);
                 (*launches) += 3;
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
@@ -454,6 +458,11 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     ctx->device = dev;
     ctx->seed = opt ? opt->seed : 0;
     ctx->flags = opt ? opt->flags : 0;
+    // tuning knobs (development only; defaults are the measured optimum)
+    if (const char *e = getenv("B200RT_WF_BATCH")) ctx->wf_batch = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_WF_LEAF_T")) ctx->wf_leaf_t = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_WF_LEAF_T_LIGHT")) ctx->wf_leaf_t_light = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));
     cudaError_t e;
     if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||

@@ -20,8 +20,17 @@
 
 namespace b200rt {
 
-#define B200RT_WF_BATCH 8        /* traversal steps between refills */
-#define B200RT_WF_LEAF_T 6       /* lanes waiting at a leaf that trigger a leaf phase */
+#define B200RT_WF_BATCH 16       /* traversal steps between refills (sweep: profiles/r01_sweep_wf.log) */
+#define B200RT_WF_LEAF_T 8       /* lanes waiting at a leaf that trigger a leaf phase */
+#ifndef B200RT_EXT_MINB
+#define B200RT_EXT_MINB 1        /* min resident blocks per SM asked of ptxas for extend / light */
+#endif
+#ifndef B200RT_SHADE_MINB
+#define B200RT_SHADE_MINB 1
+#endif
+#ifndef B200RT_STACK_TNEAR
+#define B200RT_STACK_TNEAR 1     /* keep the entry distance with stacked nodes (prunes on pop) */
+#endif
 #define B200RT_WF_MISS 0x7FFFFFFFu
 #define B200RT_FULL 0xffffffffu
 
@@ -99,11 +108,16 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
 
 // ---- persistent closest-hit traversal ------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
-                                                 const int *__restrict__ n_in, int *cursor, DCounters *counters) {
+__global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
+                                                 const int *__restrict__ n_in, int *cursor, DCounters *counters,
+                                                 const int batch, const int leaf_t) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
+#if B200RT_STACK_TNEAR
     uint2 stack[B200RT_STACK];
+#else
+    uint32_t stack[B200RT_STACK];
+#endif
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
@@ -137,14 +151,14 @@ __global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const Wave
         }
         if (__ballot_sync(B200RT_FULL, active) == 0) break;
 
-        for (int it = 0; it < B200RT_WF_BATCH; it++) {
+        for (int it = 0; it < batch; it++) {
             const bool at_leaf = active && (cur & B200RT_LEAF);
             const bool at_inner = active && !(cur & B200RT_LEAF);
             const unsigned leaf_mask = __ballot_sync(B200RT_FULL, at_leaf);
             const unsigned inner_mask = __ballot_sync(B200RT_FULL, at_inner);
             if ((leaf_mask | inner_mask) == 0) break;
             bool pop = false;
-            if (inner_mask == 0 || __popc(leaf_mask) >= B200RT_WF_LEAF_T) {
+            if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) {
                 if (at_leaf) {
                     const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
                     for (uint32_t i = first; i < first + count; i++) {
@@ -174,7 +188,11 @@ __global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const Wave
                 const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
                 if (hl && hr) {
                     const bool left_first = tl <= tr;
+#if B200RT_STACK_TNEAR
                     if (sp < B200RT_STACK) stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
+#else
+                    if (sp < B200RT_STACK) stack[sp++] = left_first ? mr : ml;
+#endif
                     else overflow = true;
                     cur = left_first ? ml : mr;
                 } else if (hl) cur = ml;
@@ -184,10 +202,14 @@ __global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const Wave
             if (pop) {
                 // skip stacked subtrees that a closer hit has made irrelevant
                 bool got = false;
+#if B200RT_STACK_TNEAR
                 while (sp > 0) {
                     const uint2 e = stack[--sp];
                     if (__uint_as_float(e.y) <= tbest) { cur = e.x; got = true; break; }
                 }
+#else
+                if (sp > 0) { cur = stack[--sp]; got = true; }
+#endif
                 if (!got) {
                     const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
                     wb.hit[p] = make_float4(tbest, hu, hv, __uint_as_float(bits));
@@ -213,7 +235,7 @@ __global__ void __launch_bounds__(128) wf_extend(const DGltfScene sc, const Wave
 
 // ---- shade --------------------------------------------------------------------------------------
 template <bool HW8, bool COUNT>
-__global__ void __launch_bounds__(128) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
+__global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int bounce,
                                                 const float *__restrict__ lut_srgb_g, DCounters *counters) {
     __shared__ float lut_srgb[256];
@@ -272,8 +294,9 @@ __global__ void __launch_bounds__(128) wf_shade(const DGltfScene sc, const WaveB
 
 // ---- persistent light-pdf traversal + end of the bounce ---------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
-                                                const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters) {
+__global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
+                                                const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters,
+                                                const int batch, const int leaf_t) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
     uint32_t stack[B200RT_STACK];
@@ -319,14 +342,14 @@ __global__ void __launch_bounds__(128) wf_light(const DGltfScene sc, const WaveB
         }
         if (__ballot_sync(B200RT_FULL, active) == 0) break;
 
-        for (int it = 0; it < B200RT_WF_BATCH; it++) {
+        for (int it = 0; it < batch; it++) {
             const bool at_leaf = active && (cur & B200RT_LEAF);
             const bool at_inner = active && !(cur & B200RT_LEAF);
             const unsigned leaf_mask = __ballot_sync(B200RT_FULL, at_leaf);
             const unsigned inner_mask = __ballot_sync(B200RT_FULL, at_inner);
             if ((leaf_mask | inner_mask) == 0) break;
             bool pop = false;
-            if (inner_mask == 0 || __popc(leaf_mask) >= B200RT_WF_LEAF_T) {
+            if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) {
                 if (at_leaf) {
                     const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
                     for (uint32_t i = first; i < first + count; i++) {
