@@ -171,6 +171,10 @@ typedef struct b200rt_stats {
     uint64_t shaded_hits;      /* hits that fetched a shading record (COUNTERS only)    */
     uint64_t tex_lookups;      /* bilinear texture lookups           (COUNTERS only)    */
     int32_t  launches;         /* kernels launched by the last render+resolve           */
+    int32_t  extend_launches;  /* wavefront: closest-hit traversal launches in the last render */
+    double   extend_ms;        /* wavefront: summed device time of those launches (CUDA events) */
+    double   shade_ms;         /* wavefront: summed device time of the shade launches   */
+    double   light_ms;         /* wavefront: summed device time of the light-pdf launches */
 } b200rt_stats;
 
 /* Replaces: constructing the render state inside main() (hw8/src/main.cpp:8-15). */

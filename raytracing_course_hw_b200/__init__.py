@@ -34,7 +34,9 @@ class Stats(ctypes.Structure):
     _fields_ = [("kernel_ms", ctypes.c_double), ("paths", ctypes.c_uint64), ("rays", ctypes.c_uint64),
                 ("light_queries", ctypes.c_uint64), ("node_tests", ctypes.c_uint64), ("tri_tests", ctypes.c_uint64),
                 ("light_node_tests", ctypes.c_uint64), ("light_tri_tests", ctypes.c_uint64),
-                ("shaded_hits", ctypes.c_uint64), ("tex_lookups", ctypes.c_uint64), ("launches", ctypes.c_int32)]
+                ("shaded_hits", ctypes.c_uint64), ("tex_lookups", ctypes.c_uint64), ("launches", ctypes.c_int32),
+                ("extend_launches", ctypes.c_int32), ("extend_ms", ctypes.c_double), ("shade_ms", ctypes.c_double),
+                ("light_ms", ctypes.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

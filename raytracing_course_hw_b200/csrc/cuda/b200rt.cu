@@ -45,6 +45,22 @@ struct b200rt_ctx {
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T, wf_blocks_cap = 0;
     b200rt_stats stats{};
     bool timing_pending = false;
+    // per-stage timing of the wavefront: event pairs (begin, end, stage) recorded around launches
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<int> ev_stage;      // stage of pair i (0 extend, 1 shade, 2 light)
+    size_t ev_used = 0;
+    bool stage_timing = true;
+
+    int stamp(bool begin, int stage) {
+        if (!stage_timing) return 0;
+        if (ev_used == ev_pool.size()) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) return -1;
+            ev_pool.push_back(e);
+        }
+        if (begin) ev_stage.push_back(stage);
+        return cudaEventRecord(ev_pool[ev_used++], stream) == cudaSuccess ? 0 : -1;
+    }
 };
 
 namespace {
@@ -404,15 +420,23 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
             int *c = wb.ctr + 4 * b;
+            ctx->stamp(true, 0);
             wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
+            ctx->stamp(false, 0);
             const bool last = b == rp.ray_depth - 1;
             if (lights && !last) {
+                ctx->stamp(true, 1);
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
+                ctx->stamp(false, 1);
+                ctx->stamp(true, 2);
                 wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t_light);
+                ctx->stamp(false, 2);
                 (*launches) += 3;
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
+                ctx->stamp(true, 1);
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, b, ctx->lut_srgb, ctx->counters);
+                ctx->stamp(false, 1);
                 (*launches) += 2;
             }
             std::swap(qa, qb);
@@ -462,6 +486,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_BATCH")) ctx->wf_batch = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T")) ctx->wf_leaf_t = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T_LIGHT")) ctx->wf_leaf_t_light = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_STAGE_TIMING")) ctx->stage_timing = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));
     cudaError_t e;
     if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -482,6 +507,7 @@ void b200rt_destroy(b200rt_ctx *ctx) {
     free_wave(ctx);
     cudaFree(ctx->total); cudaFree(ctx->slabs); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->counters);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -566,6 +592,8 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
     rp.seed = ctx->seed; rp.accum = ctx->slabs; rp.counters = ctx->counters;
 
     CK(cudaMemsetAsync(ctx->counters, 0, sizeof(DCounters), ctx->stream));
+    ctx->ev_used = 0;
+    ctx->ev_stage.clear();
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     int launches = 0;
     if (d.mode == B200RT_MODE_HW1) { CK(launch_cast(rp.cam, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
@@ -686,6 +714,14 @@ int b200rt_get_stats(b200rt_ctx *ctx, b200rt_stats *out) {
         ctx->stats.node_tests = c.node_tests; ctx->stats.tri_tests = c.tri_tests;
         ctx->stats.light_node_tests = c.light_node_tests; ctx->stats.light_tri_tests = c.light_tri_tests;
         ctx->stats.shaded_hits = c.shaded_hits; ctx->stats.tex_lookups = c.tex_lookups;
+        for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
+            float t = 0;
+            CK(cudaEventElapsedTime(&t, ctx->ev_pool[i], ctx->ev_pool[i + 1]));
+            const int stage = ctx->ev_stage[i / 2];
+            if (stage == 0) { ctx->stats.extend_ms += t; ctx->stats.extend_launches++; }
+            else if (stage == 1) ctx->stats.shade_ms += t;
+            else ctx->stats.light_ms += t;
+        }
         ctx->timing_pending = false;
         if (c.stack_overflow) return fail(ctx, B200RT_ERR_STACK, "traversal stack overflow during render");
     }
