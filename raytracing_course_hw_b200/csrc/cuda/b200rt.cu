@@ -94,11 +94,16 @@ void release_scene(b200rt_ctx *c) {
     c->has_scene = false;
 }
 
-// ---- BVH flattening: reference-shaped 40-byte nodes -> 32-byte sibling-pair layout ------------
+// ---- BVH flattening: reference-shaped 40-byte nodes -> 32-byte quantised sibling-pair records ------
+struct FBox { float mn[3], mx[3]; };
+
 struct Flattener {
-    const b200rt_bvh_node *ref;
-    const b200rt_triangle *tris;
-    std::vector<DNode> out;
+    const b200rt_bvh_node *ref = nullptr;
+    const b200rt_triangle *tris = nullptr;
+    std::vector<DPair> out;
+    DQuant q{};
+    FBox root_box{};
+    uint32_t root_word = B200RT_LEAF;
     int max_depth = 0;
 
     static void tri_box(const b200rt_triangle &t, float *mn, float *mx) {
@@ -107,55 +112,80 @@ struct Flattener {
             mx[a] = std::max(t.p[0][a], std::max(t.p[1][a], t.p[2][a]));
         }
     }
-    void range_box(uint32_t first, uint32_t last, DNode &n) const {
-        float mn[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
+    FBox range_box(uint32_t first, uint32_t last) const {
+        FBox b{};
         for (uint32_t i = first; i < last; i++) {
-            float a[3], b[3];
-            tri_box(tris[i], a, b);
+            float a[3], c[3];
+            tri_box(tris[i], a, c);
             for (int k = 0; k < 3; k++) {
-                mn[k] = i == first ? a[k] : std::min(mn[k], a[k]);
-                mx[k] = i == first ? b[k] : std::max(mx[k], b[k]);
+                b.mn[k] = i == first ? a[k] : std::min(b.mn[k], a[k]);
+                b.mx[k] = i == first ? c[k] : std::max(b.mx[k], c[k]);
             }
         }
-        n.mnx = mn[0]; n.mny = mn[1]; n.mnz = mn[2]; n.mxx = mx[0]; n.mxy = mx[1]; n.mxz = mx[2];
+        return b;
     }
-    void ref_box(uint32_t r, DNode &n) const {
-        n.mnx = ref[r].aabb_min[0]; n.mny = ref[r].aabb_min[1]; n.mnz = ref[r].aabb_min[2];
-        n.mxx = ref[r].aabb_max[0]; n.mxy = ref[r].aabb_max[1]; n.mxz = ref[r].aabb_max[2];
+    FBox ref_box(uint32_t r) const {
+        FBox b;
+        for (int k = 0; k < 3; k++) { b.mn[k] = ref[r].aabb_min[k]; b.mx[k] = ref[r].aabb_max[k]; }
+        return b;
+    }
+    // Conservative 16-bit quantisation: lo rounded down, hi rounded up (the float rounding of the
+    // ray's own transform to grid space is covered by the guard band B200RT_QEPS in slab_q).
+    void quantise(const FBox &b, uint16_t *lo, uint16_t *hi) const {
+        for (int k = 0; k < 3; k++) {
+            double l = std::floor(((double)b.mn[k] - q.base[k]) / q.scale[k]);
+            double h = std::ceil(((double)b.mx[k] - q.base[k]) / q.scale[k]);
+            lo[k] = (uint16_t)std::min(65535.0, std::max(0.0, l));
+            hi[k] = (uint16_t)std::min(65535.0, std::max(0.0, h));
+        }
+    }
+    static DPair pack(const uint16_t *l0, const uint16_t *h0, const uint16_t *l1, const uint16_t *h1, uint32_t m0, uint32_t m1) {
+        DPair p;
+        p.a.x = l0[0] | ((uint32_t)l0[1] << 16); p.a.y = l0[2] | ((uint32_t)h0[0] << 16); p.a.z = h0[1] | ((uint32_t)h0[2] << 16);
+        p.a.w = l1[0] | ((uint32_t)l1[1] << 16); p.b.x = l1[2] | ((uint32_t)h1[0] << 16); p.b.y = h1[1] | ((uint32_t)h1[2] << 16);
+        p.b.z = m0; p.b.w = m1;
+        return p;
     }
     // A node is either a reference node (r >= 0) or a virtual range produced by splitting a
     // leaf with more than 15 triangles (closest-hit results are tree-independent).
     uint32_t emit(long r, uint32_t first, uint32_t last, int depth) {
         max_depth = std::max(max_depth, depth);
-        bool leaf = r < 0 || ref[r].left == 0;
+        const bool leaf = r < 0 || ref[r].left == 0;
         if (r >= 0) { first = ref[r].first; last = ref[r].last; }
         if (leaf && last - first <= 15) return B200RT_LEAF | ((last - first) << 27) | first;
-        uint32_t pair = (uint32_t)out.size();
-        out.resize(out.size() + 2);
-        DNode l{}, rr{};
+        const uint32_t idx = (uint32_t)out.size();
+        out.emplace_back();
+        FBox bl, br;
+        uint32_t ml, mr;
         if (leaf) {
-            uint32_t mid = first + (last - first) / 2;
-            range_box(first, mid, l); range_box(mid, last, rr);
-            uint32_t ml = emit(-1, first, mid, depth + 1), mr = emit(-1, mid, last, depth + 1);
-            l.a = ml; rr.a = mr;
+            const uint32_t mid = first + (last - first) / 2;
+            bl = range_box(first, mid); br = range_box(mid, last);
+            ml = emit(-1, first, mid, depth + 1); mr = emit(-1, mid, last, depth + 1);
         } else {
-            ref_box(ref[r].left, l); ref_box(ref[r].right, rr);
-            uint32_t ml = emit(ref[r].left, 0, 0, depth + 1), mr = emit(ref[r].right, 0, 0, depth + 1);
-            l.a = ml; rr.a = mr;
+            bl = ref_box(ref[r].left); br = ref_box(ref[r].right);
+            ml = emit(ref[r].left, 0, 0, depth + 1); mr = emit(ref[r].right, 0, 0, depth + 1);
         }
-        l.b = (l.a & B200RT_LEAF) ? ((l.a >> 27) & 15u) : 0;
-        rr.b = (rr.a & B200RT_LEAF) ? ((rr.a >> 27) & 15u) : 0;
-        out[pair] = l; out[pair + 1] = rr;
-        return pair;
+        uint16_t l0[3], h0[3], l1[3], h1[3];
+        quantise(bl, l0, h0); quantise(br, l1, h1);
+        out[idx] = pack(l0, h0, l1, h1, ml, mr);
+        return idx;
     }
     void run(const b200rt_bvh_node *nodes, int n_nodes, int root, const b200rt_triangle *t, int n_tris) {
         ref = nodes; tris = t;
-        out.assign(2, DNode{});
-        if (n_nodes <= 0 || n_tris <= 0) { out[0].a = B200RT_LEAF; return; }
-        ref_box((uint32_t)root, out[0]);
-        uint32_t meta = emit(root, 0, 0, 1);
-        out[0].a = meta;
-        out[0].b = (meta & B200RT_LEAF) ? ((meta >> 27) & 15u) : 0;
+        out.clear();
+        for (int k = 0; k < 3; k++) { q.base[k] = 0.f; q.scale[k] = 1.f; q.inv_scale[k] = 1.f; root_box.mn[k] = root_box.mx[k] = 0.f; }
+        root_word = B200RT_LEAF;
+        if (n_nodes <= 0 || n_tris <= 0) { out.emplace_back(); return; }
+        root_box = ref_box((uint32_t)root);
+        for (int k = 0; k < 3; k++) {
+            const double ext = (double)root_box.mx[k] - (double)root_box.mn[k];
+            const double sc = ext > 0 ? ext / 65533.0 : 1.0;       // leaves room for the +-1 slack
+            q.scale[k] = (float)sc;
+            q.base[k] = (float)((double)root_box.mn[k] - sc);
+            q.inv_scale[k] = (float)(1.0 / (double)q.scale[k]);
+        }
+        root_word = emit(root, 0, 0, 1);
+        if (out.empty()) out.emplace_back();
     }
 };
 
@@ -259,6 +289,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     fl.run(s->nodes, s->n_nodes, s->root, s->tris, s->n_tris);
     if (fl.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "scene BVH deeper than the traversal stack");
     if ((rc = dev_upload(ctx, fl.out, &g.nodes))) return rc;
+    g.root = fl.root_word; g.q = fl.q;
 
     std::vector<DTri> tris((size_t)s->n_tris);
     std::vector<DShade> shade((size_t)s->n_tris);
@@ -283,6 +314,8 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     ll.run(s->light_nodes, s->n_light_nodes, 0, s->light_tris, s->n_light_tris);
     if (ll.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "light BVH deeper than the traversal stack");
     if ((rc = dev_upload(ctx, ll.out, &g.light_nodes))) return rc;
+    g.light_root = ll.root_word; g.lq = ll.q;
+    for (int k = 0; k < 3; k++) { g.light_min[k] = ll.root_box.mn[k]; g.light_max[k] = ll.root_box.mx[k]; }
     std::vector<DTri> ltris((size_t)s->n_light_tris);
     std::vector<DLightNormals> lnorm((size_t)s->n_light_tris);
     for (int i = 0; i < s->n_light_tris; i++) {

@@ -6,15 +6,24 @@
 
 namespace b200rt {
 
-// 32-byte BVH node, fetched as two float4.  Siblings are stored ADJACENT (left = 2p, right = 2p+1,
-// 64-byte aligned), so one traversal step reads both child boxes with four float4 __ldg.
-//   internal: a = index of the left child (even), b = 0
-//   leaf    : a = first triangle,               b = triangle count (> 0)
-struct DNode {
-    float mnx, mny, mnz; uint32_t a;
-    float mxx, mxy, mxz; uint32_t b;
+// 32-byte BVH record = ONE traversal step: the boxes of BOTH children of an inner node, quantised
+// to 16 bits per coordinate on the grid spanned by the tree's root box (conservatively: lo rounded
+// down, hi rounded up, one extra grid unit of slack), plus the two child words.  Fetched as two
+// 128-bit __ldg.  (ncu on the first wavefront showed the L1/TEX pipe at 91 % of peak with 64-byte
+// float pairs -- profiles/r01_ncu_full_summary.json -- so the record was halved.)
+//   a.x = lo0.x | lo0.y << 16   a.y = lo0.z | hi0.x << 16   a.z = hi0.y | hi0.z << 16
+//   a.w = lo1.x | lo1.y << 16   b.x = lo1.z | hi1.x << 16   b.y = hi1.y | hi1.z << 16
+//   b.z = child word 0          b.w = child word 1
+// child word: inner node -> index of its own record; leaf -> B200RT_LEAF | count << 27 | first triangle
+struct DPair {
+    uint4 a, b;
 };
-static_assert(sizeof(DNode) == 32, "DNode must be 32 bytes");
+static_assert(sizeof(DPair) == 32, "DPair must be 32 bytes");
+
+// Quantisation grid of one tree: world = base + q * scale.
+struct DQuant {
+    float base[3], scale[3], inv_scale[3];
+};
 
 // 48-byte Moeller-Trumbore record: v0 = data3 (barycentric origin), e1 = data - data3 (weight u),
 // e2 = data2 - data3 (weight v)  (hw8/src/primitives.cpp:86-88).
@@ -55,15 +64,17 @@ struct DCamera {
 };
 
 struct DGltfScene {
-    const DNode *nodes;
+    const DPair *nodes;
     const DTri *tris;
     const DShade *shade;
-    const DNode *light_nodes;
+    const DPair *light_nodes;
     const DTri *light_tris;
     const DLightNormals *light_normals;
     const DMaterial *materials;
     int32_t n_light_tris;
-    int32_t root_is_leaf, light_root_is_leaf;
+    uint32_t root, light_root;   // child word of each tree's root
+    DQuant q, lq;                // quantisation grids of the scene BVH and the light BVH
+    float light_min[3], light_max[3];   // root box of the light BVH (a real filter, unlike the scene's)
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
     float bg[3];
     cudaTextureObject_t env;     // 0 = absent

@@ -28,35 +28,86 @@ struct ThreadCounters {
     unsigned paths, rays, light_queries, node_tests, tri_tests, light_node_tests, light_tri_tests, shaded, tex, overflow;
 };
 
-__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const V3 o, const V3 inv, float tbest, float &tnear) {
-    float x0 = (lo.x - o.x) * inv.x, x1 = (hi.x - o.x) * inv.x;
-    float y0 = (lo.y - o.y) * inv.y, y1 = (hi.y - o.y) * inv.y;
-    float z0 = (lo.z - o.z) * inv.z, z1 = (hi.z - o.z) * inv.z;
-    float tmin = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
-    float tmax = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+// Slab test.  AABB::intersect accepts t1 <= t2 && t2 >= 0 (hw8/src/primitives.cpp:38); tbest adds the
+// distance prune of BVH::intersect_ (bvh.h:118) -- conservative (<=) so ties still descend.
+__device__ __forceinline__ bool slab6(float lx, float ly, float lz, float hx, float hy, float hz,
+                                      const V3 o, const V3 inv, float tbest, float &tnear) {
+    const float x0 = (lx - o.x) * inv.x, x1 = (hx - o.x) * inv.x;
+    const float y0 = (ly - o.y) * inv.y, y1 = (hy - o.y) * inv.y;
+    const float z0 = (lz - o.z) * inv.z, z1 = (hz - o.z) * inv.z;
+    const float tmin = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+    const float tmax = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
     tnear = tmin;
-    // AABB::intersect accepts t1 <= t2 && t2 >= 0 (hw8/src/primitives.cpp:38); tbest adds the
-    // distance prune of BVH::intersect_ (bvh.h:118) -- conservative (<=) so ties still descend.
     return tmin <= tmax && tmax >= 0.f && tmin <= tbest;
+}
+
+// A ray expressed on the 16-bit grid of a tree.  With o' = (o - base) / scale and inv' = scale / d the
+// ray parameter of a grid plane q is t = q * inv' - o' * inv' (same t as in world space): one FFMA.
+// The near/far plane of each axis is picked by the sign of d, and the constant terms carry a
+// +-B200RT_QEPS grid-unit guard band that absorbs the float rounding of o' (boxes stay conservative).
+// Zero direction components get a huge finite reciprocal so that no 0 * inf NaN can hide a miss.
+#define B200RT_QEPS 0.02f
+struct QRay {
+    V3 inv;        // scale / d
+    V3 bn, bf;     // -(o' * inv') -/+ eps * |inv'|
+    bool nx, ny, nz;   // direction component negative: near plane is `hi`
+};
+__device__ __forceinline__ float safe_rcp(float d) {
+    const float r = 1.f / d;
+    return fabsf(r) < 1e30f ? r : copysignf(1e30f, d);
+}
+__device__ __forceinline__ QRay make_qray(const DQuant &q, const V3 o, const V3 d) {
+    QRay r;
+    const V3 oq = mk((o.x - q.base[0]) * q.inv_scale[0], (o.y - q.base[1]) * q.inv_scale[1], (o.z - q.base[2]) * q.inv_scale[2]);
+    r.inv = mk(q.scale[0] * safe_rcp(d.x), q.scale[1] * safe_rcp(d.y), q.scale[2] * safe_rcp(d.z));
+    const V3 c = mk(-oq.x * r.inv.x, -oq.y * r.inv.y, -oq.z * r.inv.z);
+    const V3 g = mk(B200RT_QEPS * fabsf(r.inv.x), B200RT_QEPS * fabsf(r.inv.y), B200RT_QEPS * fabsf(r.inv.z));
+    r.bn = c - g; r.bf = c + g;
+    r.nx = d.x < 0.f; r.ny = d.y < 0.f; r.nz = d.z < 0.f;
+    return r;
+}
+// u16 -> float without the conversion pipe: splice the 16 bits into the mantissa of 2^23.
+__device__ __forceinline__ float q16lo(uint32_t x) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8388608.f; }
+__device__ __forceinline__ float q16hi(uint32_t x) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8388608.f; }
+
+// AABB::intersect accepts t1 <= t2 && t2 >= 0 (hw8/src/primitives.cpp:38); tbest adds the distance
+// prune of BVH::intersect_ (bvh.h:118) -- conservative (<=) so ties still descend.
+__device__ __forceinline__ bool slab_q(float lx, float ly, float lz, float hx, float hy, float hz,
+                                       const QRay &r, float tbest, float &tnear) {
+    const float tx0 = fmaf(r.nx ? hx : lx, r.inv.x, r.bn.x), tx1 = fmaf(r.nx ? lx : hx, r.inv.x, r.bf.x);
+    const float ty0 = fmaf(r.ny ? hy : ly, r.inv.y, r.bn.y), ty1 = fmaf(r.ny ? ly : hy, r.inv.y, r.bf.y);
+    const float tz0 = fmaf(r.nz ? hz : lz, r.inv.z, r.bn.z), tz1 = fmaf(r.nz ? lz : hz, r.inv.z, r.bf.z);
+    const float tmin = fmaxf(fmaxf(tx0, ty0), tz0);
+    const float tmax = fminf(fminf(tx1, ty1), tz1);
+    tnear = tmin;
+    return tmin <= tmax && tmax >= 0.f && tmin <= tbest;
+}
+
+// One traversal step: fetch a 32-byte record (two 128-bit loads) and test both child boxes.
+__device__ __forceinline__ void pair_test(const DPair *nodes, uint32_t idx, const QRay &r, float tbest,
+                                          bool &hl, bool &hr, float &tl, float &tr, uint32_t &ml, uint32_t &mr) {
+    const uint4 *p = reinterpret_cast<const uint4 *>(nodes + idx);
+    const uint4 a = __ldg(p), b = __ldg(p + 1);
+    hl = slab_q(q16lo(a.x), q16hi(a.x), q16lo(a.y), q16hi(a.y), q16lo(a.z), q16hi(a.z), r, tbest, tl);
+    hr = slab_q(q16lo(a.w), q16hi(a.w), q16lo(b.x), q16hi(b.x), q16lo(b.y), q16hi(b.y), r, tbest, tr);
+    ml = b.z; mr = b.w;
 }
 
 // Closest hit over the scene BVH.  t in (0, 1e4) like intersectPlaneAndRay (primitives.cpp:20).
 template <bool COUNT>
 __device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, const V3 d, TraceHit &h, ThreadCounters &tc) {
     h.t = B200RT_TMAX; h.tri = -1; h.u = h.v = 0.f; h.det = 0.f;
-    const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    const QRay qr = make_qray(sc.q, o, d);
     uint32_t stack[B200RT_STACK];
     int sp = 0;
-    uint32_t cur = __ldg(&sc.nodes[0].a);   // root meta: its box is not tested (always the scene)
+    uint32_t cur = sc.root;   // the root's own box is not tested (it is the whole scene)
     while (true) {
         if (!(cur & B200RT_LEAF)) {
-            const float4 *p = reinterpret_cast<const float4 *>(sc.nodes + cur);
-            const float4 l0 = __ldg(p), l1 = __ldg(p + 1), r0 = __ldg(p + 2), r1 = __ldg(p + 3);
             float tl, tr;
-            const bool hl = slab(l0, l1, o, inv, h.t, tl);
-            const bool hr = slab(r0, r1, o, inv, h.t, tr);
+            bool hl, hr;
+            uint32_t ml, mr;
+            pair_test(sc.nodes, cur, qr, h.t, hl, hr, tl, tr, ml, mr);
             if (COUNT) tc.node_tests += 2;
-            const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
             if (hl && hr) {
                 const bool left_first = tl <= tr;
                 if (sp < B200RT_STACK) stack[sp++] = left_first ? mr : ml; else tc.overflow = 1;
@@ -92,26 +143,24 @@ __device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, 
 // (x, d) pierces contributes pointProb * |x-y|^2 / |d . n_y|; NO distance pruning.
 template <bool COUNT>
 __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o, const V3 d, ThreadCounters &tc) {
-    const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
     uint32_t stack[B200RT_STACK];
     int sp = 0;
     float total = 0.f;
     {   // unlike the scene root, the light root's box IS a real filter
-        const float4 *p = reinterpret_cast<const float4 *>(sc.light_nodes);
         float tn;
         if (COUNT) tc.light_node_tests++;
-        if (!slab(__ldg(p), __ldg(p + 1), o, inv, INFINITY, tn)) return 0.f;
+        if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
+                   o, mk(1.f / d.x, 1.f / d.y, 1.f / d.z), INFINITY, tn)) return 0.f;
     }
-    uint32_t cur = __ldg(&sc.light_nodes[0].a);
+    const QRay qr = make_qray(sc.lq, o, d);
+    uint32_t cur = sc.light_root;
     while (true) {
         if (!(cur & B200RT_LEAF)) {
-            const float4 *p = reinterpret_cast<const float4 *>(sc.light_nodes + cur);
-            const float4 l0 = __ldg(p), l1 = __ldg(p + 1), r0 = __ldg(p + 2), r1 = __ldg(p + 3);
             float tl, tr;
-            const bool hl = slab(l0, l1, o, inv, INFINITY, tl);
-            const bool hr = slab(r0, r1, o, inv, INFINITY, tr);
+            bool hl, hr;
+            uint32_t ml, mr;
+            pair_test(sc.light_nodes, cur, qr, INFINITY, hl, hr, tl, tr, ml, mr);
             if (COUNT) tc.light_node_tests += 2;
-            const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
             if (hl && hr) {
                 if (sp < B200RT_STACK) stack[sp++] = mr; else tc.overflow = 1;
                 cur = ml;

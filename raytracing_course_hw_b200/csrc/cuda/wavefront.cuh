@@ -23,13 +23,13 @@ namespace b200rt {
 #define B200RT_WF_BATCH 16       /* traversal steps between refills (sweep: profiles/r01_sweep_wf.log) */
 #define B200RT_WF_LEAF_T 8       /* lanes waiting at a leaf that trigger a leaf phase */
 #ifndef B200RT_EXT_MINB
-#define B200RT_EXT_MINB 1        /* min resident blocks per SM asked of ptxas for extend / light */
+#define B200RT_EXT_MINB 9        /* min resident blocks per SM asked of ptxas for extend / light (sweep: profiles/r01_sweep_quantised_nodes.log) */
 #endif
 #ifndef B200RT_SHADE_MINB
 #define B200RT_SHADE_MINB 1
 #endif
 #ifndef B200RT_STACK_TNEAR
-#define B200RT_STACK_TNEAR 1     /* keep the entry distance with stacked nodes (prunes on pop) */
+#define B200RT_STACK_TNEAR 0     /* 1 = keep the entry distance with stacked nodes (prunes on pop; slower: doubles stack traffic) */
 #endif
 #define B200RT_WF_MISS 0x7FFFFFFFu
 #define B200RT_FULL 0xffffffffu
@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
-    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 0);
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
+    QRay qr = {};
     float tbest = 0.f, hu = 0.f, hv = 0.f, hdet = 0.f;
     uint32_t htri = B200RT_WF_MISS, cur = 0;
     unsigned node_tests = 0, tri_tests = 0;
@@ -140,10 +141,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                     p = q_in[idx];
                     const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
-                    inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+                    qr = make_qray(sc.q, o, d);
                     tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
                     sp = 0;
-                    cur = __ldg(&sc.nodes[0].a);
+                    cur = sc.root;
                     active = true;
                 }
             }
@@ -179,13 +180,11 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                     pop = true;
                 }
             } else if (at_inner) {
-                const float4 *pn = reinterpret_cast<const float4 *>(sc.nodes + cur);
-                const float4 l0 = __ldg(pn), l1 = __ldg(pn + 1), r0 = __ldg(pn + 2), r1 = __ldg(pn + 3);
                 float tl, tr;
-                const bool hl = slab(l0, l1, o, inv, tbest, tl);
-                const bool hr = slab(r0, r1, o, inv, tbest, tr);
+                bool hl, hr;
+                uint32_t ml, mr;
+                pair_test(sc.nodes, cur, qr, tbest, hl, hr, tl, tr, ml, mr);
                 if (COUNT) node_tests += 2;
-                const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
                 if (hl && hr) {
                     const bool left_first = tl <= tr;
 #if B200RT_STACK_TNEAR
@@ -303,7 +302,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
-    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 0);
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
+    QRay qr = {};
     float total = 0.f;
     uint32_t cur = 0;
     unsigned node_tests = 0, tri_tests = 0;
@@ -327,14 +327,14 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     p = q_in[idx];
                     const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
-                    inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+                    qr = make_qray(sc.lq, o, d);
                     total = 0.f; sp = 0;
                     active = true;
                     // the light root's box is a real filter (unlike the scene root)
-                    const float4 *pr = reinterpret_cast<const float4 *>(sc.light_nodes);
                     float tn;
                     if (COUNT) node_tests++;
-                    if (slab(__ldg(pr), __ldg(pr + 1), o, inv, INFINITY, tn)) cur = __ldg(&sc.light_nodes[0].a);
+                    if (slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
+                              o, mk(1.f / d.x, 1.f / d.y, 1.f / d.z), INFINITY, tn)) cur = sc.light_root;
                     else cur = B200RT_LEAF;      // empty leaf: finishes on the next leaf phase
                 }
             }
@@ -383,13 +383,11 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     pop = true;
                 }
             } else if (at_inner) {
-                const float4 *pn = reinterpret_cast<const float4 *>(sc.light_nodes + cur);
-                const float4 l0 = __ldg(pn), l1 = __ldg(pn + 1), r0 = __ldg(pn + 2), r1 = __ldg(pn + 3);
                 float tl, tr;
-                const bool hl = slab(l0, l1, o, inv, INFINITY, tl);
-                const bool hr = slab(r0, r1, o, inv, INFINITY, tr);
+                bool hl, hr;
+                uint32_t ml, mr;
+                pair_test(sc.light_nodes, cur, qr, INFINITY, hl, hr, tl, tr, ml, mr);
                 if (COUNT) node_tests += 2;
-                const uint32_t ml = __float_as_uint(l0.w), mr = __float_as_uint(r0.w);
                 if (hl && hr) {
                     if (sp < B200RT_STACK) stack[sp++] = mr; else overflow = true;
                     cur = ml;
