@@ -12,7 +12,7 @@
 #include "b200rt.h"
 #include "device_scene.h"
 #include "gltf_kernel.cuh"
-#include "wavefront.cuh"
+#include "wavefront_trace.cuh"
 
 using namespace b200rt;
 
@@ -41,7 +41,8 @@ struct b200rt_ctx {
     WaveBuffers wave{};
     size_t wave_capacity = 0;
     int num_sms = 0;
-    int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0};
+    int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
+    bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T, wf_blocks_cap = 0;
     b200rt_stats stats{};
     bool timing_pending = false;
@@ -129,20 +130,20 @@ struct Flattener {
         for (int k = 0; k < 3; k++) { b.mn[k] = ref[r].aabb_min[k]; b.mx[k] = ref[r].aabb_max[k]; }
         return b;
     }
-    // Conservative 16-bit quantisation: lo rounded down, hi rounded up (the float rounding of the
+    // Conservative quantisation: lo rounded down, hi rounded up (the float rounding of the
     // ray's own transform to grid space is covered by the guard band B200RT_QEPS in slab_q).
     void quantise(const FBox &b, uint16_t *lo, uint16_t *hi) const {
         for (int k = 0; k < 3; k++) {
             double l = std::floor(((double)b.mn[k] - q.base[k]) / q.scale[k]);
             double h = std::ceil(((double)b.mx[k] - q.base[k]) / q.scale[k]);
-            lo[k] = (uint16_t)std::min(65535.0, std::max(0.0, l));
-            hi[k] = (uint16_t)std::min(65535.0, std::max(0.0, h));
+            lo[k] = (uint16_t)std::min((double)B200RT_QMAX, std::max(0.0, l));
+            hi[k] = (uint16_t)std::min((double)B200RT_QMAX, std::max(0.0, h));
         }
     }
     static DPair pack(const uint16_t *l0, const uint16_t *h0, const uint16_t *l1, const uint16_t *h1, uint32_t m0, uint32_t m1) {
         DPair p;
-        p.a.x = l0[0] | ((uint32_t)l0[1] << 16); p.a.y = l0[2] | ((uint32_t)h0[0] << 16); p.a.z = h0[1] | ((uint32_t)h0[2] << 16);
-        p.a.w = l1[0] | ((uint32_t)l1[1] << 16); p.b.x = l1[2] | ((uint32_t)h1[0] << 16); p.b.y = h1[1] | ((uint32_t)h1[2] << 16);
+        p.a.x = l0[0] | ((uint32_t)h0[0] << 16); p.a.y = l0[1] | ((uint32_t)h0[1] << 16); p.a.z = l0[2] | ((uint32_t)h0[2] << 16);
+        p.a.w = l1[0] | ((uint32_t)h1[0] << 16); p.b.x = l1[1] | ((uint32_t)h1[1] << 16); p.b.y = l1[2] | ((uint32_t)h1[2] << 16);
         p.b.z = m0; p.b.w = m1;
         return p;
     }
@@ -179,7 +180,7 @@ struct Flattener {
         root_box = ref_box((uint32_t)root);
         for (int k = 0; k < 3; k++) {
             const double ext = (double)root_box.mx[k] - (double)root_box.mn[k];
-            const double sc = ext > 0 ? ext / 65533.0 : 1.0;       // leaves room for the +-1 slack
+            const double sc = ext > 0 ? ext / (B200RT_QMAX - 2.0) : 1.0;   // one spare grid unit on each side
             q.scale[k] = (float)sc;
             q.base[k] = (float)((double)root_box.mn[k] - sc);
             q.inv_scale[k] = (float)(1.0 / (double)q.scale[k]);
@@ -439,6 +440,9 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_light<COUNT>, 128, 0));
         if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
         ctx->blocks_light[COUNT] = std::max(1, nb) * ctx->num_sms;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_trace<COUNT>, 128, 0));
+        if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
+        ctx->blocks_trace[COUNT] = std::max(1, nb) * ctx->num_sms;
     }
     const WaveBuffers &wb = ctx->wave;
     const bool lights = ctx->gs.n_light_tris > 0;
@@ -453,6 +457,19 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
             int *c = wb.ctr + 4 * b;
+            if (ctx->wf_fused && lights) {
+                // fused scheduling: the traversal of bounce b also answers the light-pdf query of
+                // bounce b-1 for the same ray and applies its weight / clamp (wavefront_trace.cuh)
+                ctx->stamp(true, 0);
+                wf_trace<COUNT><<<ctx->blocks_trace[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, b > 0 ? 1 : 0);
+                ctx->stamp(false, 0);
+                ctx->stamp(true, 1);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, c + 4, b, ctx->lut_srgb, ctx->counters);
+                ctx->stamp(false, 1);
+                (*launches) += 2;
+                std::swap(qa, qb);
+                continue;
+            }
             ctx->stamp(true, 0);
             wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
             ctx->stamp(false, 0);
@@ -520,6 +537,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_LEAF_T")) ctx->wf_leaf_t = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T_LIGHT")) ctx->wf_leaf_t_light = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_STAGE_TIMING")) ctx->stage_timing = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));
     cudaError_t e;
     if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -757,6 +775,18 @@ int b200rt_get_stats(b200rt_ctx *ctx, b200rt_stats *out) {
         }
         ctx->timing_pending = false;
         if (c.stack_overflow) return fail(ctx, B200RT_ERR_STACK, "traversal stack overflow during render");
+#ifdef B200RT_DBG_PHASE
+        {
+            unsigned long long ph[8];
+            if (cudaMemcpyFromSymbol(ph, g_phase, sizeof(ph)) == cudaSuccess) {
+                fprintf(stderr, "[phase] inner steps %llu lanes %.2f (waiting at leaf %.2f, idle %.2f) | leaf steps %llu lanes %.2f | refills %llu\n",
+                        ph[0], ph[0] ? (double)ph[1] / ph[0] : 0., ph[0] ? (double)ph[6] / ph[0] : 0., ph[0] ? (double)ph[7] / ph[0] : 0.,
+                        ph[2], ph[2] ? (double)ph[3] / ph[2] : 0., ph[5]);
+                memset(ph, 0, sizeof(ph));
+                cudaMemcpyToSymbol(g_phase, ph, sizeof(ph));
+            }
+        }
+#endif
     }
     *out = ctx->stats;
     return B200RT_OK;

@@ -7,14 +7,19 @@
 namespace b200rt {
 
 // 32-byte BVH record = ONE traversal step: the boxes of BOTH children of an inner node, quantised
-// to 16 bits per coordinate on the grid spanned by the tree's root box (conservatively: lo rounded
-// down, hi rounded up, one extra grid unit of slack), plus the two child words.  Fetched as two
-// 128-bit __ldg.  (ncu on the first wavefront showed the L1/TEX pipe at 91 % of peak with 64-byte
-// float pairs -- profiles/r01_ncu_full_summary.json -- so the record was halved.)
-//   a.x = lo0.x | lo0.y << 16   a.y = lo0.z | hi0.x << 16   a.z = hi0.y | hi0.z << 16
-//   a.w = lo1.x | lo1.y << 16   b.x = lo1.z | hi1.x << 16   b.y = hi1.y | hi1.z << 16
+// to B200RT_QBITS (15) bits per coordinate on the grid spanned by the tree's root box (conservatively:
+// lo rounded down, hi rounded up), plus the two child words.  Fetched with one 256-bit read-only load.
+// (ncu on the first wavefront showed the L1/TEX pipe at 91 % of peak with 64-byte float pairs --
+// profiles/r01_ncu_full_summary.json -- so the record was halved.)  lo and hi of one axis share a
+// word so that a per-ray PRMT selector picks the near / far plane without a select instruction:
+//   a.x = lo0.x | hi0.x << 16   a.y = lo0.y | hi0.y << 16   a.z = lo0.z | hi0.z << 16
+//   a.w = lo1.x | hi1.x << 16   b.x = lo1.y | hi1.y << 16   b.y = lo1.z | hi1.z << 16
 //   b.z = child word 0          b.w = child word 1
 // child word: inner node -> index of its own record; leaf -> B200RT_LEAF | count << 27 | first triangle
+#ifndef B200RT_QBITS
+#define B200RT_QBITS 15      /* 15: the PRMT result is used as a float directly (no FADD); 16: finer grid, one more op per plane */
+#endif
+#define B200RT_QMAX ((1 << B200RT_QBITS) - 1)
 struct DPair {
     uint4 a, b;
 };

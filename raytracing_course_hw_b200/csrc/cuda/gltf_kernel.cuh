@@ -46,50 +46,90 @@ __device__ __forceinline__ bool slab6(float lx, float ly, float lz, float hx, fl
 // The near/far plane of each axis is picked by the sign of d, and the constant terms carry a
 // +-B200RT_QEPS grid-unit guard band that absorbs the float rounding of o' (boxes stay conservative).
 // Zero direction components get a huge finite reciprocal so that no 0 * inf NaN can hide a miss.
-#define B200RT_QEPS 0.02f
+#ifndef B200RT_QEPS
+#define B200RT_QEPS 0.03f
+#endif
 struct QRay {
-    V3 inv;        // scale / d
-    V3 bn, bf;     // -(o' * inv') -/+ eps * |inv'|
-    bool nx, ny, nz;   // direction component negative: near plane is `hi`
+    V3 inv;        // scale / d (times 2^16 for the 15-bit encoding)
+    V3 bn, bf;     // -(o' * inv') -/+ eps * |inv'|  (minus the encoding offset)
+    uint32_t sx, sy, sz;   // PRMT selector of the NEAR plane of each axis (far = near ^ B200RT_SEL_FLIP)
 };
 __device__ __forceinline__ float safe_rcp(float d) {
     const float r = 1.f / d;
     return fabsf(r) < 1e30f ? r : copysignf(1e30f, d);
 }
+// u16 -> float without the conversion pipe: one PRMT splices a half of the record word into a float.
+//   16-bit grid: into the low mantissa of 2^23 -> 2^23 + q, then one FADD removes the 2^23.
+//   15-bit grid: into bits 8..22 under the exponent of 0.5 -> m = 0.5 + q * 2^-16, used AS IS: the plane
+//   parameter q * inv + b becomes m * (2^16 inv) + (b - 2^15 inv), one FFMA; the rounding of the folded
+//   constant moves a plane by < 2^-9 grid units (covered by B200RT_QEPS).
+#if B200RT_QBITS == 15
+#define B200RT_SEL_LO 0x7104u
+#define B200RT_SEL_HI 0x7324u
+#define B200RT_SEL_FLIP 0x0220u
+__device__ __forceinline__ float q16(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x3F000000u, sel)); }
+#else
+#define B200RT_SEL_LO 0x7610u
+#define B200RT_SEL_HI 0x7632u
+#define B200RT_SEL_FLIP 0x0022u
+__device__ __forceinline__ float q16(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.f; }
+#endif
 __device__ __forceinline__ QRay make_qray(const DQuant &q, const V3 o, const V3 d) {
     QRay r;
     const V3 oq = mk((o.x - q.base[0]) * q.inv_scale[0], (o.y - q.base[1]) * q.inv_scale[1], (o.z - q.base[2]) * q.inv_scale[2]);
-    r.inv = mk(q.scale[0] * safe_rcp(d.x), q.scale[1] * safe_rcp(d.y), q.scale[2] * safe_rcp(d.z));
-    const V3 c = mk(-oq.x * r.inv.x, -oq.y * r.inv.y, -oq.z * r.inv.z);
-    const V3 g = mk(B200RT_QEPS * fabsf(r.inv.x), B200RT_QEPS * fabsf(r.inv.y), B200RT_QEPS * fabsf(r.inv.z));
+    const V3 ig = mk(q.scale[0] * safe_rcp(d.x), q.scale[1] * safe_rcp(d.y), q.scale[2] * safe_rcp(d.z));
+    const V3 c = mk(-oq.x * ig.x, -oq.y * ig.y, -oq.z * ig.z);
+    const V3 g = mk(B200RT_QEPS * fabsf(ig.x), B200RT_QEPS * fabsf(ig.y), B200RT_QEPS * fabsf(ig.z));
     r.bn = c - g; r.bf = c + g;
-    r.nx = d.x < 0.f; r.ny = d.y < 0.f; r.nz = d.z < 0.f;
+#if B200RT_QBITS == 15
+    r.inv = 65536.f * ig;
+    const V3 off = 32768.f * ig;
+    r.bn = r.bn - off; r.bf = r.bf - off;
+#else
+    r.inv = ig;
+#endif
+    r.sx = d.x < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
+    r.sy = d.y < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
+    r.sz = d.z < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
     return r;
 }
-// u16 -> float without the conversion pipe: splice the 16 bits into the mantissa of 2^23.
-__device__ __forceinline__ float q16lo(uint32_t x) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8388608.f; }
-__device__ __forceinline__ float q16hi(uint32_t x) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8388608.f; }
 
 // AABB::intersect accepts t1 <= t2 && t2 >= 0 (hw8/src/primitives.cpp:38); tbest adds the distance
 // prune of BVH::intersect_ (bvh.h:118) -- conservative (<=) so ties still descend.
-__device__ __forceinline__ bool slab_q(float lx, float ly, float lz, float hx, float hy, float hz,
-                                       const QRay &r, float tbest, float &tnear) {
-    const float tx0 = fmaf(r.nx ? hx : lx, r.inv.x, r.bn.x), tx1 = fmaf(r.nx ? lx : hx, r.inv.x, r.bf.x);
-    const float ty0 = fmaf(r.ny ? hy : ly, r.inv.y, r.bn.y), ty1 = fmaf(r.ny ? ly : hy, r.inv.y, r.bf.y);
-    const float tz0 = fmaf(r.nz ? hz : lz, r.inv.z, r.bn.z), tz1 = fmaf(r.nz ? lz : hz, r.inv.z, r.bf.z);
+__device__ __forceinline__ bool slab_q(uint32_t wx, uint32_t wy, uint32_t wz, const QRay &r, float tbest, float &tnear) {
+    const float tx0 = fmaf(q16(wx, r.sx), r.inv.x, r.bn.x), tx1 = fmaf(q16(wx, r.sx ^ B200RT_SEL_FLIP), r.inv.x, r.bf.x);
+    const float ty0 = fmaf(q16(wy, r.sy), r.inv.y, r.bn.y), ty1 = fmaf(q16(wy, r.sy ^ B200RT_SEL_FLIP), r.inv.y, r.bf.y);
+    const float tz0 = fmaf(q16(wz, r.sz), r.inv.z, r.bn.z), tz1 = fmaf(q16(wz, r.sz ^ B200RT_SEL_FLIP), r.inv.z, r.bf.z);
     const float tmin = fmaxf(fmaxf(tx0, ty0), tz0);
     const float tmax = fminf(fminf(tx1, ty1), tz1);
     tnear = tmin;
     return tmin <= tmax && tmax >= 0.f && tmin <= tbest;
 }
 
-// One traversal step: fetch a 32-byte record (two 128-bit loads) and test both child boxes.
+// sm_100 256-bit read-only load: one 32-byte record = one L1 request per lane.  ncu on the two-LDG.128
+// version showed the traversal bound by L1 tag throughput (one wavefront per distinct sector per
+// instruction, profiles/r01_ncu_full_summary.json); a single LDG.E.256 halves the wavefronts.
+#ifndef B200RT_LDG256
+#define B200RT_LDG256 1
+#endif
+__device__ __forceinline__ void ldg32B(const void *ptr, uint4 &a, uint4 &b) {
+#if B200RT_LDG256
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(ptr));
+#else
+    const uint4 *p = reinterpret_cast<const uint4 *>(ptr);
+    a = __ldg(p); b = __ldg(p + 1);
+#endif
+}
+
+// One traversal step: fetch a 32-byte record and test both child boxes.
 __device__ __forceinline__ void pair_test(const DPair *nodes, uint32_t idx, const QRay &r, float tbest,
                                           bool &hl, bool &hr, float &tl, float &tr, uint32_t &ml, uint32_t &mr) {
-    const uint4 *p = reinterpret_cast<const uint4 *>(nodes + idx);
-    const uint4 a = __ldg(p), b = __ldg(p + 1);
-    hl = slab_q(q16lo(a.x), q16hi(a.x), q16lo(a.y), q16hi(a.y), q16lo(a.z), q16hi(a.z), r, tbest, tl);
-    hr = slab_q(q16lo(a.w), q16hi(a.w), q16lo(b.x), q16hi(b.x), q16lo(b.y), q16hi(b.y), r, tbest, tr);
+    uint4 a, b;
+    ldg32B(nodes + idx, a, b);
+    hl = slab_q(a.x, a.y, a.z, r, tbest, tl);
+    hr = slab_q(a.w, b.x, b.y, r, tbest, tr);
     ml = b.z; mr = b.w;
 }
 

@@ -32,6 +32,7 @@ namespace b200rt {
 #define B200RT_STACK_TNEAR 0     /* 1 = keep the entry distance with stacked nodes (prunes on pop; slower: doubles stack traffic) */
 #endif
 #define B200RT_WF_MISS 0x7FFFFFFFu
+#define B200RT_WF_DEAD 0x7FFFFFFEu   /* written by wf_trace: the firefly clamp ended this path */
 #define B200RT_FULL 0xffffffffu
 
 struct WaveBuffers {
@@ -106,6 +107,16 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
     if (lane == 0 && made) atomicAdd(&counters->paths, (unsigned long long)made);
 }
 
+#ifdef B200RT_DBG_PHASE
+// development instrumentation (off by default): warp-level phase statistics of wf_extend
+//   0 inner warp-steps, 1 lanes at inner in those, 2 leaf warp-steps, 3 lanes at leaf in those,
+//   4 triangle iterations (warp), 5 refills, 6 lanes waiting at a leaf during inner steps, 7 idle lanes during inner steps
+__device__ unsigned long long g_phase[8];
+#define DBG_PHASE(i, v) do { if (lane == 0) dbg[i] += (v); } while (0)
+#else
+#define DBG_PHASE(i, v) do { } while (0)
+#endif
+
 // ---- persistent closest-hit traversal ------------------------------------------------------------
 template <bool COUNT>
 __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
@@ -126,7 +137,9 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
     float tbest = 0.f, hu = 0.f, hv = 0.f, hdet = 0.f;
     uint32_t htri = B200RT_WF_MISS, cur = 0;
     unsigned node_tests = 0, tri_tests = 0;
-    bool overflow = false;
+#ifdef B200RT_DBG_PHASE
+    unsigned long long dbg[8] = {};
+#endif
 
     while (true) {
         const unsigned idle = __ballot_sync(B200RT_FULL, !active);
@@ -149,6 +162,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                 }
             }
             if (base + n_idle >= n) exhausted = true;
+            DBG_PHASE(5, 1);
         }
         if (__ballot_sync(B200RT_FULL, active) == 0) break;
 
@@ -158,6 +172,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             const unsigned leaf_mask = __ballot_sync(B200RT_FULL, at_leaf);
             const unsigned inner_mask = __ballot_sync(B200RT_FULL, at_inner);
             if ((leaf_mask | inner_mask) == 0) break;
+#ifdef B200RT_DBG_PHASE
+            if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) { DBG_PHASE(2, 1); DBG_PHASE(3, __popc(leaf_mask)); }
+            else { DBG_PHASE(0, 1); DBG_PHASE(1, __popc(inner_mask)); DBG_PHASE(6, __popc(leaf_mask)); DBG_PHASE(7, 32 - __popc(leaf_mask | inner_mask)); }
+#endif
             bool pop = false;
             if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) {
                 if (at_leaf) {
@@ -187,12 +205,12 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                 if (COUNT) node_tests += 2;
                 if (hl && hr) {
                     const bool left_first = tl <= tr;
+                    // no bound check: b200rt_upload_scene rejects trees deeper than B200RT_STACK
 #if B200RT_STACK_TNEAR
-                    if (sp < B200RT_STACK) stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
+                    stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
 #else
-                    if (sp < B200RT_STACK) stack[sp++] = left_first ? mr : ml;
+                    stack[sp++] = left_first ? mr : ml;
 #endif
-                    else overflow = true;
                     cur = left_first ? ml : mr;
                 } else if (hl) cur = ml;
                 else if (hr) cur = mr;
@@ -218,6 +236,9 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&counters->rays, (unsigned long long)n);
+#ifdef B200RT_DBG_PHASE
+    if (lane == 0) for (int k = 0; k < 8; k++) if (dbg[k]) atomicAdd(&g_phase[k], dbg[k]);
+#endif
     if (COUNT) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
@@ -229,7 +250,6 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             atomicAdd(&counters->tri_tests, (unsigned long long)tri_tests);
         }
     }
-    if (overflow) atomicAdd(&counters->stack_overflow, 1ull);
 }
 
 // ---- shade --------------------------------------------------------------------------------------
@@ -262,7 +282,9 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfSc
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
             const uint32_t bits = __float_as_uint(h.w);
-            if (bits == B200RT_WF_MISS) {
+            if (bits == B200RT_WF_DEAD) {
+                // clamped at the end of the previous bounce (wf_trace): nothing more is added
+            } else if (bits == B200RT_WF_MISS) {
                 V3 bg = ld3(sc.bg);
                 if (HW8 && sc.env) {
                     const float tx = 0.5f + 0.5f * atan2f(d.z, d.x) * 0.318309886183791f;
@@ -307,7 +329,6 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
     float total = 0.f;
     uint32_t cur = 0;
     unsigned node_tests = 0, tri_tests = 0;
-    bool overflow = false;
     bool push_pending = false;
     int push_p = 0;
 
@@ -389,7 +410,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                 pair_test(sc.light_nodes, cur, qr, INFINITY, hl, hr, tl, tr, ml, mr);
                 if (COUNT) node_tests += 2;
                 if (hl && hr) {
-                    if (sp < B200RT_STACK) stack[sp++] = mr; else overflow = true;
+                    stack[sp++] = mr;
                     cur = ml;
                 } else if (hl) cur = ml;
                 else if (hr) cur = mr;
@@ -423,7 +444,6 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
             atomicAdd(&counters->light_tri_tests, (unsigned long long)tri_tests);
         }
     }
-    if (overflow) atomicAdd(&counters->stack_overflow, 1ull);
 }
 
 // total[pixel] += sum of the wave's samples, in sample order (deterministic)
