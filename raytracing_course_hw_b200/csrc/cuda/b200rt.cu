@@ -16,6 +16,8 @@
 
 using namespace b200rt;
 
+#define B200RT_PIPE 3
+
 struct b200rt_ctx {
     int device = 0;
     uint32_t seed = 0;
@@ -38,10 +40,16 @@ struct b200rt_ctx {
     int32_t *ids = nullptr;
     DCounters *counters = nullptr;
     // wavefront pipeline state (glTF modes)
-    WaveBuffers wave{};
+    // Up to B200RT_PIPE waves are in flight, each on its own stream with its own buffers (pipe 0 uses
+    // the main stream): while one wave's persistent traversal drains, the next wave's kernels fill the SMs.
+    WaveBuffers wave[B200RT_PIPE]{};
+    cudaStream_t pipe_stream[B200RT_PIPE] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[B200RT_PIPE] = {}, ev_acc[B200RT_PIPE] = {};
+    int wf_pipe = 2;
     size_t wave_capacity = 0;
     int num_sms = 0;
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
+    long long wf_wave_paths = 4ll << 20;
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T, wf_blocks_cap = 0;
     b200rt_stats stats{};
@@ -52,7 +60,7 @@ struct b200rt_ctx {
     size_t ev_used = 0;
     bool stage_timing = true;
 
-    int stamp(bool begin, int stage) {
+    int stamp(bool begin, int stage, cudaStream_t on) {
         if (!stage_timing) return 0;
         if (ev_used == ev_pool.size()) {
             cudaEvent_t e;
@@ -60,7 +68,7 @@ struct b200rt_ctx {
             ev_pool.push_back(e);
         }
         if (begin) ev_stage.push_back(stage);
-        return cudaEventRecord(ev_pool[ev_used++], stream) == cudaSuccess ? 0 : -1;
+        return cudaEventRecord(ev_pool[ev_used++], on) == cudaSuccess ? 0 : -1;
     }
 };
 
@@ -391,10 +399,12 @@ int ensure_buffers(b200rt_ctx *ctx, int w, int h, int n_slabs) {
 }
 
 void free_wave(b200rt_ctx *c) {
-    cudaFree(c->wave.ray_o); cudaFree(c->wave.ray_d); cudaFree(c->wave.thr); cudaFree(c->wave.rad);
-    cudaFree(c->wave.bsdf); cudaFree(c->wave.hit); cudaFree(c->wave.ctr);
-    for (int i = 0; i < 3; i++) cudaFree(c->wave.queue[i]);
-    c->wave = WaveBuffers{};
+    for (WaveBuffers &w : c->wave) {
+        cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.thr); cudaFree(w.rad);
+        cudaFree(w.bsdf); cudaFree(w.hit); cudaFree(w.ctr);
+        for (int i = 0; i < 3; i++) cudaFree(w.queue[i]);
+        w = WaveBuffers{};
+    }
     c->wave_capacity = 0;
 }
 
@@ -402,15 +412,17 @@ void free_wave(b200rt_ctx *c) {
 int ensure_wave(b200rt_ctx *ctx, size_t slots) {
     if (slots <= ctx->wave_capacity) return B200RT_OK;
     free_wave(ctx);
-    WaveBuffers &w = ctx->wave;
-    CK(cudaMalloc(&w.ray_o, slots * sizeof(float4)));
-    CK(cudaMalloc(&w.ray_d, slots * sizeof(float4)));
-    CK(cudaMalloc(&w.thr, slots * sizeof(float4)));
-    CK(cudaMalloc(&w.rad, slots * sizeof(float4)));
-    CK(cudaMalloc(&w.bsdf, slots * sizeof(float4)));
-    CK(cudaMalloc(&w.hit, slots * sizeof(float4)));
-    for (int i = 0; i < 3; i++) CK(cudaMalloc(&w.queue[i], slots * sizeof(int)));
-    CK(cudaMalloc(&w.ctr, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int)));
+    for (int k = 0; k < ctx->wf_pipe; k++) {
+        WaveBuffers &w = ctx->wave[k];
+        CK(cudaMalloc(&w.ray_o, slots * sizeof(float4)));
+        CK(cudaMalloc(&w.ray_d, slots * sizeof(float4)));
+        CK(cudaMalloc(&w.thr, slots * sizeof(float4)));
+        CK(cudaMalloc(&w.rad, slots * sizeof(float4)));
+        CK(cudaMalloc(&w.bsdf, slots * sizeof(float4)));
+        CK(cudaMalloc(&w.hit, slots * sizeof(float4)));
+        for (int i = 0; i < 3; i++) CK(cudaMalloc(&w.queue[i], slots * sizeof(int)));
+        CK(cudaMalloc(&w.ctr, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int)));
+    }
     ctx->wave_capacity = slots;
     return B200RT_OK;
 }
@@ -426,8 +438,15 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
     wp.seed = rp.seed;
     const long long per = (long long)wp.n_tiles * 32;
     const int total = rp.spp_end - rp.spp_begin;
-    long long s_w = std::max<long long>(1, (4ll << 20) / per);           // aim at >= 4 M paths per wave
-    s_w = std::min<long long>({s_w, (long long)total, std::max<long long>(1, (16ll << 20) / per)});
+    long long s_w = std::max<long long>(1, ctx->wf_wave_paths / per);    // aim at >= wf_wave_paths paths per wave
+    s_w = std::min<long long>({s_w, (long long)total, std::max<long long>(1, (32ll << 20) / per)});
+    // enough waves to keep the pipes busy, as long as a wave stays above 2 M paths
+    if (ctx->wf_pipe > 1 && (total + s_w - 1) / s_w < ctx->wf_pipe) {
+        const long long split = (total + ctx->wf_pipe - 1) / ctx->wf_pipe;
+        if (split * per >= (2ll << 20)) s_w = split;
+    }
+    const int n_waves = (int)((total + s_w - 1) / s_w);
+    const int n_pipe = std::max(1, std::min(ctx->wf_pipe, n_waves));
     int rc = ensure_wave(ctx, (size_t)(per * s_w));
     if (rc) return rc;
     if (rp.ray_depth > B200RT_MAX_DEPTH) return fail(ctx, B200RT_ERR_UNSUPPORTED, "ray depth above 64");
@@ -444,11 +463,18 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
         ctx->blocks_trace[COUNT] = std::max(1, nb) * ctx->num_sms;
     }
-    const WaveBuffers &wb = ctx->wave;
     const bool lights = ctx->gs.n_light_tris > 0;
     const int flat_blocks = ctx->num_sms * 16;
-    cudaStream_t st = ctx->stream;
-    for (int s0 = rp.spp_begin; s0 < rp.spp_end; s0 += (int)s_w) {
+    ctx->pipe_stream[0] = ctx->stream;
+    if (n_pipe > 1) {      // fork: the side streams start after everything already queued on the main stream
+        CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+        for (int k = 1; k < n_pipe; k++) CK(cudaStreamWaitEvent(ctx->pipe_stream[k], ctx->ev_fork, 0));
+    }
+    int wave = 0;
+    for (int s0 = rp.spp_begin; s0 < rp.spp_end; s0 += (int)s_w, wave++) {
+        const int k = wave % n_pipe;
+        const WaveBuffers &wb = ctx->wave[k];
+        cudaStream_t st = ctx->pipe_stream[k];
         wp.s_begin = s0;
         wp.s_count = std::min<int>((int)s_w, rp.spp_end - s0);
         CK(cudaMemsetAsync(wb.ctr, 0, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int), st));
@@ -460,40 +486,47 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             if (ctx->wf_fused && lights) {
                 // fused scheduling: the traversal of bounce b also answers the light-pdf query of
                 // bounce b-1 for the same ray and applies its weight / clamp (wavefront_trace.cuh)
-                ctx->stamp(true, 0);
+                ctx->stamp(true, 0, st);
                 wf_trace<COUNT><<<ctx->blocks_trace[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, b > 0 ? 1 : 0);
-                ctx->stamp(false, 0);
-                ctx->stamp(true, 1);
+                ctx->stamp(false, 0, st);
+                ctx->stamp(true, 1, st);
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, c + 4, b, ctx->lut_srgb, ctx->counters);
-                ctx->stamp(false, 1);
+                ctx->stamp(false, 1, st);
                 (*launches) += 2;
                 std::swap(qa, qb);
                 continue;
             }
-            ctx->stamp(true, 0);
+            ctx->stamp(true, 0, st);
             wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
-            ctx->stamp(false, 0);
+            ctx->stamp(false, 0, st);
             const bool last = b == rp.ray_depth - 1;
             if (lights && !last) {
-                ctx->stamp(true, 1);
+                ctx->stamp(true, 1, st);
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
-                ctx->stamp(false, 1);
-                ctx->stamp(true, 2);
+                ctx->stamp(false, 1, st);
+                ctx->stamp(true, 2, st);
                 wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t_light);
-                ctx->stamp(false, 2);
+                ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
-                ctx->stamp(true, 1);
+                ctx->stamp(true, 1, st);
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, b, ctx->lut_srgb, ctx->counters);
-                ctx->stamp(false, 1);
+                ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }
             std::swap(qa, qb);
         }
+        // total[] is summed wave after wave in sample order, whatever stream a wave ran on
+        if (n_pipe > 1 && wave > 0) CK(cudaStreamWaitEvent(st, ctx->ev_acc[(wave - 1) % n_pipe], 0));
         wf_accumulate<<<(unsigned)((per + 255) / 256), 256, 0, st>>>(wp, wb, ctx->total);
+        if (n_pipe > 1) CK(cudaEventRecord(ctx->ev_acc[k], st));
         (*launches)++;
         CK(cudaGetLastError());
+    }
+    for (int k = 1; k < n_pipe; k++) {     // join
+        CK(cudaEventRecord(ctx->ev_join[k], ctx->pipe_stream[k]));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[k], 0));
     }
     return B200RT_OK;
 }
@@ -537,14 +570,25 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_LEAF_T")) ctx->wf_leaf_t = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T_LIGHT")) ctx->wf_leaf_t_light = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_STAGE_TIMING")) ctx->stage_timing = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));
     cudaError_t e;
     if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->counters, sizeof(DCounters))) != cudaSuccess) {
+        (e = cudaMalloc(&ctx->counters, sizeof(DCounters))) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess) {
         delete ctx;
         return B200RT_ERR_CUDA;
+    }
+    for (int k = 0; k < B200RT_PIPE; k++) {
+        if ((k > 0 && (e = cudaStreamCreateWithFlags(&ctx->pipe_stream[k], cudaStreamNonBlocking)) != cudaSuccess) ||
+            (e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess ||
+            (e = cudaEventCreateWithFlags(&ctx->ev_acc[k], cudaEventDisableTiming)) != cudaSuccess) {
+            delete ctx;
+            return B200RT_ERR_CUDA;
+        }
     }
     *out = ctx;
     return B200RT_OK;
@@ -557,7 +601,11 @@ void b200rt_destroy(b200rt_ctx *ctx) {
     release_scene(ctx);
     free_wave(ctx);
     cudaFree(ctx->total); cudaFree(ctx->slabs); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->counters);
-    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev_fork);
+    for (int k = 0; k < B200RT_PIPE; k++) {
+        if (k > 0 && ctx->pipe_stream[k]) cudaStreamDestroy(ctx->pipe_stream[k]);
+        cudaEventDestroy(ctx->ev_join[k]); cudaEventDestroy(ctx->ev_acc[k]);
+    }
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
