@@ -158,6 +158,8 @@ typedef struct b200rt_options {
 
 #define B200RT_FLAG_COUNTERS   1  /* also count node fetches / triangle tests / texture lookups */
 #define B200RT_FLAG_MEGAKERNEL 2  /* glTF modes: one-kernel-per-path variant instead of the wavefront pipeline */
+#define B200RT_FLAG_SERIAL_WAVES 4 /* wavefront: one wave in flight on one stream (default: two waves overlap on two
+                                      streams); the per-stage times in b200rt_stats are then exclusive kernel times */
 
 typedef struct b200rt_stats {
     double   kernel_ms;        /* device time of the last b200rt_render (CUDA events) */

@@ -573,6 +573,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
+    if (ctx->flags & B200RT_FLAG_SERIAL_WAVES) ctx->wf_pipe = 1;
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));
     cudaError_t e;
     if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
