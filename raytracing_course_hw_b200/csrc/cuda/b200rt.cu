@@ -262,7 +262,8 @@ int make_texture(b200rt_ctx *ctx, const b200rt_image &img, cudaTextureObject_t *
     if (!img.rgb || img.width <= 0 || img.height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
     std::vector<uchar4> rgba((size_t)img.width * img.height);
     for (size_t i = 0; i < rgba.size(); i++) rgba[i] = make_uchar4(img.rgb[3 * i], img.rgb[3 * i + 1], img.rgb[3 * i + 2], 255);
-    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+    // texels are fetched as ONE 32-bit word (R | G << 8 | B << 16 | A << 24): one result register per tap
+    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned int>();
     cudaArray_t arr = nullptr;
     CK(cudaMallocArray(&arr, &fmt, (size_t)img.width, (size_t)img.height));
     ctx->arrays.push_back(arr);

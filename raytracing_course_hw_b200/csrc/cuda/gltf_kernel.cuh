@@ -249,22 +249,38 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
 // ---- textures (hw8/src/scene.cpp:9-35): wrap, bilinear on the integer texel grid, sRGB decode
 // per texel BEFORE blending.  Texels are RGBA8 in a point-sampled texture object; decode goes
 // through a 256-entry table (host-computed with the reference's powf) in shared memory.
-__device__ __forceinline__ V3 texel(cudaTextureObject_t tex, int ix, int iy, const float *lut) {
-    const uchar4 c = tex2D<uchar4>(tex, (float)ix + 0.5f, (float)iy + 0.5f);
-    return mk(lut[c.x], lut[c.y], lut[c.z]);
-}
-__device__ __forceinline__ V3 sample_texture(cudaTextureObject_t tex, int w, int h, float tx, float ty, const float *lut) {
+// A sample is split into a fetch (4 point taps issued back to back) and a resolve, so that the taps
+// of all textures of a material are in flight together: ncu attributed half of the shade stage's
+// stall samples to four serial fetch round trips executed by a handful of lanes.
+struct TexTaps {
+    uint32_t c11, c12, c21, c22;      // packed RGBA8 texels (one register per tap)
+    float dx, dy;
+};
+__device__ __forceinline__ void tex_fetch(cudaTextureObject_t tex, int w, int h, float tx, float ty, TexTaps &k) {
     tx -= floorf(tx);
     ty -= floorf(ty);
     tx *= (float)w;
     ty *= (float)h;
     int ix1 = (int)floorf(tx), iy1 = (int)floorf(ty);
-    const int ix2 = (ix1 + 1) % w, iy2 = (iy1 + 1) % h;
+    // (i + 1) % n for i in [0, n] without the integer division
+    int ix2 = ix1 + 1, iy2 = iy1 + 1;
+    if (ix2 >= w) ix2 -= w;
+    if (iy2 >= h) iy2 -= h;
     ix1 = min(ix1, w - 1); iy1 = min(iy1, h - 1);
-    const float dx = tx - (float)ix1, dy = ty - (float)iy1;
-    const V3 p11 = texel(tex, ix1, iy1, lut), p12 = texel(tex, ix1, iy2, lut);
-    const V3 p21 = texel(tex, ix2, iy1, lut), p22 = texel(tex, ix2, iy2, lut);
-    return (1.f - dx) * ((1.f - dy) * p11 + dy * p12) + dx * ((1.f - dy) * p21 + dy * p22);
+    k.dx = tx - (float)ix1; k.dy = ty - (float)iy1;
+    const float x1 = (float)ix1 + 0.5f, x2 = (float)ix2 + 0.5f, y1 = (float)iy1 + 0.5f, y2 = (float)iy2 + 0.5f;
+    k.c11 = tex2D<unsigned int>(tex, x1, y1); k.c12 = tex2D<unsigned int>(tex, x1, y2);
+    k.c21 = tex2D<unsigned int>(tex, x2, y1); k.c22 = tex2D<unsigned int>(tex, x2, y2);
+}
+__device__ __forceinline__ V3 texel(const uint32_t c, const float *lut) { return mk(lut[c & 255u], lut[(c >> 8) & 255u], lut[(c >> 16) & 255u]); }
+__device__ __forceinline__ V3 tex_resolve(const TexTaps &k, const float *lut) {
+    const V3 p11 = texel(k.c11, lut), p12 = texel(k.c12, lut), p21 = texel(k.c21, lut), p22 = texel(k.c22, lut);
+    return (1.f - k.dx) * ((1.f - k.dy) * p11 + k.dy * p12) + k.dx * ((1.f - k.dy) * p21 + k.dy * p22);
+}
+__device__ __forceinline__ V3 sample_texture(cudaTextureObject_t tex, int w, int h, float tx, float ty, const float *lut) {
+    TexTaps k;
+    tex_fetch(tex, w, h, tx, ty, k);
+    return tex_resolve(k, lut);
 }
 
 // ---- BRDF (hw8/src/include/material.h:11-65) ----
@@ -404,13 +420,18 @@ __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float 
         const float tx = s4.w + u * (s0.w - s4.w) + v * (s2.w - s4.w);
         const float ty = s5.w + u * (s1.w - s5.w) + v * (s3.w - s5.w);
         const cudaTextureObject_t tb = m->tex_base, te = m->tex_emissive, tm = m->tex_mr, tn = m->tex_normal;
-        if (tb) { color = sample_texture(tb, m->w_base, m->h_base, tx, ty, lut_srgb); if (COUNT) tc.tex++; }
-        if (te) { emission = emission * sample_texture(te, m->w_emissive, m->h_emissive, tx, ty, lut_srgb); if (COUNT) tc.tex++; }
+        TexTaps kb, ke, km, kn;
+        if (tb) tex_fetch(tb, m->w_base, m->h_base, tx, ty, kb);
+        if (te) tex_fetch(te, m->w_emissive, m->h_emissive, tx, ty, ke);
+        if (tm) tex_fetch(tm, m->w_mr, m->h_mr, tx, ty, km);
+        if (tn) tex_fetch(tn, m->w_normal, m->h_normal, tx, ty, kn);
+        if (tb) { color = tex_resolve(kb, lut_srgb); if (COUNT) tc.tex++; }
+        if (te) { emission = emission * tex_resolve(ke, lut_srgb); if (COUNT) tc.tex++; }
         V3 mr = mk(1, 1, 1);
-        if (tm) { mr = sample_texture(tm, m->w_mr, m->h_mr, tx, ty, lut_lin); if (COUNT) tc.tex++; }
+        if (tm) { mr = tex_resolve(km, lut_lin); if (COUNT) tc.tex++; }
         if (tn) {
             // applyNormalMaps (scene.cpp:37-52): X = tangent, Z = shading normal, Y = w * X.cross(Z) = w * (Z x X)
-            const V3 smp = sample_texture(tn, m->w_normal, m->h_normal, tx, ty, lut_lin);
+            const V3 smp = tex_resolve(kn, lut_lin);
             if (COUNT) tc.tex++;
             const V3 X = normalize(mk(s5.x + u * (s3.x - s5.x) + v * (s4.x - s5.x),
                                       s5.y + u * (s3.y - s5.y) + v * (s4.y - s5.y),

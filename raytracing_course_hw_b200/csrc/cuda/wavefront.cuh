@@ -26,7 +26,7 @@ namespace b200rt {
 #define B200RT_EXT_MINB 9        /* min resident blocks per SM asked of ptxas for extend / light (sweep: profiles/r01_sweep_quantised_nodes.log) */
 #endif
 #ifndef B200RT_SHADE_MINB
-#define B200RT_SHADE_MINB 1
+#define B200RT_SHADE_MINB 4
 #endif
 #ifndef B200RT_STACK_TNEAR
 #define B200RT_STACK_TNEAR 0     /* 1 = keep the entry distance with stacked nodes (prunes on pop; slower: doubles stack traffic) */
@@ -36,10 +36,10 @@ namespace b200rt {
 #define B200RT_FULL 0xffffffffu
 
 struct WaveBuffers {
-    float4 *ray_o;   // o.xyz, -
+    float4 *ray_o;   // o.xyz, pixel index (int bits): the Philox key of the path
     float4 *ray_d;   // d.xyz, |nd . n_s| of the bounce that produced this ray
     float4 *thr;     // throughput T.xyz, partial pdf (cosine + vndf)
-    float4 *rad;     // radiance L.xyz, -
+    float4 *rad;     // radiance L.xyz, global sample index (int bits): the Philox counter of the path
     float4 *bsdf;    // BRDF value of the pending bounce
     float4 *hit;     // t, u, v, bits: triangle index | inside << 31 (B200RT_WF_MISS = no hit)
     int *queue[3];
@@ -54,6 +54,27 @@ struct WaveParams {
     int32_t s_begin, s_count;     // global sample indices [s_begin, s_begin + s_count) in this wave
     uint32_t seed;
 };
+
+// Wave state accessors.  B200RT_STATE_CS=1 makes them evict-first (.cs) so that the 0.9 GB of state
+// streamed per stage does not push the scene out of L2; measured: extend and light gain 1 %, shade
+// loses 15 % (it re-reads what the previous stage just wrote), so the default is plain caching.
+#ifndef B200RT_STATE_CS
+#define B200RT_STATE_CS 0
+#endif
+__device__ __forceinline__ float4 ld_state(const float4 *p) {
+#if B200RT_STATE_CS
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+__device__ __forceinline__ void st_state(float4 *p, const float4 v) {
+#if B200RT_STATE_CS
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
 
 __device__ __forceinline__ bool slot_to_pixel(const WaveParams &wp, int slot, int &px, int &py, int &s_local) {
     const int per = wp.n_tiles * 32;
@@ -74,7 +95,7 @@ __device__ __forceinline__ void queue_push(int *queue, int *counter, bool want, 
     int base = 0;
     if (lane == leader) base = atomicAdd(counter, __popc(m));
     base = __shfl_sync(B200RT_FULL, base, leader);
-    if (want) queue[base + __popc(m & ((1u << lane) - 1u))] = value;
+    if (want) __stcs(queue + base + __popc(m & ((1u << lane) - 1u)), value);
 }
 
 __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters) {
@@ -94,10 +115,10 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             const float nx = wp.cam.tan_x * (2.f * fx / (float)wp.cam.width - 1.f);
             const float ny = wp.cam.tan_y * (2.f * fy / (float)wp.cam.height - 1.f);
             const V3 d = normalize(nx * cright - ny * cup + cfwd);
-            wb.ray_o[slot] = make_float4(cpos.x, cpos.y, cpos.z, 0.f);
-            wb.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.f);
-            wb.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-            wb.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            st_state(&wb.ray_o[slot], make_float4(cpos.x, cpos.y, cpos.z, __uint_as_float(pixel)));
+            st_state(&wb.ray_d[slot], make_float4(d.x, d.y, d.z, 0.f));
+            st_state(&wb.thr[slot], make_float4(1.f, 1.f, 1.f, 0.f));
+            st_state(&wb.rad[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl))));
             made++;
         }
         queue_push(wb.queue[0], wb.ctr + 0, ok, slot);
@@ -151,8 +172,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             if (!active) {
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
-                    p = q_in[idx];
-                    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+                    p = __ldcs(q_in + idx);
+                    const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.q, o, d);
                     tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
@@ -229,7 +250,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 #endif
                 if (!got) {
                     const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
-                    wb.hit[p] = make_float4(tbest, hu, hv, __uint_as_float(bits));
+                    st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
                     active = false;
                 }
             }
@@ -274,11 +295,11 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfSc
         bool cont = false;
         int p = 0;
         if (i < n) {
-            p = q_in[i];
-            const float4 h = wb.hit[p];
-            const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
-            const float4 th = wb.thr[p];
-            float4 ra = wb.rad[p];
+            p = __ldcs(q_in + i);
+            const float4 h = ld_state(&wb.hit[p]);
+            const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
+            const float4 th = ld_state(&wb.thr[p]);
+            float4 ra = ld_state(&wb.rad[p]);
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
             const uint32_t bits = __float_as_uint(h.w);
@@ -293,20 +314,19 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfSc
                 }
                 L = L + T * bg;
             } else {
-                int px, py, sl;
-                slot_to_pixel(wp, p, px, py, sl);
-                const uint4 rnd = philox4x32_10((uint32_t)(wp.s_begin + sl), 16u * (uint32_t)(bounce + 1), (uint32_t)(py * wp.cam.width + px), wp.seed);
+                // key = pixel, counter = (global sample index, block of this bounce); both ride in spare state lanes
+                const uint4 rnd = philox4x32_10(__float_as_uint(ra.w), 16u * (uint32_t)(bounce + 1), __float_as_uint(ro.w), wp.seed);
                 BounceOut bo;
                 cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, (int)(bits & 0x7FFFFFFFu), (bits >> 31) != 0, L, T, rnd, tc, bo);
                 if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
                 if (cont) {
-                    wb.ray_o[p] = make_float4(bo.xo.x, bo.xo.y, bo.xo.z, 0.f);
-                    wb.ray_d[p] = make_float4(bo.nd.x, bo.nd.y, bo.nd.z, bo.absdot);
-                    wb.thr[p] = make_float4(T.x, T.y, T.z, bo.pdf_partial);
-                    if (has_lights) wb.bsdf[p] = make_float4(bo.brdf.x, bo.brdf.y, bo.brdf.z, 0.f);
+                    st_state(&wb.ray_o[p], make_float4(bo.xo.x, bo.xo.y, bo.xo.z, ro.w));
+                    st_state(&wb.ray_d[p], make_float4(bo.nd.x, bo.nd.y, bo.nd.z, bo.absdot));
+                    st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, bo.pdf_partial));
+                    if (has_lights) st_state(&wb.bsdf[p], make_float4(bo.brdf.x, bo.brdf.y, bo.brdf.z, 0.f));
                 }
             }
-            wb.rad[p] = make_float4(L.x, L.y, L.z, 0.f);
+            st_state(&wb.rad[p], make_float4(L.x, L.y, L.z, ra.w));
         }
         queue_push(q_out, n_out, cont, p);
     }
@@ -345,8 +365,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
             if (!active) {
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
-                    p = q_in[idx];
-                    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+                    p = __ldcs(q_in + idx);
+                    const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.lq, o, d);
                     total = 0.f; sp = 0;
@@ -420,10 +440,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                 if (sp > 0) cur = stack[--sp];
                 else {
                     // end of the bounce: mean pdf, weight, firefly clamp (scene.cpp:158-163)
-                    const float4 th = wb.thr[p], bs = wb.bsdf[p];
+                    const float4 th = ld_state(&wb.thr[p]), bs = ld_state(&wb.bsdf[p]);
                     V3 T = mk(th.x, th.y, th.z);
-                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, wb.ray_d[p].w, total, sc.n_light_tris, T)) {
-                        wb.thr[p] = make_float4(T.x, T.y, T.z, 0.f);
+                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T)) {
+                        st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, 0.f));
                         push_pending = true;
                         push_p = p;
                     }
@@ -455,7 +475,7 @@ __global__ void wf_accumulate(const WaveParams wp, const WaveBuffers wb, float *
     if (!slot_to_pixel(wp, r, px, py, sl)) return;
     float3 acc = make_float3(0.f, 0.f, 0.f);
     for (int s = 0; s < wp.s_count; s++) {
-        const float4 v = wb.rad[(size_t)s * per + r];
+        const float4 v = ld_state(&wb.rad[(size_t)s * per + r]);
         acc.x += v.x; acc.y += v.y; acc.z += v.z;
     }
     float *dst = total + ((size_t)py * wp.cam.width + px) * 3;

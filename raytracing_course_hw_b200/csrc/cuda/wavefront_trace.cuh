@@ -40,8 +40,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_trace(const DGltfScen
             if (!active) {
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
-                    p = q_in[idx];
-                    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+                    p = __ldcs(q_in + idx);
+                    const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.q, o, d);
                     tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_trace(const DGltfScen
                 else if (!light) {
                     // scene query done
                     const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
-                    wb.hit[p] = make_float4(tbest, hu, hv, __uint_as_float(bits));
+                    st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
                     if (do_light) {
                         // same ray against the light BVH; its root box is a real filter
                         light = true; total = 0.f;
@@ -131,10 +131,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_trace(const DGltfScen
                     } else active = false;
                 } else {
                     // end of the previous bounce: mean pdf, weight, firefly clamp (scene.cpp:158-163)
-                    const float4 th = wb.thr[p], bs = wb.bsdf[p];
+                    const float4 th = ld_state(&wb.thr[p]), bs = ld_state(&wb.bsdf[p]);
                     V3 T = mk(th.x, th.y, th.z);
-                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, wb.ray_d[p].w, total, sc.n_light_tris, T))
-                        wb.thr[p] = make_float4(T.x, T.y, T.z, 0.f);
+                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T))
+                        st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, 0.f));
                     else {
                         wb.hit[p].w = __uint_as_float(B200RT_WF_DEAD);
                         dead++;
