@@ -13,6 +13,8 @@
 #include "device_scene.h"
 #include "gltf_kernel.cuh"
 #include "wavefront_trace.cuh"
+#include <chrono>
+#include <thread>
 
 using namespace b200rt;
 
@@ -29,9 +31,16 @@ struct b200rt_ctx {
     bool has_scene = false;
     b200rt_scene_desc desc{};     // scalar fields only (pointers are not retained)
     DGltfScene gs{};
-    std::vector<void *> allocations;
-    std::vector<cudaArray_t> arrays;
-    std::vector<cudaTextureObject_t> textures;
+    // Scene arena: ONE device allocation and ONE pinned staging buffer of the same layout hold every
+    // scene array (BVH records, triangle / shading records, light set, materials, sRGB table); an upload
+    // builds the records in the staging buffer on all host cores and moves them with one async copy.
+    // Both grow on demand and are reused by later uploads (no cudaMalloc / cudaFree per frame).
+    char *arena_dev = nullptr, *arena_pin = nullptr;
+    size_t arena_cap = 0;
+    struct TexSlot { int w = 0, h = 0; cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0; };
+    std::vector<TexSlot> tex_slots;          // reused when an upload brings images of the same sizes
+    uint32_t *tex_pin = nullptr;             // pinned RGBA8 staging for the RGB8 -> RGBA8 expansion
+    size_t tex_pin_cap = 0;
     float *lut_srgb = nullptr;
 
     int acc_w = 0, acc_h = 0, n_slabs = 0;
@@ -83,23 +92,49 @@ int fail(b200rt_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess)
 }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, B200RT_ERR_CUDA, #call, e_); } while (0)
 
-template <class T>
-int dev_upload(b200rt_ctx *ctx, const std::vector<T> &host, const T **out) {
-    *out = nullptr;
-    size_t bytes = std::max<size_t>(host.size(), 1) * sizeof(T);
-    void *p = nullptr;
-    CK(cudaMalloc(&p, bytes));
-    ctx->allocations.push_back(p);
-    if (!host.empty()) CK(cudaMemcpyAsync(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
-    *out = static_cast<const T *>(p);
+// Runs f(begin, end) over [0, n) on the host cores (record building is embarrassingly parallel).
+template <class F>
+void parallel_for(size_t n, const F &f) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = (unsigned)std::min<size_t>({(size_t)hw, (size_t)16, (n + 16383) / 16384});
+    if (nt <= 1) { f((size_t)0, n); return; }
+    const size_t chunk = (n + nt - 1) / nt;
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < nt; t++) {
+        const size_t a = t * chunk, b = std::min(n, a + chunk);
+        if (a < b) pool.emplace_back([a, b, &f] { f(a, b); });
+    }
+    f((size_t)0, std::min(n, chunk));
+    for (auto &th : pool) th.join();
+}
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+int ensure_arena(b200rt_ctx *ctx, size_t bytes) {
+    if (bytes <= ctx->arena_cap) return B200RT_OK;
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->arena_dev); cudaFreeHost(ctx->arena_pin);
+    ctx->arena_dev = ctx->arena_pin = nullptr; ctx->arena_cap = 0;
+    const size_t cap = bytes + bytes / 8;
+    CK(cudaMalloc((void **)&ctx->arena_dev, cap));
+    CK(cudaHostAlloc((void **)&ctx->arena_pin, cap, cudaHostAllocDefault));
+    ctx->arena_cap = cap;
     return B200RT_OK;
 }
 
-void release_scene(b200rt_ctx *c) {
-    for (auto t : c->textures) cudaDestroyTextureObject(t);
-    for (auto a : c->arrays) cudaFreeArray(a);
-    for (auto p : c->allocations) cudaFree(p);
-    c->textures.clear(); c->arrays.clear(); c->allocations.clear();
+void free_textures(b200rt_ctx *c) {
+    for (auto &t : c->tex_slots) { if (t.tex) cudaDestroyTextureObject(t.tex); if (t.arr) cudaFreeArray(t.arr); }
+    c->tex_slots.clear();
+}
+
+// The arena and the texture slots stay allocated for the next upload; b200rt_destroy frees them.
+void release_scene(b200rt_ctx *c) { c->has_scene = false; }
+
+void free_scene_memory(b200rt_ctx *c) {
+    free_textures(c);
+    cudaFree(c->arena_dev); cudaFreeHost(c->arena_pin); cudaFreeHost(c->tex_pin);
+    c->arena_dev = c->arena_pin = nullptr; c->tex_pin = nullptr;
+    c->arena_cap = c->tex_pin_cap = 0;
     c->has_scene = false;
 }
 
@@ -179,13 +214,8 @@ struct Flattener {
         out[idx] = pack(l0, h0, l1, h1, ml, mr);
         return idx;
     }
-    void run(const b200rt_bvh_node *nodes, int n_nodes, int root, const b200rt_triangle *t, int n_tris) {
-        ref = nodes; tris = t;
-        out.clear();
-        for (int k = 0; k < 3; k++) { q.base[k] = 0.f; q.scale[k] = 1.f; q.inv_scale[k] = 1.f; root_box.mn[k] = root_box.mx[k] = 0.f; }
-        root_word = B200RT_LEAF;
-        if (n_nodes <= 0 || n_tris <= 0) { out.emplace_back(); return; }
-        root_box = ref_box((uint32_t)root);
+    void set_grid(const FBox &rb) {
+        root_box = rb;
         for (int k = 0; k < 3; k++) {
             const double ext = (double)root_box.mx[k] - (double)root_box.mn[k];
             const double sc = ext > 0 ? ext / (B200RT_QMAX - 2.0) : 1.0;   // one spare grid unit on each side
@@ -193,6 +223,60 @@ struct Flattener {
             q.base[k] = (float)((double)root_box.mn[k] - sc);
             q.inv_scale[k] = (float)(1.0 / (double)q.scale[k]);
         }
+    }
+    // Non-recursive form for the common case (no leaf above 15 triangles): record index = rank of the
+    // inner node in array order (the reference builder emits parents before children, so this is the
+    // depth-first order too).  plan() is one serial pass; fill() is independent per node.
+    std::vector<uint32_t> rank;
+    std::vector<uint8_t> depth;      // 0 = not reachable from the root
+    uint32_t n_inner = 0;
+    bool plan(const b200rt_bvh_node *nodes, int n_nodes, int root, int n_tris) {
+        ref = nodes;
+        for (int k = 0; k < 3; k++) { q.base[k] = 0.f; q.scale[k] = 1.f; q.inv_scale[k] = 1.f; root_box.mn[k] = root_box.mx[k] = 0.f; }
+        root_word = B200RT_LEAF; n_inner = 0; max_depth = 0;
+        if (n_nodes <= 0 || n_tris <= 0) return true;
+        rank.assign((size_t)n_nodes, 0u);
+        depth.assign((size_t)n_nodes, 0);
+        depth[(size_t)root] = 1;
+        for (int i = 0; i < n_nodes; i++) {
+            const b200rt_bvh_node &n = nodes[i];
+            if (!depth[(size_t)i]) continue;
+            if (n.left == 0) {
+                if (n.last - n.first > 15) return false;
+            } else {
+                rank[(size_t)i] = n_inner++;
+                const uint8_t dd = (uint8_t)std::min(255, depth[(size_t)i] + 1);
+                depth[n.left] = dd; depth[n.right] = dd;
+            }
+            max_depth = std::max(max_depth, (int)depth[(size_t)i]);
+        }
+        set_grid(ref_box((uint32_t)root));
+        root_word = word_of((uint32_t)root);
+        return true;
+    }
+    uint32_t word_of(uint32_t r) const {
+        const b200rt_bvh_node &n = ref[r];
+        return n.left == 0 ? (B200RT_LEAF | ((n.last - n.first) << 27) | n.first) : rank[r];
+    }
+    void fill(int n_nodes, DPair *dst) const {
+        parallel_for((size_t)n_nodes, [&](size_t a, size_t b) {
+            for (size_t i = a; i < b; i++) {
+                const b200rt_bvh_node &n = ref[i];
+                if (n.left == 0 || !depth[i]) continue;
+                uint16_t l0[3], h0[3], l1[3], h1[3];
+                quantise(ref_box(n.left), l0, h0); quantise(ref_box(n.right), l1, h1);
+                dst[rank[i]] = pack(l0, h0, l1, h1, word_of(n.left), word_of(n.right));
+            }
+        });
+    }
+    void run(const b200rt_bvh_node *nodes, int n_nodes, int root, const b200rt_triangle *t, int n_tris) {
+        ref = nodes; tris = t;
+        out.clear();
+        for (int k = 0; k < 3; k++) { q.base[k] = 0.f; q.scale[k] = 1.f; q.inv_scale[k] = 1.f; root_box.mn[k] = root_box.mx[k] = 0.f; }
+        root_word = B200RT_LEAF;
+        if (n_nodes <= 0 || n_tris <= 0) { out.emplace_back(); return; }
+        set_grid(ref_box((uint32_t)root));
+        max_depth = 0;
         root_word = emit(root, 0, 0, 1);
         if (out.empty()) out.emplace_back();
     }
@@ -257,78 +341,146 @@ __global__ void resolve_kernel(const float *__restrict__ total, uint8_t *__restr
 
 namespace {
 
-int make_texture(b200rt_ctx *ctx, const b200rt_image &img, cudaTextureObject_t *out) {
-    *out = 0;
-    if (!img.rgb || img.width <= 0 || img.height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
-    std::vector<uchar4> rgba((size_t)img.width * img.height);
-    for (size_t i = 0; i < rgba.size(); i++) rgba[i] = make_uchar4(img.rgb[3 * i], img.rgb[3 * i + 1], img.rgb[3 * i + 2], 255);
-    // texels are fetched as ONE 32-bit word (R | G << 8 | B << 16 | A << 24): one result register per tap
-    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned int>();
-    cudaArray_t arr = nullptr;
-    CK(cudaMallocArray(&arr, &fmt, (size_t)img.width, (size_t)img.height));
-    ctx->arrays.push_back(arr);
-    CK(cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)img.width * 4, (size_t)img.width * 4, (size_t)img.height, cudaMemcpyHostToDevice));
-    cudaResourceDesc rd{};
-    rd.resType = cudaResourceTypeArray;
-    rd.res.array.array = arr;
-    cudaTextureDesc td{};
-    td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
-    td.filterMode = cudaFilterModePoint;          // the bilinear blend is done in the kernel
-    td.readMode = cudaReadModeElementType;
-    td.normalizedCoords = 0;
-    cudaTextureObject_t tex = 0;
-    CK(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
-    ctx->textures.push_back(tex);
-    *out = tex;
+// Textures of one upload: expand RGB8 -> RGBA8 into pinned staging on the host cores, then one async
+// 2D copy per image into a cudaArray.  Arrays and texture objects are kept in ctx->tex_slots and reused
+// when the next upload brings the same image sizes in the same order (a re-upload of the same scene).
+int upload_textures(b200rt_ctx *ctx, const std::vector<const b200rt_image *> &imgs, std::vector<cudaTextureObject_t> &out) {
+    out.assign(imgs.size(), 0);
+    size_t texels = 0;
+    bool same = imgs.size() == ctx->tex_slots.size();
+    for (size_t i = 0; i < imgs.size(); i++) {
+        const b200rt_image &img = *imgs[i];
+        if (!img.rgb || img.width <= 0 || img.height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
+        texels += (size_t)img.width * img.height;
+        if (same && (ctx->tex_slots[i].w != img.width || ctx->tex_slots[i].h != img.height)) same = false;
+    }
+    if (!same) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        free_textures(ctx);
+        // texels are fetched as ONE 32-bit word (R | G << 8 | B << 16 | A << 24): one result register per tap
+        const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned int>();
+        for (size_t i = 0; i < imgs.size(); i++) {
+            b200rt_ctx::TexSlot t;
+            t.w = imgs[i]->width; t.h = imgs[i]->height;
+            CK(cudaMallocArray(&t.arr, &fmt, (size_t)t.w, (size_t)t.h));
+            cudaResourceDesc rd{};
+            rd.resType = cudaResourceTypeArray;
+            rd.res.array.array = t.arr;
+            cudaTextureDesc td{};
+            td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+            td.filterMode = cudaFilterModePoint;          // the bilinear blend is done in the kernel
+            td.readMode = cudaReadModeElementType;
+            td.normalizedCoords = 0;
+            ctx->tex_slots.push_back(t);                  // owned from here on, also on a failure below
+            CK(cudaCreateTextureObject(&ctx->tex_slots.back().tex, &rd, &td, nullptr));
+        }
+    }
+    if (texels > ctx->tex_pin_cap) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        cudaFreeHost(ctx->tex_pin); ctx->tex_pin = nullptr; ctx->tex_pin_cap = 0;
+        CK(cudaHostAlloc((void **)&ctx->tex_pin, texels * sizeof(uint32_t), cudaHostAllocDefault));
+        ctx->tex_pin_cap = texels;
+    }
+    size_t off = 0;
+    for (size_t i = 0; i < imgs.size(); i++) {
+        const b200rt_image &img = *imgs[i];
+        const size_t n = (size_t)img.width * img.height;
+        uint32_t *dst = ctx->tex_pin + off;
+        const uint8_t *src = img.rgb;
+        parallel_for(n, [&](size_t a, size_t b) {
+            for (size_t k = a; k < b; k++) dst[k] = (uint32_t)src[3 * k] | ((uint32_t)src[3 * k + 1] << 8) | ((uint32_t)src[3 * k + 2] << 16) | 0xFF000000u;
+        });
+        CK(cudaMemcpy2DToArrayAsync(ctx->tex_slots[i].arr, 0, 0, dst, (size_t)img.width * 4, (size_t)img.width * 4, (size_t)img.height,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+        out[i] = ctx->tex_slots[i].tex;
+        off += n;
+    }
     return B200RT_OK;
 }
 
 int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     if (s->n_tris < 0 || s->n_tris >= (1 << 27)) return fail(ctx, B200RT_ERR_INVALID, "triangle count out of range");
     if (s->n_tris > 0 && (!s->tris || !s->materials)) return fail(ctx, B200RT_ERR_INVALID, "missing triangle/material arrays");
+    if (s->n_light_tris < 0 || s->n_materials < 0) return fail(ctx, B200RT_ERR_INVALID, "negative array size");
     if (!validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
     if (s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
-    for (int i = 0; i < s->n_tris; i++) if (s->tris[i].material >= (uint32_t)s->n_materials) return fail(ctx, B200RT_ERR_INVALID, "material index out of range");
 
     DGltfScene g{};
     g.hw8 = s->mode == B200RT_MODE_HW8;
     for (int k = 0; k < 3; k++) g.bg[k] = s->bg_color[k];
     int rc;
+    const bool timing = getenv("B200RT_UPLOAD_TIMING") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[upload] %-22s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
 
-    Flattener fl;
-    fl.run(s->nodes, s->n_nodes, s->root, s->tris, s->n_tris);
+    // 1. plan both trees (serial pass each); a leaf above 15 triangles needs the recursive splitter
+    Flattener fl, ll;
+    const bool fast_scene = fl.plan(s->nodes, s->n_nodes, s->root, s->n_tris);
+    if (!fast_scene) fl.run(s->nodes, s->n_nodes, s->root, s->tris, s->n_tris);
+    const bool fast_light = ll.plan(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris);
+    if (!fast_light) ll.run(s->light_nodes, s->n_light_nodes, 0, s->light_tris, s->n_light_tris);
     if (fl.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "scene BVH deeper than the traversal stack");
-    if ((rc = dev_upload(ctx, fl.out, &g.nodes))) return rc;
-    g.root = fl.root_word; g.q = fl.q;
+    if (ll.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "light BVH deeper than the traversal stack");
+    const size_t n_pairs = std::max<size_t>(1, fast_scene ? fl.n_inner : fl.out.size());
+    const size_t n_lpairs = std::max<size_t>(1, fast_light ? ll.n_inner : ll.out.size());
+    lap("plan");
 
-    std::vector<DTri> tris((size_t)s->n_tris);
-    std::vector<DShade> shade((size_t)s->n_tris);
-    for (int i = 0; i < s->n_tris; i++) {
-        const b200rt_triangle &t = s->tris[i];
-        tris[i] = make_tri(t);
-        tris[i].v0.w = __int_as_float_host((int)t.material);
-        DShade &q = shade[i];
-        q.q[0] = make_float4(t.n[0][0], t.n[0][1], t.n[0][2], t.uv[0][0]);
-        q.q[1] = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], t.uv[0][1]);
-        q.q[2] = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], t.uv[1][0]);
-        q.q[3] = make_float4(t.tan[0][0], t.tan[0][1], t.tan[0][2], t.uv[1][1]);
-        q.q[4] = make_float4(t.tan[1][0], t.tan[1][1], t.tan[1][2], t.uv[2][0]);
-        q.q[5] = make_float4(t.tan[2][0], t.tan[2][1], t.tan[2][2], t.uv[2][1]);
-    }
-    if ((rc = dev_upload(ctx, tris, &g.tris))) return rc;
-    if ((rc = dev_upload(ctx, shade, &g.shade))) return rc;
+    // 2. arena layout
+    const size_t nt = (size_t)s->n_tris, nl = (size_t)s->n_light_tris, nm = (size_t)s->n_materials;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off = align256(off + std::max<size_t>(bytes, 16)); return o; };
+    const size_t o_nodes = take(n_pairs * sizeof(DPair)), o_tris = take(nt * sizeof(DTri)), o_shade = take(nt * sizeof(DShade));
+    const size_t o_lnodes = take(n_lpairs * sizeof(DPair)), o_ltris = take(nl * sizeof(DTri)), o_lnorm = take(nl * sizeof(DLightNormals));
+    const size_t o_mats = take(nm * sizeof(DMaterial)), o_lut = take(256 * sizeof(float));
+    if ((rc = ensure_arena(ctx, off))) return rc;
+    char *pin = ctx->arena_pin, *dev = ctx->arena_dev;
+    // the staging buffer may still feed the copy of the previous upload
+    CK(cudaStreamSynchronize(ctx->stream));
+    lap("arena");
+
+    // 3. records, built in the staging buffer
+    DPair *pairs = reinterpret_cast<DPair *>(pin + o_nodes);
+    if (fast_scene) { if (fl.n_inner) fl.fill(s->n_nodes, pairs); else pairs[0] = DPair{}; }
+    else memcpy(pairs, fl.out.data(), fl.out.size() * sizeof(DPair));
+    g.root = fl.root_word; g.q = fl.q;
+    lap("scene BVH records");
+
+    DTri *tris = reinterpret_cast<DTri *>(pin + o_tris);
+    DShade *shade = reinterpret_cast<DShade *>(pin + o_shade);
+    std::vector<int> bad_material(1, 0);
+    parallel_for(nt, [&](size_t a, size_t b) {
+        for (size_t i = a; i < b; i++) {
+            const b200rt_triangle &t = s->tris[i];
+            if (t.material >= (uint32_t)s->n_materials) { bad_material[0] = 1; continue; }
+            tris[i] = make_tri(t);
+            tris[i].v0.w = __int_as_float_host((int)t.material);
+            DShade &q = shade[i];
+            q.q[0] = make_float4(t.n[0][0], t.n[0][1], t.n[0][2], t.uv[0][0]);
+            q.q[1] = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], t.uv[0][1]);
+            q.q[2] = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], t.uv[1][0]);
+            q.q[3] = make_float4(t.tan[0][0], t.tan[0][1], t.tan[0][2], t.uv[1][1]);
+            q.q[4] = make_float4(t.tan[1][0], t.tan[1][1], t.tan[1][2], t.uv[2][0]);
+            q.q[5] = make_float4(t.tan[2][0], t.tan[2][1], t.tan[2][2], t.uv[2][1]);
+        }
+    });
+    if (bad_material[0]) return fail(ctx, B200RT_ERR_INVALID, "material index out of range");
+    lap("triangle records");
 
     // lights: FiguresMix::figures_ + its BVH (hw8/src/include/distributions.h:99-115)
     g.n_light_tris = s->n_light_tris;
-    Flattener ll;
-    ll.run(s->light_nodes, s->n_light_nodes, 0, s->light_tris, s->n_light_tris);
-    if (ll.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "light BVH deeper than the traversal stack");
-    if ((rc = dev_upload(ctx, ll.out, &g.light_nodes))) return rc;
+    DPair *lpairs = reinterpret_cast<DPair *>(pin + o_lnodes);
+    if (fast_light) { if (ll.n_inner) ll.fill(s->n_light_nodes, lpairs); else lpairs[0] = DPair{}; }
+    else memcpy(lpairs, ll.out.data(), ll.out.size() * sizeof(DPair));
     g.light_root = ll.root_word; g.lq = ll.q;
     for (int k = 0; k < 3; k++) { g.light_min[k] = ll.root_box.mn[k]; g.light_max[k] = ll.root_box.mx[k]; }
-    std::vector<DTri> ltris((size_t)s->n_light_tris);
-    std::vector<DLightNormals> lnorm((size_t)s->n_light_tris);
-    for (int i = 0; i < s->n_light_tris; i++) {
+    DTri *ltris = reinterpret_cast<DTri *>(pin + o_ltris);
+    DLightNormals *lnorm = reinterpret_cast<DLightNormals *>(pin + o_lnorm);
+    for (size_t i = 0; i < nl; i++) {
         const b200rt_triangle &t = s->light_tris[i];
         ltris[i] = make_tri(t);
         // pointProb = 1.0 / (0.5 * |b.cross(c)|) in the reference's float/double mix (distributions.h:71-76)
@@ -340,16 +492,21 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         lnorm[i].n1 = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], 0);
         lnorm[i].n2 = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], 0);
     }
-    if ((rc = dev_upload(ctx, ltris, &g.light_tris))) return rc;
-    if ((rc = dev_upload(ctx, lnorm, &g.light_normals))) return rc;
+    lap("light set");
 
-    // textures: one point-sampled RGBA8 texture object per image (hw8 only)
-    std::vector<cudaTextureObject_t> tex((size_t)std::max(0, s->n_images), 0);
-    if (g.hw8)
-        for (int i = 0; i < s->n_images; i++)
-            if ((rc = make_texture(ctx, s->images[i], &tex[i]))) return rc;
-    std::vector<DMaterial> mats((size_t)s->n_materials);
-    for (int i = 0; i < s->n_materials; i++) {
+    // textures: one point-sampled texture object per image (hw8 only); the environment map is the last slot
+    std::vector<const b200rt_image *> imgs;
+    if (g.hw8) {
+        for (int i = 0; i < s->n_images; i++) imgs.push_back(&s->images[i]);
+        if (s->env_map) imgs.push_back(s->env_map);
+    }
+    std::vector<cudaTextureObject_t> tex;
+    if ((rc = upload_textures(ctx, imgs, tex))) return rc;
+    if (g.hw8 && s->env_map) { g.env = tex.back(); g.env_w = s->env_map->width; g.env_h = s->env_map->height; }
+    lap("textures");
+
+    DMaterial *mats = reinterpret_cast<DMaterial *>(pin + o_mats);
+    for (size_t i = 0; i < nm; i++) {
         const b200rt_material &m = s->materials[i];
         DMaterial &d = mats[i];
         memset(&d, 0, sizeof(d));
@@ -358,25 +515,29 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         auto bind = [&](int32_t idx, cudaTextureObject_t &t, int32_t &w, int32_t &h) -> bool {
             if (!g.hw8 || idx < 0) return true;
             if (idx >= s->n_images) return false;
-            t = tex[idx]; w = s->images[idx].width; h = s->images[idx].height;
+            t = tex[(size_t)idx]; w = s->images[idx].width; h = s->images[idx].height;
             return true;
         };
         if (!bind(m.base_color_image, d.tex_base, d.w_base, d.h_base) || !bind(m.emissive_image, d.tex_emissive, d.w_emissive, d.h_emissive) ||
             !bind(m.metallic_roughness_image, d.tex_mr, d.w_mr, d.h_mr) || !bind(m.normal_image, d.tex_normal, d.w_normal, d.h_normal))
             return fail(ctx, B200RT_ERR_INVALID, "image index out of range");
     }
-    if ((rc = dev_upload(ctx, mats, &g.materials))) return rc;
-    if (g.hw8 && s->env_map) {
-        if ((rc = make_texture(ctx, *s->env_map, &g.env))) return rc;
-        g.env_w = s->env_map->width; g.env_h = s->env_map->height;
-    }
     // sRGB decode table with the reference's own arithmetic: powf(float(1./255) * c, 2.2f) (scene.cpp:11-13)
-    std::vector<float> lut(256);
+    float *lut = reinterpret_cast<float *>(pin + o_lut);
     for (int c = 0; c < 256; c++) lut[c] = std::pow((float)(1. / 255) * (1.f * (float)c), 2.2f);
-    const float *lp = nullptr;
-    if ((rc = dev_upload(ctx, lut, &lp))) return rc;
-    ctx->lut_srgb = const_cast<float *>(lp);
+
+    // 4. one copy for everything
+    CK(cudaMemcpyAsync(dev, pin, off, cudaMemcpyHostToDevice, ctx->stream));
+    g.nodes = reinterpret_cast<const DPair *>(dev + o_nodes);
+    g.tris = reinterpret_cast<const DTri *>(dev + o_tris);
+    g.shade = reinterpret_cast<const DShade *>(dev + o_shade);
+    g.light_nodes = reinterpret_cast<const DPair *>(dev + o_lnodes);
+    g.light_tris = reinterpret_cast<const DTri *>(dev + o_ltris);
+    g.light_normals = reinterpret_cast<const DLightNormals *>(dev + o_lnorm);
+    g.materials = reinterpret_cast<const DMaterial *>(dev + o_mats);
+    ctx->lut_srgb = reinterpret_cast<float *>(dev + o_lut);
     ctx->gs = g;
+    lap("materials, lut, copy");
     return B200RT_OK;
 }
 
@@ -600,7 +761,7 @@ void b200rt_destroy(b200rt_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    release_scene(ctx);
+    free_scene_memory(ctx);
     free_wave(ctx);
     cudaFree(ctx->total); cudaFree(ctx->slabs); cudaFree(ctx->rgb8); cudaFree(ctx->ids); cudaFree(ctx->counters);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev_fork);
