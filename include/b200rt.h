@@ -116,6 +116,10 @@ typedef struct b200rt_material {
     int32_t emissive_image;
     int32_t metallic_roughness_image;
     int32_t normal_image;
+    /* hw6 only (hw6/src/include/gltf_structs.h:28-36, hw6/src/sceneio.cpp:179-183): the loader maps
+     * baseColorFactor alpha < 1 to DIELECTRIC (ior 1.5), else metallicFactor > 0 to METALLIC, else DIFFUSE. */
+    int32_t kind;             /* B200RT_MAT_* */
+    float   ior;
 } b200rt_material;
 
 /* `Texture` (hw8/src/include/gltf_structs.h:10-13): tightly packed RGB8, row 0 first. */

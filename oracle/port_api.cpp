@@ -23,6 +23,7 @@ int oracle_render(const b200rt_scene_desc *s, int rng_kind, uint32_t seed, int s
             port::render_deterministic(*s, rgb, primary_ids, accum_sum);
             return 0;
         case B200RT_MODE_HW4:
+        case B200RT_MODE_HW6:
         case B200RT_MODE_HW7:
         case B200RT_MODE_HW8:
             if (spp_end <= spp_begin) return -1;

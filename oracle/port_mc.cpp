@@ -611,6 +611,194 @@ struct Gltf {
     }
 };
 
+// =========================================== hw6 ============================================
+// hw6 = the hw5 integrator (DIFFUSE / METALLIC mirror / DIELECTRIC, Mix{Cosine, FiguresMix}) on glTF
+// triangles through the BVH (hw6/src/scene.cpp:8-126, hw6/src/primitives.cpp:76-85,143-164,
+// hw6/src/include/distributions.h:36-58,107-141,167-302).  Triangles carry no shading normals.
+struct Hit6 { float t = 0; V norma; bool inside = false; };
+
+// Figure::intersect (position 0, identity rotation) -> intersectAsTriangle: plane hit + three edge tests.
+static inline bool hit_triangle6(const b200rt_triangle &f, const Ray &ray, Hit6 &h) {
+    V a(f.p[2]);
+    V b = V(f.p[0]) - a;
+    V c = V(f.p[1]) - a;
+    V n = b.cross(c);
+    Ray r = ray.shifted(a);
+    float t = -r.o.dot(n) / r.d.dot(n);
+    if (!(t > 0 && t < kTMax)) return false;
+    V norma; bool inside;
+    if (r.d.dot(n) > 0) { norma = -1. * n; inside = true; }
+    else { norma = n; inside = false; }
+    V p = ray.o - a + t * ray.d;
+    if (b.cross(p).dot(n) < 0) return false;
+    if (p.cross(c).dot(n) < 0) return false;
+    if ((c - b).cross(p - b).dot(n) < 0) return false;
+    h.t = t; h.norma = norma.normalize(); h.inside = inside;
+    return true;
+}
+
+template <class Rng>
+struct Hw6 {
+    const b200rt_scene_desc &s;
+    Rng &rng;
+    Counters *cnt;
+
+    Hw6(const b200rt_scene_desc &s_, Rng &r, Counters *c) : s(s_), rng(r), cnt(c) {}
+
+    // BVH::intersect_ (hw6/src/include/bvh.h:111-142): same control flow as hw8 (see Gltf::closest)
+    bool closest(uint32_t pos, const Ray &ray, bool have, float cur_best, Hit6 &out, int &out_id) const {
+        const b200rt_bvh_node &nd = s.nodes[pos];
+        float tb; bool inside;
+        if (cnt) cnt->node_tests++;
+        if (!hit_aabb(nd, ray, tb, inside)) return false;
+        if (have && cur_best < tb && !inside) return false;
+        bool found = false;
+        if (nd.left == 0) {
+            for (uint32_t i = nd.first; i < nd.last; i++) {
+                Hit6 h;
+                if (cnt) cnt->tri_tests++;
+                if (hit_triangle6(s.tris[i], ray, h) && (!found || h.t < out.t)) { out = h; out_id = (int)i; found = true; }
+            }
+            return found;
+        }
+        found = closest(nd.left, ray, have, cur_best, out, out_id);
+        if (found && (!have || out.t < cur_best)) { have = true; cur_best = out.t; }
+        Hit6 rh; int rid = -1;
+        if (closest(nd.right, ray, have, cur_best, rh, rid) && (!found || rh.t < out.t)) { out = rh; out_id = rid; found = true; }
+        return found;
+    }
+
+    V cosine_sample(V n) {
+        V d = rng.sphere();
+        d = d + n;
+        float len = d.len();
+        if (len <= 1e-9f || d.dot(n) <= 1e-9f || std::isnan(len)) return n;
+        return 1. / len * d;
+    }
+    static float cosine_pdf(V n, V d) { return std::max(0.f, d.dot(n) / PI); }
+
+    // FiguresMix::sample -> TriangleLight::sample (distributions.h:127-141, 222-231)
+    V light_sample(V x) {
+        int which = rng.u() * (size_t)s.n_light_tris;
+        const b200rt_triangle &f = s.light_tris[which];
+        V a(f.p[2]); V b = V(f.p[0]) - a; V c = V(f.p[1]) - a;
+        float u = rng.u();
+        float v = rng.u();
+        if (u + v > 1.) { u = 1 - u; v = 1 - v; }
+        V point = a + u * b + v * c;
+        return (point - x).normalize();
+    }
+    // pdfOneFigureLight for a triangle (:242-262): first hit only
+    float light_pdf_one(const b200rt_triangle &f, V x, V d) const {
+        Hit6 h;
+        if (cnt) cnt->light_tri_tests++;
+        if (!hit_triangle6(f, Ray(x, d), h)) return 0.;
+        if (std::isnan(h.t)) return INFINITY;
+        V y = x + h.t * d;
+        V a(f.p[2]); V b = V(f.p[0]) - a; V c = V(f.p[1]) - a;
+        V n = b.cross(c);
+        float pointProb = 1.0 / (0.5 * n.len());
+        return pointProb * (x - y).len2() / fabs(d.dot(h.norma));
+    }
+    float light_total(uint32_t pos, V x, V d) const {
+        const b200rt_bvh_node &nd = s.light_nodes[pos];
+        float tb; bool inside;
+        if (cnt) cnt->light_node_tests++;
+        if (!hit_aabb(nd, Ray(x, d), tb, inside)) return 0;
+        if (nd.left == 0) {
+            float result = 0;
+            for (uint32_t i = nd.first; i < nd.last; i++) result += light_pdf_one(s.light_tris[i], x, d);
+            return result;
+        }
+        return light_total(nd.left, x, d) + light_total(nd.right, x, d);
+    }
+    size_t components() const { return s.n_light_tris > 0 ? 2 : 1; }
+    V mix_sample(V x, V n) {
+        int which = rng.u() * components();
+        if (which == 0) return cosine_sample(n);
+        return light_sample(x);
+    }
+    float mix_pdf(V x, V n, V d) const {
+        float ans = 0;
+        ans += cosine_pdf(n, d);
+        if (s.n_light_tris > 0) {
+            if (cnt) cnt->light_queries++;
+            ans += light_total(0, x, d) / (size_t)s.n_light_tris;
+        }
+        return ans / components();
+    }
+
+    V color(const Ray &ray, int rec) {
+        if (rec == 0) return V(0., 0., 0.);
+        Hit6 h; int pos = -1;
+        if (cnt) cnt->rays++;
+        if (!closest((uint32_t)s.root, ray, false, 0.f, h, pos)) return V(s.bg_color);
+        rng.begin_bounce((uint32_t)(s.ray_depth - rec));
+        const b200rt_material &m = s.materials[s.tris[pos].material];
+        float t = h.t; V norma = h.norma; bool is_inside = h.inside;
+        V x = ray.o + t * ray.d;
+        V emission(m.emission), fcolor(m.base_color);
+        if (m.kind == B200RT_MAT_DIFFUSE) {
+            V d = mix_sample(x + eps * norma, norma);
+            if (d.dot(norma) < 0) return emission;
+            float pdf = mix_pdf(x + eps * norma, norma, d);
+            Ray dRay(x + eps * d, d);
+            return emission + 1. / (PI * pdf) * d.dot(norma) * fcolor * color(dRay, rec - 1);
+        } else if (m.kind == B200RT_MAT_METALLIC) {
+            V reflectedDir = ray.d.normalize() - 2. * norma.dot(ray.d.normalize()) * norma;
+            Ray reflected(ray.o + t * ray.d + eps * reflectedDir, reflectedDir);
+            return emission + fcolor * color(reflected, rec - 1);
+        } else {
+            V reflectedDir = ray.d.normalize() - 2. * norma.dot(ray.d.normalize()) * norma;
+            Ray reflected(ray.o + t * ray.d + eps * reflectedDir, reflectedDir);
+            // reference: reflected branch traced before, and regardless of, the Fresnel coin (see Hw4::color)
+            V reflectedColor;
+            float coin = 0;
+            if (Rng::kCounterBased) coin = rng.u();
+            else reflectedColor = color(reflected, rec - 1);
+            float eta1 = 1., eta2 = m.ior;
+            if (is_inside) std::swap(eta1, eta2);
+            V l = -1. * ray.d.normalize();
+            float sinTheta2 = eta1 / eta2 * sqrt(1 - norma.dot(l) * norma.dot(l));
+            if (fabs(sinTheta2) > 1.) {
+                if (Rng::kCounterBased) reflectedColor = color(reflected, rec - 1);
+                return emission + reflectedColor;
+            }
+            float r0 = pow((eta1 - eta2) / (eta1 + eta2), 2.);
+            float r = r0 + (1 - r0) * pow(1 - norma.dot(l), 5.);
+            if (!Rng::kCounterBased) coin = rng.u();
+            if (coin < r) {
+                if (Rng::kCounterBased) reflectedColor = color(reflected, rec - 1);
+                return emission + reflectedColor;
+            }
+            float cosTheta2 = sqrt(1 - sinTheta2 * sinTheta2);
+            V refractedDir = eta1 / eta2 * (-1. * l) + (eta1 / eta2 * norma.dot(l) - cosTheta2) * norma;
+            Ray refracted(ray.o + t * ray.d + eps * refractedDir, refractedDir);
+            V refractedColor = color(refracted, rec - 1);
+            if (!is_inside) refractedColor = refractedColor * fcolor;
+            return emission + refractedColor;
+        }
+    }
+
+    Ray camera_ray(float x, float y) const {   // fovY based, direction NOT normalised (hw6/src/scene.cpp:118-126)
+        float tanFovY = tan(s.cam_fov / 2);
+        float tanFovX = tanFovY * s.width / s.height;
+        float nx = tanFovX * (2 * x / s.width - 1);
+        float ny = tanFovY * (2 * y / s.height - 1);
+        return {V(s.cam_pos), nx * V(s.cam_right) - ny * V(s.cam_up) + V(s.cam_forward)};
+    }
+    V pixel_sum(int x, int y, int b, int e) {
+        V c{0, 0, 0};
+        for (int k = b; k < e; k++) {
+            rng.begin_sample((uint32_t)k);
+            float nx = x + rng.u();
+            float ny = y + rng.u();
+            c = c + color(camera_ray(nx, ny), s.ray_depth);
+        }
+        return c;
+    }
+};
+
 }  // namespace mc
 
 // ------------------------------------------------------------------------------------------
@@ -669,6 +857,9 @@ void render_mc(const b200rt_scene_desc &s, int rng_kind, uint32_t seed, int b, i
         } else {
             render_per_pixel_rng<Hw4Adapter<mc::Hw4Philox>, mc::Hw4Philox>(s, seed, b, e, accum, rgb, nullptr);
         }
+    } else if (s.mode == B200RT_MODE_HW6) {
+        if (rng_kind == 0) render_per_pixel_rng<mc::Hw6<RngMinstd>, RngMinstd>(s, seed, b, e, accum, rgb, cp);
+        else render_per_pixel_rng<mc::Hw6<RngPhilox>, RngPhilox>(s, seed, b, e, accum, rgb, cp);
     } else {
         if (rng_kind == 0) render_per_pixel_rng<mc::Gltf<RngMinstd>, RngMinstd>(s, seed, b, e, accum, rgb, cp);
         else render_per_pixel_rng<mc::Gltf<RngPhilox>, RngPhilox>(s, seed, b, e, accum, rgb, cp);

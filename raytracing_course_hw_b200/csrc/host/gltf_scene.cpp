@@ -116,9 +116,14 @@ struct Loader {
             cur.base_color[0] = cur.base_color[1] = cur.base_color[2] = 1.f;
             cur.metallic_factor = 1.f; cur.roughness_factor = 1.f;
             cur.base_color_image = cur.emissive_image = cur.metallic_roughness_image = cur.normal_image = -1;
+            cur.kind = B200RT_MAT_DIFFUSE; cur.ior = 1.5f;
+            float alpha = 1.f;
             const Json &pbr = m["pbrMetallicRoughness"];
             if (!pbr.is_null()) {
-                if (pbr.has("baseColorFactor")) for (int i = 0; i < 3; i++) cur.base_color[i] = pbr["baseColorFactor"][i].as_float();
+                if (pbr.has("baseColorFactor")) {
+                    for (int i = 0; i < 3; i++) cur.base_color[i] = pbr["baseColorFactor"][i].as_float();
+                    alpha = pbr["baseColorFactor"][3].as_float();
+                }
                 cur.base_color_image = tex(pbr["baseColorTexture"]);
                 if (pbr.has("metallicFactor")) cur.metallic_factor = pbr["metallicFactor"].as_float();
                 if (pbr.has("roughnessFactor")) {
@@ -135,6 +140,10 @@ struct Loader {
             if (!strength.is_null()) {
                 float k = strength["emissiveStrength"].as_float();
                 for (int i = 0; i < 3; i++) cur.emission[i] = k * cur.emission[i];
+            }
+            if (mode == B200RT_MODE_HW6) {   // hw6/src/sceneio.cpp:179-183
+                if (alpha < 1) cur.kind = B200RT_MAT_DIELECTRIC;
+                else if (cur.metallic_factor > 0) cur.kind = B200RT_MAT_METALLIC;
             }
             s.materials.push_back(cur);
         }
@@ -162,7 +171,10 @@ struct Loader {
                 const Json &at = pr["attributes"];
                 auto idx = [&](const Json &j) -> long { return j.is_number() ? (long)j.as_uint() : -1; };
                 std::vector<float> pos, uv, nrm, tan;
-                if (!read_floats(idx(at["POSITION"]), 3, pos) || !read_floats(idx(at["NORMAL"]), 3, nrm)) return B200RT_HOST_ERR_PARSE;
+                if (!read_floats(idx(at["POSITION"]), 3, pos)) return B200RT_HOST_ERR_PARSE;
+                // hw6 reads POSITION only (hw6/src/sceneio.cpp:85-87); hw7/hw8 require NORMAL
+                const bool has_nrm = read_floats(idx(at["NORMAL"]), 3, nrm) && nrm.size() == pos.size();
+                if (!has_nrm && mode != B200RT_MODE_HW6) return B200RT_HOST_ERR_PARSE;
                 bool has_uv = read_floats(idx(at["TEXCOORD_0"]), 2, uv);
                 bool has_tan = read_floats(idx(at["TANGENT"]), 4, tan);
                 if (mode == B200RT_MODE_HW8 && (!has_uv || !has_tan)) return B200RT_HOST_ERR_PARSE;
@@ -194,9 +206,11 @@ struct Loader {
                     for (int k = 0; k < 3; k++) {
                         size_t v = id[k]; int d = slot[k];
                         V3 P = M.apply(V3(pos[3 * v], pos[3 * v + 1], pos[3 * v + 2]));
-                        V3 Nn = N.apply(V3(nrm[3 * v], nrm[3 * v + 1], nrm[3 * v + 2])).normalized();
                         t.p[d][0] = P.x; t.p[d][1] = P.y; t.p[d][2] = P.z;
-                        t.n[d][0] = Nn.x; t.n[d][1] = Nn.y; t.n[d][2] = Nn.z;
+                        if (has_nrm) {
+                            V3 Nn = N.apply(V3(nrm[3 * v], nrm[3 * v + 1], nrm[3 * v + 2])).normalized();
+                            t.n[d][0] = Nn.x; t.n[d][1] = Nn.y; t.n[d][2] = Nn.z;
+                        }
                         if (has_uv && v * 2 + 1 < uv.size()) { t.uv[d][0] = uv[2 * v]; t.uv[d][1] = uv[2 * v + 1]; }
                         if (has_tan && v * 4 + 3 < tan.size()) {
                             V3 T = (M.apply(V3(tan[4 * v], tan[4 * v + 1], tan[4 * v + 2])) - shift).normalized();

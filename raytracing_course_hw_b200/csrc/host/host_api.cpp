@@ -47,10 +47,12 @@ int load_image_rgb8(const std::string &path, int32_t &w, int32_t &h, std::vector
 #endif
 }
 
-static BvhItem item_of(const b200rt_triangle &t, uint32_t index) {
+static BvhItem item_of(const b200rt_triangle &t, uint32_t index, bool hw6_key) {
     BvhItem it;
     for (int a = 0; a < 3; a++) {
-        it.key[a] = t.p[2][a];  // data3.coords (hw8/src/include/bvh.h:63-65)
+        // hw7/hw8 sort by data3.coords (hw8/src/include/bvh.h:63-65); hw6 sorts by Figure::position, which is
+        // (0,0,0) for every glTF triangle (hw6/src/include/bvh.h:63-65): the sorts then only permute equal keys
+        it.key[a] = hw6_key ? 0.f : t.p[2][a];
         it.mn[a] = std::min(t.p[2][a], std::min(t.p[0][a], t.p[1][a]));
         it.mx[a] = std::max(t.p[2][a], std::max(t.p[0][a], t.p[1][a]));
     }
@@ -58,9 +60,9 @@ static BvhItem item_of(const b200rt_triangle &t, uint32_t index) {
     return it;
 }
 
-static void build_over(std::vector<b200rt_triangle> &tris, uint32_t n, std::vector<b200rt_bvh_node> &nodes, int32_t *root) {
+static void build_over(std::vector<b200rt_triangle> &tris, uint32_t n, std::vector<b200rt_bvh_node> &nodes, int32_t *root, bool hw6_key) {
     std::vector<BvhItem> items(n);
-    for (uint32_t i = 0; i < n; i++) items[i] = item_of(tris[i], i);
+    for (uint32_t i = 0; i < n; i++) items[i] = item_of(tris[i], i, hw6_key);
     BvhBuilder b;
     b.build(items, n);
     std::vector<b200rt_triangle> sorted(n);
@@ -75,7 +77,8 @@ static void build_over(std::vector<b200rt_triangle> &tris, uint32_t n, std::vect
 // emissive ones (material emissiveFactor != 0; textures ignored) to the front, build a second
 // BVH over them.
 void build_triangle_accel(b200rt_host_scene &s) {
-    build_over(s.tris, (uint32_t)s.tris.size(), s.nodes, &s.desc.root);
+    const bool hw6_key = s.desc.mode == B200RT_MODE_HW6;
+    build_over(s.tris, (uint32_t)s.tris.size(), s.nodes, &s.desc.root, hw6_key);
     std::vector<b200rt_triangle> copy = s.tris;
     auto emissive = [&](const b200rt_triangle &t) {
         const float *e = s.materials[t.material].emission;
@@ -85,7 +88,7 @@ void build_triangle_accel(b200rt_host_scene &s) {
     copy.resize(n);
     s.light_tris = std::move(copy);
     s.light_nodes.clear();
-    if (n > 0) build_over(s.light_tris, (uint32_t)n, s.light_nodes, nullptr);
+    if (n > 0) build_over(s.light_tris, (uint32_t)n, s.light_nodes, nullptr, hw6_key);
     // n == 0: the reference still builds a one-node BVH over nothing but never uses it.
 }
 
