@@ -13,6 +13,8 @@
 #include "device_scene.h"
 #include "gltf_kernel.cuh"
 #include "wavefront_trace.cuh"
+#include "hw6_kernel.cuh"
+#include "bvh_rebuild.h"
 #include <chrono>
 #include <thread>
 
@@ -418,6 +420,21 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         t_last = now;
     };
 
+    // hw6: the reference tree is a SAH split of an arbitrary order (all sort keys equal); traverse our own
+    RebuiltBvh own;
+    std::vector<b200rt_triangle> own_tris;
+    b200rt_scene_desc local;
+    if (s->mode == B200RT_MODE_HW6 && s->n_tris > 0) {
+        rebuild_bvh_binned_sah(s->tris, s->n_tris, own);
+        own_tris.resize((size_t)s->n_tris);
+        for (int i = 0; i < s->n_tris; i++) own_tris[(size_t)i] = s->tris[own.order[(size_t)i]];
+        local = *s;
+        local.tris = own_tris.data();
+        local.nodes = own.nodes.data(); local.n_nodes = (int32_t)own.nodes.size(); local.root = 0;
+        s = &local;
+        lap("rebuild BVH (hw6)");
+    }
+
     // 1. plan both trees (serial pass each); a leaf above 15 triangles needs the recursive splitter
     Flattener fl, ll;
     const bool fast_scene = fl.plan(s->nodes, s->n_nodes, s->root, s->n_tris);
@@ -512,6 +529,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         memset(&d, 0, sizeof(d));
         for (int k = 0; k < 3; k++) { d.base_color[k] = m.base_color[k]; d.emission[k] = m.emission[k]; }
         d.metallic_factor = m.metallic_factor; d.roughness_factor = m.roughness_factor;
+        d.kind = m.kind; d.ior = m.ior;
         auto bind = [&](int32_t idx, cudaTextureObject_t &t, int32_t &w, int32_t &h) -> bool {
             if (!g.hw8 || idx < 0) return true;
             if (idx >= s->n_images) return false;
@@ -802,11 +820,11 @@ int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
             CK(analytic_upload(a, ctx->stream));
             break;
         }
-        case B200RT_MODE_HW7: case B200RT_MODE_HW8:
+        case B200RT_MODE_HW6: case B200RT_MODE_HW7: case B200RT_MODE_HW8:
             rc = upload_gltf(ctx, s);
             break;
         default:
-            return fail(ctx, B200RT_ERR_UNSUPPORTED, "scene mode not implemented on the device path (hw3, hw5, hw6)");
+            return fail(ctx, B200RT_ERR_UNSUPPORTED, "scene mode not implemented on the device path (hw3, hw5)");
     }
     if (rc) { release_scene(ctx); return rc; }
     CK(cudaStreamSynchronize(ctx->stream));
@@ -861,6 +879,15 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
     if (d.mode == B200RT_MODE_HW1) { CK(launch_cast(rp.cam, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
     else if (d.mode == B200RT_MODE_HW2) { CK(launch_whitted(rp.cam, ray_depth, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
     else if (d.mode == B200RT_MODE_HW4) { CK(launch_pt_analytic(rp, ctx->stream)); launches++; }
+    else if (d.mode == B200RT_MODE_HW6) {
+        const long long warps = (long long)((width + 7) / 8) * ((height + 3) / 4) * n_chunks;
+        const long long blocks = (warps * 32 + 127) / 128;
+        if (blocks > 0x7fffffffll) return fail(ctx, B200RT_ERR_INVALID, "grid too large");
+        if (ctx->flags & B200RT_FLAG_COUNTERS) hw6_path_kernel<true><<<(unsigned)blocks, 128, 0, ctx->stream>>>(ctx->gs, rp);
+        else hw6_path_kernel<false><<<(unsigned)blocks, 128, 0, ctx->stream>>>(ctx->gs, rp);
+        CK(cudaGetLastError());
+        launches++;
+    }
     else if (!(ctx->flags & B200RT_FLAG_MEGAKERNEL)) {
         const bool count = ctx->flags & B200RT_FLAG_COUNTERS;
         int wrc;

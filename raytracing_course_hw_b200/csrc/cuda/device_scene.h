@@ -60,6 +60,8 @@ struct DMaterial {
     float roughness_factor;
     cudaTextureObject_t tex_base, tex_emissive, tex_mr, tex_normal;  // 0 = absent
     int32_t w_base, h_base, w_emissive, h_emissive, w_mr, h_mr, w_normal, h_normal;
+    int32_t kind;        // hw6: B200RT_MAT_DIFFUSE / METALLIC / DIELECTRIC
+    float ior;           // hw6 dielectric
 };
 
 struct DCamera {

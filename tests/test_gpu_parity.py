@@ -101,6 +101,22 @@ def test_gltf_matches_port_on_same_stream(renderer, path, frac):
     assert st["paths"] == 128 * 96 * 16
 
 
+@pytest.mark.parametrize("path,frac", [("hw7/practice7_1.gltf", 0.85), ("hw6/practice7_1_glass.gltf", 0.85)])
+def test_hw6_matches_port_on_same_stream(renderer, path, frac):
+    """hw6 mode (hw5 integrator on triangles; the device traverses its own binned-SAH tree, the port the
+    reference's): same Philox stream => same paths up to float rounding of the hit points."""
+    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16, mode=6)
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1, want_counters=True)
+    ok, got = _mean_close(acc, port["accum"], 16, frac, rel=5e-2)
+    assert ok, got
+    assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+    st = renderer.stats()
+    assert abs(int(st["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    assert abs(int(st["light_queries"]) - int(port["counters"][3])) <= 2e-3 * int(port["counters"][3])
+    assert st["paths"] == 128 * 96 * 16
+
+
 # ---------------------------------------------------------------- MC: north_star statistical bar
 def _linear(img8):
     return ou.inv_display(img8)
@@ -110,6 +126,8 @@ def _linear(img8):
     ("hw8_sphere_emissive_128x96", "hw8/sphere_emissive.gltf", "gltf"),
     ("hw7_practice7_1_128x96", "hw7/practice7_1.gltf", "gltf"),
     ("hw7_practice7_4_128x96", "hw7/practice7_4.gltf", "gltf"),
+    ("hw6_practice7_1_128x96", "hw7/practice7_1.gltf", "gltf6"),
+    ("hw6_practice7_1_glass_128x96", "hw6/practice7_1_glass.gltf", "gltf6"),
     ("hw4_p3_1", "hw4_p3_1_spp4096.txt", "text"),
     ("hw4_p3_3", "hw4_p3_3_spp4096.txt", "text"),
     ("hw4_p3_4", "hw4_p3_4_spp4096.txt", "text"),
@@ -118,6 +136,8 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
     spp = 64
     if kind == "gltf":
         sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp)
+    elif kind == "gltf6":
+        sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
     else:
         sc = rt.load_scene(os.path.join(G, path), samples=spp)
     truth = _linear(ou.golden(name + "_spp4096"))

@@ -50,6 +50,17 @@ def test_port_gltf_bytes_equal_reference(name, path):
     assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
 
 
+@pytest.mark.parametrize("name,path", [("hw6_practice7_1", "hw7/practice7_1.gltf"),
+                                       ("hw6_practice7_1_glass", "hw6/practice7_1_glass.gltf")])
+def test_port_hw6_bytes_equal_reference(name, path):
+    """hw6 = hw5 integrator (diffuse / mirror / dielectric) on glTF triangles: the port with the reference's
+    generator reproduces the hw6 binary's PPM byte for byte (this also pins the hw6 loader's material
+    mapping and its BVH build over all-equal sort keys, which fixes the light order)."""
+    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=4, mode=6)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
+
+
 def test_port_philox_is_statistically_the_same_estimator():
     """The Philox policy changes only the random numbers: at equal spp its error against the
     4096-spp reference render must be comparable to the minstd policy's, and the mean must agree."""

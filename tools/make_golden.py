@@ -9,6 +9,8 @@ Fixtures:
   hw4_p3_{k}_spp4096.ppm.gz                       ground truth for the RMSE tests (160x120, SAMPLES 4096)
   hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
   hw8_sphere_emissive_128x96_spp4.ppm.gz / _spp4096
+  hw6_{name}_128x96_spp4.ppm.gz / _spp4096        hw6 binary on practice7_1 (mirrors + diffuse) and on
+                                                  hw6/practice7_1_glass (same geometry, cube alpha 0.5 => dielectric)
 """
 import gzip, os, re, subprocess, sys, tempfile
 
@@ -44,7 +46,9 @@ def main():
         run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4.txt"), "@OUT"], f"hw4_p3_{k}_spp4")
     for name, path, binary in (("hw7_practice7_1", "hw7/practice7_1.gltf", "hw7"),
                                ("hw7_practice7_4", "hw7/practice7_4.gltf", "hw7"),
-                               ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf", "hw8")):
+                               ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf", "hw8"),
+                               ("hw6_practice7_1", "hw7/practice7_1.gltf", "hw6"),
+                               ("hw6_practice7_1_glass", "hw6/practice7_1_glass.gltf", "hw6")):
         for spp in (4, 4096):
             run(binary, [os.path.join(SC, path), "128", "96", str(spp), "@OUT"], f"{name}_128x96_spp{spp}")
     for k in (1, 3, 4):  # slow (single-threaded reference): last
