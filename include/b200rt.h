@@ -162,6 +162,10 @@ typedef struct b200rt_options {
 
 #define B200RT_FLAG_COUNTERS   1  /* also count node fetches / triangle tests / texture lookups */
 #define B200RT_FLAG_MEGAKERNEL 2  /* glTF modes: one-kernel-per-path variant instead of the wavefront pipeline */
+#define B200RT_FLAG_REFERENCE_BVH 8 /* glTF modes: traverse the scene BVH exactly as given in the description (the reference's
+                                      SAH tree) instead of the binned-SAH tree the library builds over the same triangles;
+                                      results are identical up to closest-hit ties, the rebuilt tree tests ~20 % fewer boxes.
+                                      hw6 always rebuilds (its reference tree is degenerate) */
 #define B200RT_FLAG_SERIAL_WAVES 4 /* wavefront: one wave in flight on one stream (default: two waves overlap on two
                                       streams); the per-stage times in b200rt_stats are then exclusive kernel times */
 

@@ -44,6 +44,8 @@ struct b200rt_ctx {
     uint32_t *tex_pin = nullptr;             // pinned RGBA8 staging for the RGB8 -> RGBA8 expansion
     size_t tex_pin_cap = 0;
     float *lut_srgb = nullptr;
+    RebuiltBvh own_bvh;                      // host scratch of the BVH rebuild (bvh_rebuild.h)
+    std::vector<b200rt_triangle> own_tris;   // triangles in the rebuilt tree's order
 
     int acc_w = 0, acc_h = 0, n_slabs = 0;
     float *total = nullptr, *slabs = nullptr;
@@ -420,19 +422,24 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         t_last = now;
     };
 
-    // hw6: the reference tree is a SAH split of an arbitrary order (all sort keys equal); traverse our own
-    RebuiltBvh own;
-    std::vector<b200rt_triangle> own_tris;
+    // The scene tree is rebuilt behind the ABI (bvh_rebuild.h) unless the caller asks for the tree of the
+    // description; hw6 always rebuilds (its reference tree is a SAH split of an arbitrary order).
+    RebuiltBvh &own = ctx->own_bvh;                        // buffers reused by the next upload
+    std::vector<b200rt_triangle> &own_tris = ctx->own_tris;
     b200rt_scene_desc local;
-    if (s->mode == B200RT_MODE_HW6 && s->n_tris > 0) {
+    const bool rebuild = s->mode == B200RT_MODE_HW6 || !(ctx->flags & B200RT_FLAG_REFERENCE_BVH);
+    if (rebuild && s->n_tris > 0) {
         rebuild_bvh_binned_sah(s->tris, s->n_tris, own);
         own_tris.resize((size_t)s->n_tris);
-        for (int i = 0; i < s->n_tris; i++) own_tris[(size_t)i] = s->tris[own.order[(size_t)i]];
+        {
+            const b200rt_triangle *src = s->tris;
+            parallel_for((size_t)s->n_tris, [&](size_t a, size_t b) { for (size_t i = a; i < b; i++) own_tris[i] = src[own.order[i]]; });
+        }
         local = *s;
         local.tris = own_tris.data();
         local.nodes = own.nodes.data(); local.n_nodes = (int32_t)own.nodes.size(); local.root = 0;
         s = &local;
-        lap("rebuild BVH (hw6)");
+        lap("rebuild BVH");
     }
 
     // 1. plan both trees (serial pass each); a leaf above 15 triangles needs the recursive splitter

@@ -1,14 +1,25 @@
-// Binned-SAH BVH builder used behind the C ABI when the tree that crosses the boundary is unusable
-// for traversal: hw6 sorts its triangles by Figure::position, which is (0,0,0) for every glTF
-// triangle (hw6/src/include/bvh.h:63-65), so the reference tree is a SAH split of an arbitrary
-// order -- depth ~60 and two orders of magnitude slower to traverse.
-// Closest-hit results do not depend on the tree, so the device path builds its own over the
-// same triangles: top-down, 16 centroid bins per axis, reference-shaped output nodes (left == 0 marks
-// a leaf holding [first, last) of the PERMUTED triangle order returned in `order`).
+// Binned-SAH BVH builder used behind the C ABI ("better BVH").
+//
+// The tree that crosses the boundary is the reference's: a full-sweep SAH over triangles sorted by ONE
+// vertex (hw8/src/include/bvh.h:63-65), or -- in hw6 -- over an arbitrary order, because hw6 sorts by
+// Figure::position, which is (0,0,0) for every glTF triangle (hw6/src/include/bvh.h:63-65; depth ~60,
+// two orders of magnitude slower to traverse).  Closest-hit results do not depend on the tree
+// (SURVEY Q7), so the device path may traverse its own: top-down, 16 centroid bins per axis, SAH with a
+// traversal-cost term, leaves of up to 4 triangles.  On the benchmark scene it tests 20 % fewer boxes
+// per ray than the reference tree (profiles/r01_sweep_bvh_rebuild.log).
+//
+// Parallel build: the top of the tree is split node by node with the binning spread over the host
+// cores; once every open node is small, the subtrees are built independently, one task each.
+// Output: reference-shaped nodes (left == 0 marks a leaf holding [first, last) of the PERMUTED triangle
+// order returned in `order`; children always have larger indices than their parent).
 #pragma once
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cstdint>
+#include <cstdlib>
+#include <mutex>
+#include <thread>
 #include <vector>
 #include "b200rt.h"
 
@@ -17,103 +28,315 @@ namespace b200rt {
 struct RebuiltBvh {
     std::vector<b200rt_bvh_node> nodes;
     std::vector<uint32_t> order;     // order[i] = index of the input triangle stored at position i
+    // scratch kept between builds (a context re-uploading a scene does not page-fault fresh memory again)
+    std::vector<float> scratch_box, scratch_cen;
 };
 
-inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBvh &out) {
-    constexpr int BINS = 16, LEAF_MAX = 4;
-    struct B3 {
-        float mn[3], mx[3];
-        void reset() { for (int a = 0; a < 3; a++) { mn[a] = FLT_MAX; mx[a] = -FLT_MAX; } }
-        void grow(const B3 &o) { for (int a = 0; a < 3; a++) { mn[a] = std::min(mn[a], o.mn[a]); mx[a] = std::max(mx[a], o.mx[a]); } }
-        float area() const {
-            const float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
-            return dx < 0 ? 0.f : 2.f * (dx * dy + dx * dz + dy * dz);
+namespace bvh_detail {
+
+constexpr int BINS = 16;
+
+struct B3 {
+    float mn[3], mx[3];
+    void reset() { for (int a = 0; a < 3; a++) { mn[a] = FLT_MAX; mx[a] = -FLT_MAX; } }
+    void grow(const B3 &o) { for (int a = 0; a < 3; a++) { mn[a] = std::min(mn[a], o.mn[a]); mx[a] = std::max(mx[a], o.mx[a]); } }
+    void grow_point(const float *p) { for (int a = 0; a < 3; a++) { mn[a] = std::min(mn[a], p[a]); mx[a] = std::max(mx[a], p[a]); } }
+    float area() const {
+        const float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+        return dx < 0 ? 0.f : 2.f * (dx * dy + dx * dz + dy * dz);
+    }
+};
+
+struct Bins {
+    B3 box[3][BINS];       // triangle bounds per bin
+    B3 cbox[3][BINS];      // centroid bounds per bin (become the children's binning ranges)
+    uint32_t cnt[3][BINS];
+    void reset() { for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) { box[a][b].reset(); cbox[a][b].reset(); cnt[a][b] = 0; } }
+    void merge(const Bins &o) {
+        for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) { box[a][b].grow(o.box[a][b]); cbox[a][b].grow(o.cbox[a][b]); cnt[a][b] += o.cnt[a][b]; }
+    }
+};
+
+// Bounds a node is created with: its triangles' box and its centroids' box (both known from the parent's bins).
+struct NodeBounds { B3 nb, cb; };
+
+struct Ctx {
+    const B3 *box;
+    const float *cen;      // 3 per triangle
+    uint32_t *order;
+    int leaf_max;
+    float trav;
+    unsigned threads;
+};
+
+inline int bin_of(float c, float lo, float k) { return std::min(BINS - 1, (int)((c - lo) * k)); }
+
+// Bounds of the triangles and of their centroids over order[first, last).
+inline void bounds(const Ctx &c, uint32_t first, uint32_t last, B3 &nb, B3 &cb) {
+    nb.reset(); cb.reset();
+    for (uint32_t i = first; i < last; i++) {
+        const uint32_t t = c.order[i];
+        nb.grow(c.box[t]);
+        cb.grow_point(c.cen + (size_t)t * 3);
+    }
+}
+
+inline void bin_range(const Ctx &c, uint32_t first, uint32_t last, const B3 &cb, const float *k, Bins &bins) {
+    for (uint32_t i = first; i < last; i++) {
+        const uint32_t t = c.order[i];
+        for (int a = 0; a < 3; a++) {
+            if (!(k[a] > 0.f)) continue;
+            const int b = bin_of(c.cen[(size_t)t * 3 + a], cb.mn[a], k[a]);
+            bins.box[a][b].grow(c.box[t]);
+            bins.cbox[a][b].grow_point(c.cen + (size_t)t * 3);
+            bins.cnt[a][b]++;
         }
+    }
+}
+
+// Chooses the split of one node and partitions order[first, last).  Returns mid, or 0 for "make a leaf".
+// `in` holds the node's bounds (from its parent's bins); `kids` receives the children's.
+// `parallel` spreads the binning over the host cores (used for the large nodes at the top).
+inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds &in, NodeBounds kids[2], bool parallel) {
+    const uint32_t first = node.first, last = node.last, count = last - first;
+    const B3 &nb = in.nb, &cb = in.cb;
+    const unsigned nt = parallel ? c.threads : 1;
+    for (int a = 0; a < 3; a++) { node.aabb_min[a] = nb.mn[a]; node.aabb_max[a] = nb.mx[a]; }
+    if (count <= 1) return 0;
+    float k[3];
+    bool any_axis = false;
+    for (int a = 0; a < 3; a++) {
+        const float ext = cb.mx[a] - cb.mn[a];
+        k[a] = ext > 0.f ? (float)BINS / ext : 0.f;
+        any_axis = any_axis || k[a] > 0.f;
+    }
+    auto halves = [&](uint32_t m) {     // no usable bins: split by index and measure the halves
+        bounds(c, first, m, kids[0].nb, kids[0].cb);
+        bounds(c, m, last, kids[1].nb, kids[1].cb);
+        return m;
     };
+    if (!any_axis) return count <= 15 ? 0 : halves(first + count / 2);      // identical centroids
+    Bins bins;
+    bins.reset();
+    if (nt > 1) {
+        std::vector<Bins> part(nt);
+        std::vector<std::thread> pool;
+        const uint32_t chunk = (count + nt - 1) / nt;
+        for (unsigned t = 0; t < nt; t++)
+            pool.emplace_back([&, t] {
+                part[t].reset();
+                bin_range(c, std::min(last, first + t * chunk), std::min(last, first + (t + 1) * chunk), cb, k, part[t]);
+            });
+        for (auto &th : pool) th.join();
+        for (unsigned t = 0; t < nt; t++) bins.merge(part[t]);
+    } else {
+        bin_range(c, first, last, cb, k, bins);
+    }
+    float best_cost = FLT_MAX;
+    int best_axis = -1, best_bin = 0;
+    for (int a = 0; a < 3; a++) {
+        if (!(k[a] > 0.f)) continue;
+        float right_area[BINS];
+        uint32_t right_cnt[BINS];
+        B3 acc;
+        acc.reset();
+        uint32_t n = 0;
+        for (int b = BINS - 1; b > 0; b--) { acc.grow(bins.box[a][b]); n += bins.cnt[a][b]; right_area[b] = acc.area(); right_cnt[b] = n; }
+        acc.reset(); n = 0;
+        for (int b = 0; b < BINS - 1; b++) {
+            acc.grow(bins.box[a][b]); n += bins.cnt[a][b];
+            if (n == 0 || right_cnt[b + 1] == 0) continue;
+            const float cost = acc.area() * (float)n + right_area[b + 1] * (float)right_cnt[b + 1];
+            if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
+        }
+    }
+    if (best_axis < 0) return count <= 15 ? 0 : halves(first + count / 2);
+    // SAH: one box step costs `trav` triangle tests
+    if (count <= (uint32_t)c.leaf_max && best_cost + c.trav * nb.area() >= nb.area() * (float)count) return 0;
+    const float lo = cb.mn[best_axis], kk = k[best_axis];
+    auto it = std::partition(c.order + first, c.order + last,
+                             [&](uint32_t t) { return bin_of(c.cen[(size_t)t * 3 + best_axis], lo, kk) <= best_bin; });
+    const uint32_t mid = (uint32_t)(it - c.order);
+    if (mid == first || mid == last) return halves(first + count / 2);
+    for (int h = 0; h < 2; h++) { kids[h].nb.reset(); kids[h].cb.reset(); }
+    for (int b = 0; b < BINS; b++) {
+        NodeBounds &k2 = kids[b <= best_bin ? 0 : 1];
+        k2.nb.grow(bins.box[best_axis][b]);
+        k2.cb.grow(bins.cbox[best_axis][b]);
+    }
+    return mid;
+}
+
+// Serial build of the subtree under nodes[root_id] (first/last set, bounds in `root`).  Descendants are
+// written to nodes[slot, slot + 2 * count): the caller reserves that range, so workers never touch the
+// same elements; unused slots stay zero (empty leaves nobody points to).
+inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id, uint32_t slot, const NodeBounds &root) {
+    struct Item { uint32_t id; NodeBounds b; };
+    std::vector<Item> todo;
+    todo.push_back({root_id, root});
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        const uint32_t first = nodes[it.id].first, last = nodes[it.id].last;
+        NodeBounds kids[2];
+        const uint32_t mid = split_node(c, nodes[it.id], it.b, kids, false);
+        if (!mid) continue;
+        const uint32_t l = slot;
+        slot += 2;
+        nodes[l] = b200rt_bvh_node{};
+        nodes[l].first = first; nodes[l].last = mid;
+        nodes[l + 1] = b200rt_bvh_node{};
+        nodes[l + 1].first = mid; nodes[l + 1].last = last;
+        nodes[it.id].left = l; nodes[it.id].right = l + 1;
+        todo.push_back({l + 1, kids[1]});
+        todo.push_back({l, kids[0]});
+    }
+}
+
+}  // namespace bvh_detail
+
+inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBvh &out) {
+    using namespace bvh_detail;
     out.nodes.clear();
     out.order.resize((size_t)std::max(n, 0));
     if (n <= 0) return;
-    std::vector<B3> box((size_t)n);
-    std::vector<float> cen((size_t)n * 3);
-    for (int i = 0; i < n; i++) {
-        B3 &b = box[(size_t)i];
-        for (int a = 0; a < 3; a++) {
-            b.mn[a] = std::min(tris[i].p[2][a], std::min(tris[i].p[0][a], tris[i].p[1][a]));
-            b.mx[a] = std::max(tris[i].p[2][a], std::max(tris[i].p[0][a], tris[i].p[1][a]));
-            cen[(size_t)i * 3 + a] = 0.5f * (b.mn[a] + b.mx[a]);
-        }
-        out.order[(size_t)i] = (uint32_t)i;
+    Ctx c{};
+    c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
+    if (const char *e = getenv("B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
+    if (const char *e = getenv("B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
+    c.threads = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    if (n < 65536) c.threads = 1;
+    static_assert(sizeof(B3) == 6 * sizeof(float), "B3 is six floats");
+    out.scratch_box.resize((size_t)n * 6);
+    out.scratch_cen.resize((size_t)n * 3);
+    B3 *box = reinterpret_cast<B3 *>(out.scratch_box.data());
+    float *cen = out.scratch_cen.data();
+    {
+        auto prep = [&](size_t a, size_t b) {
+            for (size_t i = a; i < b; i++) {
+                B3 &bx = box[i];
+                for (int k = 0; k < 3; k++) {
+                    bx.mn[k] = std::min(tris[i].p[2][k], std::min(tris[i].p[0][k], tris[i].p[1][k]));
+                    bx.mx[k] = std::max(tris[i].p[2][k], std::max(tris[i].p[0][k], tris[i].p[1][k]));
+                    cen[i * 3 + k] = 0.5f * (bx.mn[k] + bx.mx[k]);
+                }
+                out.order[i] = (uint32_t)i;
+            }
+        };
+        if (c.threads > 1) {
+            std::vector<std::thread> pool;
+            const size_t chunk = ((size_t)n + c.threads - 1) / c.threads;
+            for (unsigned t = 0; t < c.threads; t++) pool.emplace_back(prep, std::min((size_t)n, t * chunk), std::min((size_t)n, (t + 1) * chunk));
+            for (auto &th : pool) th.join();
+        } else prep(0, (size_t)n);
     }
-    out.nodes.reserve((size_t)n * 2);
-    b200rt_bvh_node root{};
-    root.first = 0; root.last = (uint32_t)n;
-    out.nodes.push_back(root);
-    std::vector<uint32_t> todo(1, 0u);
-    while (!todo.empty()) {
-        const uint32_t id = todo.back();
-        todo.pop_back();
-        const uint32_t first = out.nodes[id].first, last = out.nodes[id].last, count = last - first;
-        B3 nb, cb;
-        nb.reset(); cb.reset();
-        for (uint32_t i = first; i < last; i++) {
-            const uint32_t t = out.order[i];
-            nb.grow(box[t]);
-            for (int a = 0; a < 3; a++) { cb.mn[a] = std::min(cb.mn[a], cen[(size_t)t * 3 + a]); cb.mx[a] = std::max(cb.mx[a], cen[(size_t)t * 3 + a]); }
+    c.box = box; c.cen = cen; c.order = out.order.data();
+
+    // Node slots: 0 = root; a node with `count` triangles owns at most 2 * count - 2 descendants.  The top of
+    // the tree takes slots from a shared cursor; a subtree task gets a private range up front.
+    std::vector<b200rt_bvh_node> &nodes = out.nodes;
+    const uint32_t top_cap = c.threads > 1 ? 4096u : 1u;      // slots [0, top_cap): root and the nodes split in phases A / B
+    nodes.assign((size_t)top_cap + (size_t)n * 2 + 2, b200rt_bvh_node{});
+    nodes[0].first = 0; nodes[0].last = (uint32_t)n;
+    // root bounds: the only full bounds pass (children get theirs from their parent's bins)
+    NodeBounds rb;
+    if (c.threads > 1) {
+        std::vector<NodeBounds> part(c.threads);
+        std::vector<std::thread> pool;
+        const uint32_t chunk = ((uint32_t)n + c.threads - 1) / c.threads;
+        for (unsigned t = 0; t < c.threads; t++)
+            pool.emplace_back([&, t] { bounds(c, std::min((uint32_t)n, t * chunk), std::min((uint32_t)n, (t + 1) * chunk), part[t].nb, part[t].cb); });
+        for (auto &th : pool) th.join();
+        rb.nb.reset(); rb.cb.reset();
+        for (auto &pb : part) { rb.nb.grow(pb.nb); rb.cb.grow(pb.cb); }
+    } else {
+        bounds(c, 0, (uint32_t)n, rb.nb, rb.cb);
+    }
+    auto shrink = [&] {        // drop the unused tail (slots in the middle stay as unreferenced empty leaves)
+        size_t used = nodes.size();
+        while (used > 1 && nodes[used - 1].left == 0 && nodes[used - 1].first == nodes[used - 1].last) used--;
+        nodes.resize(used);
+    };
+    if (c.threads == 1) { build_subtree(c, nodes.data(), 0, top_cap, rb); shrink(); return; }
+
+    // phase A: the few very large nodes at the top, one by one, with the binning spread over the cores
+    const uint32_t big = 65536, task_size = (uint32_t)std::max(1024, n / (int)(c.threads * 16));
+    // the bounds of the nodes created in phases A and B live in `nbs` (same index as `nodes`)
+    uint32_t cursor = 1;
+    std::vector<NodeBounds> nbs((size_t)top_cap, rb);
+    std::vector<uint32_t> queue(1, 0u);
+    auto add_children = [&](uint32_t id, uint32_t first, uint32_t mid, uint32_t last, const NodeBounds kids[2]) {
+        const uint32_t l = cursor;
+        cursor += 2;
+        nodes[l].first = first; nodes[l].last = mid; nbs[l] = kids[0];
+        nodes[l + 1].first = mid; nodes[l + 1].last = last; nbs[l + 1] = kids[1];
+        nodes[id].left = l; nodes[id].right = l + 1;
+        queue.push_back(l + 1);
+        queue.push_back(l);
+    };
+    for (bool again = true; again;) {
+        again = false;
+        for (size_t q = 0; q < queue.size(); q++) {
+            const uint32_t id = queue[q];
+            if (nodes[id].last - nodes[id].first <= big || cursor + 2 > top_cap) continue;
+            queue.erase(queue.begin() + (long)q);
+            const uint32_t first = nodes[id].first, last = nodes[id].last;
+            NodeBounds kids[2];
+            const uint32_t mid = split_node(c, nodes[id], nbs[id], kids, true);
+            if (mid) add_children(id, first, mid, last, kids);
+            again = true;
+            break;
         }
-        for (int a = 0; a < 3; a++) { out.nodes[id].aabb_min[a] = nb.mn[a]; out.nodes[id].aabb_max[a] = nb.mx[a]; }
-        if (count <= 1) continue;
-        // best binned split over the three axes
-        float best_cost = FLT_MAX;
-        int best_axis = -1, best_bin = 0;
-        for (int a = 0; a < 3; a++) {
-            const float ext = cb.mx[a] - cb.mn[a];
-            if (!(ext > 0.f)) continue;
-            const float k = (float)BINS / ext;
-            B3 bb[BINS];
-            uint32_t bc[BINS] = {};
-            for (int b = 0; b < BINS; b++) bb[b].reset();
-            for (uint32_t i = first; i < last; i++) {
-                const uint32_t t = out.order[i];
-                const int b = std::min(BINS - 1, (int)((cen[(size_t)t * 3 + a] - cb.mn[a]) * k));
-                bb[b].grow(box[t]); bc[b]++;
-            }
-            float right_area[BINS];
-            uint32_t right_cnt[BINS];
-            B3 acc; acc.reset();
-            uint32_t c = 0;
-            for (int b = BINS - 1; b > 0; b--) { acc.grow(bb[b]); c += bc[b]; right_area[b] = acc.area(); right_cnt[b] = c; }
-            acc.reset(); c = 0;
-            for (int b = 0; b < BINS - 1; b++) {
-                acc.grow(bb[b]); c += bc[b];
-                if (c == 0 || right_cnt[b + 1] == 0) continue;
-                const float cost = acc.area() * (float)c + right_area[b + 1] * (float)right_cnt[b + 1];
-                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
-            }
-        }
-        uint32_t mid;
-        if (best_axis < 0) {
-            if (count <= 15) continue;                 // identical centroids: a leaf the flattener can store
-            mid = first + count / 2;
-        } else {
-            if (count <= LEAF_MAX && best_cost >= nb.area() * (float)count) continue;
-            const float k = (float)BINS / (cb.mx[best_axis] - cb.mn[best_axis]);
-            const float lo = cb.mn[best_axis];
-            auto it = std::partition(out.order.begin() + first, out.order.begin() + last, [&](uint32_t t) {
-                return std::min(BINS - 1, (int)((cen[(size_t)t * 3 + best_axis] - lo) * k)) <= best_bin;
+    }
+    // phase B: a shared work queue; a worker either splits a medium node (children go back to the queue)
+    // or builds a small node's whole subtree into a slot range of its own.  Subtree ranges are handed out
+    // from the END of the array downwards so that they never meet the cursor of the top nodes.
+    std::mutex mu;
+    int inflight = 0;
+    uint32_t tail = (uint32_t)nodes.size();
+    {
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < c.threads; t++)
+            pool.emplace_back([&] {
+                for (;;) {
+                    uint32_t id, slot = 0;
+                    NodeBounds mine;
+                    bool whole;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        if (queue.empty()) {
+                            if (inflight == 0) return;
+                            lk.unlock();
+                            std::this_thread::yield();
+                            continue;
+                        }
+                        id = queue.back();
+                        queue.pop_back();
+                        mine = nbs[id];
+                        const uint32_t count = nodes[id].last - nodes[id].first;
+                        whole = count <= task_size || cursor + 2 > top_cap;     // top slots exhausted: finish serially
+                        if (whole) { tail -= 2 * count; slot = tail; }
+                        inflight++;
+                    }
+                    const uint32_t first = nodes[id].first, last = nodes[id].last;
+                    if (whole) {
+                        build_subtree(c, nodes.data(), id, slot, mine);
+                        std::lock_guard<std::mutex> lk(mu);
+                        inflight--;
+                    } else {
+                        b200rt_bvh_node nd = nodes[id];
+                        NodeBounds kids[2];
+                        const uint32_t mid = split_node(c, nd, mine, kids, false);
+                        std::lock_guard<std::mutex> lk(mu);
+                        for (int a = 0; a < 3; a++) { nodes[id].aabb_min[a] = nd.aabb_min[a]; nodes[id].aabb_max[a] = nd.aabb_max[a]; }
+                        if (mid) add_children(id, first, mid, last, kids);
+                        inflight--;
+                    }
+                }
             });
-            mid = (uint32_t)(it - out.order.begin());
-            if (mid == first || mid == last) mid = first + count / 2;
-        }
-        const uint32_t l = (uint32_t)out.nodes.size();
-        b200rt_bvh_node child{};
-        child.first = first; child.last = mid;
-        out.nodes.push_back(child);
-        child.first = mid; child.last = last;
-        out.nodes.push_back(child);
-        out.nodes[id].left = l; out.nodes[id].right = l + 1;
-        todo.push_back(l + 1);
-        todo.push_back(l);
+        for (auto &th : pool) th.join();
     }
+    shrink();
 }
 
 }  // namespace b200rt

@@ -101,6 +101,23 @@ def test_gltf_matches_port_on_same_stream(renderer, path, frac):
     assert st["paths"] == 128 * 96 * 16
 
 
+def test_reference_tree_and_rebuilt_tree_agree():
+    """FLAG_REFERENCE_BVH traverses the description's SAH tree, the default the library's own binned-SAH
+    tree over the same triangles: same closest hits (ties aside) => same image on the same stream."""
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=8)
+    imgs, rays = [], []
+    for flags in (0, rt.FLAG_REFERENCE_BVH):
+        r = rt.Renderer(flags=flags)
+        r.upload(sc)
+        r.render(0, 8)
+        imgs.append(r.download_accum().astype(np.float64))
+        rays.append(int(r.stats()["rays"]))
+        r.close()
+    assert abs(rays[0] - rays[1]) <= 1e-3 * rays[1]
+    close = np.abs(imgs[0] - imgs[1]).max(axis=2) <= 1e-3 * np.maximum(1.0, imgs[1].max(axis=2))
+    assert close.mean() >= 0.995, close.mean()
+
+
 @pytest.mark.parametrize("path,frac", [("hw7/practice7_1.gltf", 0.85), ("hw6/practice7_1_glass.gltf", 0.85)])
 def test_hw6_matches_port_on_same_stream(renderer, path, frac):
     """hw6 mode (hw5 integrator on triangles; the device traverses its own binned-SAH tree, the port the
