@@ -226,6 +226,8 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    if world > 1:   # one process per GPU on one host: share the cores for the host side of the upload
+        os.environ.setdefault("B200RT_HOST_THREADS", str(max(2, min(16, (os.cpu_count() or 16) // world))))
     torch.cuda.set_device(local)
     dist = None
     if world > 1:

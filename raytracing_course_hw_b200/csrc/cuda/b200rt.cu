@@ -64,7 +64,8 @@ struct b200rt_ctx {
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
-    int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T, wf_blocks_cap = 0;
+    int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T_LIGHT, wf_blocks_cap = 0;
+    int wf_batch_light = B200RT_WF_BATCH_LIGHT;
     b200rt_stats stats{};
     bool timing_pending = false;
     // per-stage timing of the wavefront: event pairs (begin, end, stage) recorded around launches
@@ -99,8 +100,7 @@ int fail(b200rt_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess)
 // Runs f(begin, end) over [0, n) on the host cores (record building is embarrassingly parallel).
 template <class F>
 void parallel_for(size_t n, const F &f) {
-    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const unsigned nt = (unsigned)std::min<size_t>({(size_t)hw, (size_t)16, (n + 16383) / 16384});
+    const unsigned nt = (unsigned)std::min<size_t>((size_t)host_threads(), (n + 16383) / 16384);
     if (nt <= 1) { f((size_t)0, n); return; }
     const size_t chunk = (n + nt - 1) / nt;
     std::vector<std::thread> pool;
@@ -442,12 +442,27 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         lap("rebuild BVH");
     }
 
+    // the light set keeps the reference's ORDER for sampling (light_sample_tris); its traversal tree is
+    // rebuilt like the scene's, over a permuted copy (the pdf sum visits every pierced box: tree quality = cost)
+    RebuiltBvh light_own;
+    std::vector<b200rt_triangle> light_perm;
+    const b200rt_triangle *ltri_src = s->light_tris;
+    const b200rt_bvh_node *lnode_src = s->light_nodes;
+    int n_lnodes = s->n_light_nodes;
+    if (rebuild && s->n_light_tris > 0) {
+        rebuild_bvh_binned_sah(s->light_tris, s->n_light_tris, light_own, true);
+        light_perm.resize((size_t)s->n_light_tris);
+        for (int i = 0; i < s->n_light_tris; i++) light_perm[(size_t)i] = s->light_tris[light_own.order[(size_t)i]];
+        ltri_src = light_perm.data();
+        lnode_src = light_own.nodes.data(); n_lnodes = (int)light_own.nodes.size();
+    }
+
     // 1. plan both trees (serial pass each); a leaf above 15 triangles needs the recursive splitter
     Flattener fl, ll;
     const bool fast_scene = fl.plan(s->nodes, s->n_nodes, s->root, s->n_tris);
     if (!fast_scene) fl.run(s->nodes, s->n_nodes, s->root, s->tris, s->n_tris);
-    const bool fast_light = ll.plan(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris);
-    if (!fast_light) ll.run(s->light_nodes, s->n_light_nodes, 0, s->light_tris, s->n_light_tris);
+    const bool fast_light = ll.plan(lnode_src, n_lnodes, 0, s->n_light_tris);
+    if (!fast_light) ll.run(lnode_src, n_lnodes, 0, ltri_src, s->n_light_tris);
     if (fl.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "scene BVH deeper than the traversal stack");
     if (ll.max_depth > B200RT_STACK) return fail(ctx, B200RT_ERR_STACK, "light BVH deeper than the traversal stack");
     const size_t n_pairs = std::max<size_t>(1, fast_scene ? fl.n_inner : fl.out.size());
@@ -460,6 +475,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     auto take = [&](size_t bytes) { const size_t o = off; off = align256(off + std::max<size_t>(bytes, 16)); return o; };
     const size_t o_nodes = take(n_pairs * sizeof(DPair)), o_tris = take(nt * sizeof(DTri)), o_shade = take(nt * sizeof(DShade));
     const size_t o_lnodes = take(n_lpairs * sizeof(DPair)), o_ltris = take(nl * sizeof(DTri)), o_lnorm = take(nl * sizeof(DLightNormals));
+    const size_t o_lsample = take(nl * sizeof(DTri));
     const size_t o_mats = take(nm * sizeof(DMaterial)), o_lut = take(256 * sizeof(float));
     if ((rc = ensure_arena(ctx, off))) return rc;
     char *pin = ctx->arena_pin, *dev = ctx->arena_dev;
@@ -498,20 +514,25 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     // lights: FiguresMix::figures_ + its BVH (hw8/src/include/distributions.h:99-115)
     g.n_light_tris = s->n_light_tris;
     DPair *lpairs = reinterpret_cast<DPair *>(pin + o_lnodes);
-    if (fast_light) { if (ll.n_inner) ll.fill(s->n_light_nodes, lpairs); else lpairs[0] = DPair{}; }
+    if (fast_light) { if (ll.n_inner) ll.fill(n_lnodes, lpairs); else lpairs[0] = DPair{}; }
     else memcpy(lpairs, ll.out.data(), ll.out.size() * sizeof(DPair));
     g.light_root = ll.root_word; g.lq = ll.q;
     for (int k = 0; k < 3; k++) { g.light_min[k] = ll.root_box.mn[k]; g.light_max[k] = ll.root_box.mx[k]; }
     DTri *ltris = reinterpret_cast<DTri *>(pin + o_ltris);
     DLightNormals *lnorm = reinterpret_cast<DLightNormals *>(pin + o_lnorm);
-    for (size_t i = 0; i < nl; i++) {
-        const b200rt_triangle &t = s->light_tris[i];
-        ltris[i] = make_tri(t);
+    DTri *lsample = reinterpret_cast<DTri *>(pin + o_lsample);
+    auto light_record = [](const b200rt_triangle &t, DTri &d) {
+        d = make_tri(t);
         // pointProb = 1.0 / (0.5 * |b.cross(c)|) in the reference's float/double mix (distributions.h:71-76)
-        float bx = ltris[i].e1.x, by = ltris[i].e1.y, bz = ltris[i].e1.z, cx = ltris[i].e2.x, cy = ltris[i].e2.y, cz = ltris[i].e2.z;
+        float bx = d.e1.x, by = d.e1.y, bz = d.e1.z, cx = d.e2.x, cy = d.e2.y, cz = d.e2.z;
         float nx = bz * cy - by * cz, ny = bx * cz - bz * cx, nz = by * cx - bx * cy;
         float len = (float)std::sqrt((double)(nx * nx + ny * ny + nz * nz));
-        ltris[i].v0.w = (float)(1.0 / (0.5 * len));
+        d.v0.w = (float)(1.0 / (0.5 * len));
+    };
+    for (size_t i = 0; i < nl; i++) {
+        const b200rt_triangle &t = ltri_src[i];
+        light_record(t, ltris[i]);
+        light_record(s->light_tris[i], lsample[i]);
         lnorm[i].n0 = make_float4(t.n[0][0], t.n[0][1], t.n[0][2], 0);
         lnorm[i].n1 = make_float4(t.n[1][0], t.n[1][1], t.n[1][2], 0);
         lnorm[i].n2 = make_float4(t.n[2][0], t.n[2][1], t.n[2][2], 0);
@@ -559,6 +580,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     g.light_nodes = reinterpret_cast<const DPair *>(dev + o_lnodes);
     g.light_tris = reinterpret_cast<const DTri *>(dev + o_ltris);
     g.light_normals = reinterpret_cast<const DLightNormals *>(dev + o_lnorm);
+    g.light_sample_tris = reinterpret_cast<const DTri *>(dev + o_lsample);
     g.materials = reinterpret_cast<const DMaterial *>(dev + o_mats);
     ctx->lut_srgb = reinterpret_cast<float *>(dev + o_lut);
     ctx->gs = g;
@@ -692,7 +714,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t_light);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
@@ -754,6 +776,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     ctx->flags = opt ? opt->flags : 0;
     // tuning knobs (development only; defaults are the measured optimum)
     if (const char *e = getenv("B200RT_WF_BATCH")) ctx->wf_batch = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_WF_BATCH_LIGHT")) ctx->wf_batch_light = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T")) ctx->wf_leaf_t = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_LEAF_T_LIGHT")) ctx->wf_leaf_t_light = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_STAGE_TIMING")) ctx->stage_timing = atoi(e) != 0;

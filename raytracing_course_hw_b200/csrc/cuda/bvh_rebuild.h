@@ -32,6 +32,14 @@ struct RebuiltBvh {
     std::vector<float> scratch_box, scratch_cen;
 };
 
+// Host threads one context may use for record building and the BVH rebuild: min(16, cores), or
+// B200RT_HOST_THREADS (one process per GPU on a shared host: cores / GPUs avoids oversubscription).
+inline unsigned host_threads() {
+    unsigned n = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    if (const char *e = getenv("B200RT_HOST_THREADS")) n = (unsigned)std::max(1, std::min(64, atoi(e)));
+    return n;
+}
+
 namespace bvh_detail {
 
 constexpr int BINS = 16;
@@ -195,16 +203,16 @@ inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id
 
 }  // namespace bvh_detail
 
-inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBvh &out) {
+inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBvh &out, bool light_set = false) {
     using namespace bvh_detail;
     out.nodes.clear();
     out.order.resize((size_t)std::max(n, 0));
     if (n <= 0) return;
     Ctx c{};
     c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
-    if (const char *e = getenv("B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
-    if (const char *e = getenv("B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
-    c.threads = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    if (const char *e = getenv(light_set ? "B200RT_REBUILD_LEAF_LIGHT" : "B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
+    if (const char *e = getenv(light_set ? "B200RT_REBUILD_TRAV_LIGHT" : "B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
+    c.threads = host_threads();
     if (n < 65536) c.threads = 1;
     static_assert(sizeof(B3) == 6 * sizeof(float), "B3 is six floats");
     out.scratch_box.resize((size_t)n * 6);

@@ -75,7 +75,8 @@ struct DGltfScene {
     const DTri *tris;
     const DShade *shade;
     const DPair *light_nodes;
-    const DTri *light_tris;
+    const DTri *light_tris;          // emissive triangles in the order of the light BVH's leaves (traversal)
+    const DTri *light_sample_tris;   // the same triangles in FiguresMix::figures_ order (the index a random number picks)
     const DLightNormals *light_normals;
     const DMaterial *materials;
     int32_t n_light_tris;

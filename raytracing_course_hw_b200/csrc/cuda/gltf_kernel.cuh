@@ -465,7 +465,7 @@ __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float 
     } else if (which == 2) {
         // FiguresMix::sample (:117-120) + TriangleLight::sample (:81-94): draws = index, u, v
         const int li = min((int)(r1 * (float)sc.n_light_tris), sc.n_light_tris - 1);
-        const float4 *lq = reinterpret_cast<const float4 *>(sc.light_tris + li);
+        const float4 *lq = reinterpret_cast<const float4 *>(sc.light_sample_tris + li);
         const float4 a = __ldg(lq), b = __ldg(lq + 1), c = __ldg(lq + 2);
         float lu = r2, lv = r3;
         if (lu + lv > 1.f) { lu = 1.f - lu; lv = 1.f - lv; }

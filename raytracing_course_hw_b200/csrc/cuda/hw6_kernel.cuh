@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(128) hw6_path_kernel(const DGltfScene sc, cons
                         } else {
                             // FiguresMix::sample + TriangleLight::sample: draws = index, u, v
                             const int li = min((int)(u01(rnd.y) * (float)n_lights), n_lights - 1);
-                            const float4 *lq = reinterpret_cast<const float4 *>(sc.light_tris + li);
+                            const float4 *lq = reinterpret_cast<const float4 *>(sc.light_sample_tris + li);
                             const float4 a = __ldg(lq), b = __ldg(lq + 1), c = __ldg(lq + 2);
                             float lu = u01(rnd.z), lv = u01(rnd.w);
                             if (lu + lv > 1.f) { lu = 1.f - lu; lv = 1.f - lv; }

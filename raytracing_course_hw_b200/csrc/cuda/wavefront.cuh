@@ -21,6 +21,8 @@
 namespace b200rt {
 
 #define B200RT_WF_BATCH 16       /* traversal steps between refills (sweep: profiles/r01_sweep_wf.log) */
+#define B200RT_WF_BATCH_LIGHT 16 /* same for the light-pdf traversal */
+#define B200RT_WF_LEAF_T_LIGHT 24 /* light-pdf traversal: leaves are rare and dear, wait for a fuller warp (profiles/r01_sweep_light.log) */
 #define B200RT_WF_LEAF_T 8       /* lanes waiting at a leaf that trigger a leaf phase */
 #ifndef B200RT_EXT_MINB
 #define B200RT_EXT_MINB 9        /* min resident blocks per SM asked of ptxas for extend / light (sweep: profiles/r01_sweep_quantised_nodes.log) */
