@@ -63,6 +63,7 @@ struct b200rt_ctx {
     int num_sms = 0;
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
+    bool wf_direct = true;       // shade finishes bounces whose ray misses the light root box (no light-stage entry)
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T_LIGHT, wf_blocks_cap = 0;
     int wf_batch_light = B200RT_WF_BATCH_LIGHT;
@@ -699,7 +700,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                 wf_trace<COUNT><<<ctx->blocks_trace[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, b > 0 ? 1 : 0);
                 ctx->stamp(false, 0, st);
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, c + 4, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, c + 4, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
                 std::swap(qa, qb);
@@ -711,7 +712,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             const bool last = b == rp.ray_depth - 1;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 4, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
                 wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light);
@@ -720,7 +721,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }
@@ -782,6 +783,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_STAGE_TIMING")) ctx->stage_timing = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_DIRECT")) ctx->wf_direct = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
     if (ctx->flags & B200RT_FLAG_SERIAL_WAVES) ctx->wf_pipe = 1;
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));

@@ -276,9 +276,13 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 }
 
 // ---- shade --------------------------------------------------------------------------------------
+// The counting instantiation gets a looser register cap: squeezed to 128 registers it needs spills, and that
+// build was observed on B200 to shade ~0.1 % of the hits per bounce differently from the plain one (and not
+// reproducibly).  With the cap lifted both instantiations and the megakernel agree bit for bit
+// (test_counting_build_renders_the_same_image); the counting build is a measurement aid, its speed is irrelevant.
 template <bool HW8, bool COUNT>
-__global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
-                                                const int *__restrict__ n_in, int *q_out, int *n_out, int bounce,
+__global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
+                                                const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
                                                 const float *__restrict__ lut_srgb_g, DCounters *counters) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
@@ -292,9 +296,10 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfSc
     const int lane = threadIdx.x & 31;
     const bool has_lights = sc.n_light_tris > 0;
     ThreadCounters tc = {};
+    unsigned answered = 0;      // light queries answered here by the root box (they stay light queries in the stats)
     for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n; base += warps * 32) {
         const int i = base + lane;
-        bool cont = false;
+        bool cont = false, direct = false;
         int p = 0;
         if (i < n) {
             p = __ldcs(q_in + i);
@@ -321,16 +326,36 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINB) wf_shade(const DGltfSc
                 BounceOut bo;
                 cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, (int)(bits & 0x7FFFFFFFu), (bits >> 31) != 0, L, T, rnd, tc, bo);
                 if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
+                if (cont && has_lights && q_direct) {
+                    // A ray that misses the box around all emitters has a light pdf of exactly 0
+                    // (light_pdf_sum's root filter): the bounce is finished here and the path skips
+                    // the light stage (its queue entry, bsdf round trip and refill slot).
+                    float tn;
+                    if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
+                               bo.xo, mk(1.f / bo.nd.x, 1.f / bo.nd.y, 1.f / bo.nd.z), INFINITY, tn)) {
+                        if (COUNT) tc.light_node_tests++;
+                        answered++;
+                        direct = true;
+                        cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T);
+                        bo.pdf_partial = 0.f;
+                    }
+                }
                 if (cont) {
                     st_state(&wb.ray_o[p], make_float4(bo.xo.x, bo.xo.y, bo.xo.z, ro.w));
                     st_state(&wb.ray_d[p], make_float4(bo.nd.x, bo.nd.y, bo.nd.z, bo.absdot));
                     st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, bo.pdf_partial));
-                    if (has_lights) st_state(&wb.bsdf[p], make_float4(bo.brdf.x, bo.brdf.y, bo.brdf.z, 0.f));
+                    if (has_lights && !direct) st_state(&wb.bsdf[p], make_float4(bo.brdf.x, bo.brdf.y, bo.brdf.z, 0.f));
                 }
             }
             st_state(&wb.rad[p], make_float4(L.x, L.y, L.z, ra.w));
         }
-        queue_push(q_out, n_out, cont, p);
+        queue_push(q_out, n_out, cont && !direct, p);
+        if (q_direct) queue_push(q_direct, n_direct, cont && direct, p);
+    }
+    if (q_direct) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) answered += __shfl_down_sync(B200RT_FULL, answered, off);
+        if (lane == 0 && answered) atomicAdd(&counters->light_queries, (unsigned long long)answered);
     }
     if (COUNT) flush_counters(counters, tc);
 }

@@ -22,11 +22,13 @@ pytestmark = pytest.mark.gpu
 S, G = ou.SCENES, ou.GOLDEN
 
 
-@pytest.fixture(scope="module", params=["wavefront", "megakernel"])
+@pytest.fixture(scope="module", params=["wavefront", "wavefront-counting", "megakernel"])
 def renderer(request):
-    """Both schedulings of the glTF path tracer (K4w wavefront = default, K4 megakernel) run the
-    whole suite; the analytic kernels K1-K3 are the same under either flag."""
-    flags = rt.FLAG_COUNTERS | (rt.FLAG_MEGAKERNEL if request.param == "megakernel" else 0)
+    """The product build (K4w wavefront, no flags), its counting instantiation (FLAG_COUNTERS: what bench.py's
+    roofline bytes come from) and the K4 megakernel run the whole suite; the analytic kernels K1-K3 are the
+    same under every flag."""
+    flags = {"wavefront": 0, "wavefront-counting": rt.FLAG_COUNTERS,
+             "megakernel": rt.FLAG_COUNTERS | rt.FLAG_MEGAKERNEL}[request.param]
     r = rt.Renderer(flags=flags)
     r.megakernel = request.param == "megakernel"
     yield r
@@ -191,6 +193,40 @@ def test_resolve_edge_values(renderer):
     ramp[..., 1] = 1e6
     renderer.upload_accum(ramp)
     assert np.array_equal(renderer.resolve(1), ou.port_resolve(ramp, 1))
+
+
+def _room(tris=20000):
+    """Textured, normal-mapped, emissive synthetic room of the bench scene's family (tools/make_scene.py)."""
+    import sys
+    import tempfile
+    sys.path.insert(0, os.path.join(os.path.dirname(S), "..", "tools"))
+    import make_scene
+    d = os.path.join(tempfile.gettempdir(), f"b200rt_test_room_{tris}_{os.getuid()}")
+    if not os.path.exists(os.path.join(d, "b200room.gltf")):
+        make_scene.build(d, tris, 1)
+    return os.path.join(d, "b200room.gltf")
+
+
+def test_every_build_renders_the_same_image():
+    """Plain wavefront, counting wavefront, one wave in flight, and the megakernel evaluate the same
+    arithmetic on the same Philox stream: bit-identical radiance, and a second process-independent context
+    reproduces it (regression: a register-starved counting build of wf_shade once shaded ~0.1 % of the hits
+    of a bounce differently).  The port on the same stream bounds the absolute error."""
+    sc = rt.load_scene(_room(), width=320, height=180, samples=2)
+    imgs = {}
+    for name, flags in (("plain", 0), ("plain-again", 0), ("counting", rt.FLAG_COUNTERS), ("serial", rt.FLAG_SERIAL_WAVES),
+                        ("megakernel", rt.FLAG_MEGAKERNEL), ("megakernel-counting", rt.FLAG_MEGAKERNEL | rt.FLAG_COUNTERS)):
+        r = rt.Renderer(flags=flags)
+        try:
+            imgs[name] = _render(r, sc, 0, 2)
+        finally:
+            r.close()
+    for name, img in imgs.items():
+        assert np.array_equal(img, imgs["plain"]), (name, int((img != imgs["plain"]).any(axis=2).sum()))
+    port = ou.port_render(sc, 1)["accum"]
+    ok, frac = _mean_close(imgs["plain"], port, 2, 0.97, rel=5e-2)
+    assert ok, frac
+    assert abs(imgs["plain"].mean() - port.mean()) <= 1e-2 * port.mean()
 
 
 # ---------------------------------------------------------------- size-independent properties
