@@ -63,6 +63,7 @@ struct b200rt_ctx {
     int num_sms = 0;
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
+    int light_top_max = B200RT_LIGHT_TOP;  // boxes of the light-BVH cut used as the light-pdf pre-filter (0/1 = root box only)
     bool wf_direct = true;       // shade finishes bounces whose ray misses the light root box (no light-stage entry)
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T_LIGHT, wf_blocks_cap = 0;
@@ -403,6 +404,33 @@ int upload_textures(b200rt_ctx *ctx, const std::vector<const b200rt_image *> &im
     return B200RT_OK;
 }
 
+// Cut through the top of the light BVH: start at the root and keep replacing the inner node with the largest
+// surface area by its children until `want` boxes are open (or only leaves remain).
+void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, int want, DGltfScene &g) {
+    g.n_light_top = 0;
+    if (n_light_tris <= 0 || n_nodes <= 0 || want < 2) return;
+    want = std::min(want, B200RT_LIGHT_TOP);
+    auto area = [&](int i) {
+        const float dx = nodes[i].aabb_max[0] - nodes[i].aabb_min[0], dy = nodes[i].aabb_max[1] - nodes[i].aabb_min[1], dz = nodes[i].aabb_max[2] - nodes[i].aabb_min[2];
+        return dx * dy + dx * dz + dy * dz;
+    };
+    std::vector<int> open(1, 0);
+    while ((int)open.size() < want) {
+        int best = -1;
+        for (int k = 0; k < (int)open.size(); k++)
+            if (nodes[open[k]].left != 0 && (best < 0 || area(open[k]) > area(open[best]))) best = k;
+        if (best < 0) break;
+        const int id = open[best];
+        open[best] = (int)nodes[id].left;
+        open.push_back((int)nodes[id].right);
+    }
+    if (open.size() < 2) return;
+    for (int id : open) {
+        float *b = g.light_top[g.n_light_top++];
+        for (int k = 0; k < 3; k++) { b[k] = nodes[id].aabb_min[k]; b[3 + k] = nodes[id].aabb_max[k]; }
+    }
+}
+
 int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     if (s->n_tris < 0 || s->n_tris >= (1 << 27)) return fail(ctx, B200RT_ERR_INVALID, "triangle count out of range");
     if (s->n_tris > 0 && (!s->tris || !s->materials)) return fail(ctx, B200RT_ERR_INVALID, "missing triangle/material arrays");
@@ -519,6 +547,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     else memcpy(lpairs, ll.out.data(), ll.out.size() * sizeof(DPair));
     g.light_root = ll.root_word; g.lq = ll.q;
     for (int k = 0; k < 3; k++) { g.light_min[k] = ll.root_box.mn[k]; g.light_max[k] = ll.root_box.mx[k]; }
+    light_top_cut(lnode_src, n_lnodes, s->n_light_tris, ctx->light_top_max, g);
     DTri *ltris = reinterpret_cast<DTri *>(pin + o_ltris);
     DLightNormals *lnorm = reinterpret_cast<DLightNormals *>(pin + o_lnorm);
     DTri *lsample = reinterpret_cast<DTri *>(pin + o_lsample);
@@ -715,7 +744,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                 wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 4, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
@@ -784,6 +813,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_DIRECT")) ctx->wf_direct = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_LIGHT_TOP")) ctx->light_top_max = std::max(0, atoi(e));
     if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
     if (ctx->flags & B200RT_FLAG_SERIAL_WAVES) ctx->wf_pipe = 1;
     if (const char *e = getenv("B200RT_WF_BLOCKS_PER_SM")) ctx->wf_blocks_cap = std::max(0, atoi(e));

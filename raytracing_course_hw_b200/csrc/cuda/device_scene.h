@@ -70,6 +70,7 @@ struct DCamera {
     int32_t width, height;
 };
 
+#define B200RT_LIGHT_TOP 8
 struct DGltfScene {
     const DPair *nodes;
     const DTri *tris;
@@ -83,6 +84,10 @@ struct DGltfScene {
     uint32_t root, light_root;   // child word of each tree's root
     DQuant q, lq;                // quantisation grids of the scene BVH and the light BVH
     float light_min[3], light_max[3];   // root box of the light BVH (a real filter, unlike the scene's)
+    // a cut through the top of the light BVH (<= B200RT_LIGHT_TOP boxes covering every emitter): a ray that
+    // misses all of them has a light pdf of 0 -- the cheap pre-filter shade uses to skip the light stage
+    float light_top[B200RT_LIGHT_TOP][6];
+    int32_t n_light_top;
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
     float bg[3];
     cudaTextureObject_t env;     // 0 = absent

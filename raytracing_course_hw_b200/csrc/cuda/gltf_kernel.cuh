@@ -41,6 +41,22 @@ __device__ __forceinline__ bool slab6(float lx, float ly, float lz, float hx, fl
     return tmin <= tmax && tmax >= 0.f && tmin <= tbest;
 }
 
+// Light-pdf pre-filter: false when the ray (o, d) misses the light BVH's root box or every box of the cut
+// through its top levels (then FiguresMix::getTotalPdf is exactly 0: no pierced leaf box, distributions.h:122-165).
+// Every light-pdf evaluation (megakernel, hw6, wavefront shade / light stages) starts with this same test, so all
+// schedulings see the same set of non-zero queries.
+__device__ __forceinline__ bool light_boxes_hit(const DGltfScene &sc, const V3 o, const V3 d) {
+    const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    float tn;
+    if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2], o, inv, INFINITY, tn)) return false;
+    bool any = sc.n_light_top == 0;
+#pragma unroll
+    for (int k = 0; k < B200RT_LIGHT_TOP; k++)
+        if (k < sc.n_light_top)
+            any = any || slab6(sc.light_top[k][0], sc.light_top[k][1], sc.light_top[k][2], sc.light_top[k][3], sc.light_top[k][4], sc.light_top[k][5], o, inv, INFINITY, tn);
+    return any;
+}
+
 // A ray expressed on the 16-bit grid of a tree.  With o' = (o - base) / scale and inv' = scale / d the
 // ray parameter of a grid plane q is t = q * inv' - o' * inv' (same t as in world space): one FFMA.
 // The near/far plane of each axis is picked by the sign of d, and the constant terms carry a
@@ -186,12 +202,9 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
     uint32_t stack[B200RT_STACK];
     int sp = 0;
     float total = 0.f;
-    {   // unlike the scene root, the light root's box IS a real filter
-        float tn;
-        if (COUNT) tc.light_node_tests++;
-        if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
-                   o, mk(1.f / d.x, 1.f / d.y, 1.f / d.z), INFINITY, tn)) return 0.f;
-    }
+    // unlike the scene root, the light root's box IS a real filter
+    if (COUNT) tc.light_node_tests++;
+    if (!light_boxes_hit(sc, o, d)) return 0.f;
     const QRay qr = make_qray(sc.lq, o, d);
     uint32_t cur = sc.light_root;
     while (true) {

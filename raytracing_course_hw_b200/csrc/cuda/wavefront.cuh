@@ -330,9 +330,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                     // A ray that misses the box around all emitters has a light pdf of exactly 0
                     // (light_pdf_sum's root filter): the bounce is finished here and the path skips
                     // the light stage (its queue entry, bsdf round trip and refill slot).
-                    float tn;
-                    if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
-                               bo.xo, mk(1.f / bo.nd.x, 1.f / bo.nd.y, 1.f / bo.nd.z), INFINITY, tn)) {
+                    if (!light_boxes_hit(sc, bo.xo, bo.nd)) {
                         if (COUNT) tc.light_node_tests++;
                         answered++;
                         direct = true;
@@ -364,7 +362,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
 template <bool COUNT>
 __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters,
-                                                const int batch, const int leaf_t) {
+                                                const int batch, const int leaf_t, const bool filtered) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
     uint32_t stack[B200RT_STACK];
@@ -398,11 +396,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     qr = make_qray(sc.lq, o, d);
                     total = 0.f; sp = 0;
                     active = true;
-                    // the light root's box is a real filter (unlike the scene root)
-                    float tn;
+                    // the light root's box is a real filter (unlike the scene root); `filtered`: shade already
+                    // applied light_boxes_hit to every query in this queue
                     if (COUNT) node_tests++;
-                    if (slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
-                              o, mk(1.f / d.x, 1.f / d.y, 1.f / d.z), INFINITY, tn)) cur = sc.light_root;
+                    if (filtered || light_boxes_hit(sc, o, d)) cur = sc.light_root;
                     else cur = B200RT_LEAF;      // empty leaf: finishes on the next leaf phase
                 }
             }

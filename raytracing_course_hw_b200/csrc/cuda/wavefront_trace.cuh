@@ -123,10 +123,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_trace(const DGltfScen
                     if (do_light) {
                         // same ray against the light BVH; its root box is a real filter
                         light = true; total = 0.f;
-                        float tn;
                         if (COUNT) lnode_tests++;
-                        if (slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2],
-                                  o, mk(1.f / d.x, 1.f / d.y, 1.f / d.z), INFINITY, tn)) { qr = make_qray(sc.lq, o, d); cur = sc.light_root; }
+                        if (light_boxes_hit(sc, o, d)) { qr = make_qray(sc.lq, o, d); cur = sc.light_root; }
                         else cur = B200RT_LEAF;      // empty leaf: ends on the next leaf phase
                     } else active = false;
                 } else {
