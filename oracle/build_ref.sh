@@ -28,3 +28,13 @@ for n in 1 2 3 4 5 6 7 8; do
   fi
 done
 echo "build_ref: ok -> $OUT" >&2
+# Large example SCENES (data, not sources) for tools/config_sweep.py: BASELINE configs C4 name hw6/hw7 examples that are
+# too big for tests/scenes; they are staged next to the binaries (git-ignored, but they travel to the GPU box).
+mkdir -p "$OUT/scenes/hw6" "$OUT/scenes/hw7"
+for f in practice6_1 practice6_2; do
+  for e in gltf bin; do [ -f "$REF/hw6/examples/$f.$e" ] && cp -u "$REF/hw6/examples/$f.$e" "$OUT/scenes/hw6/"; done
+done
+for f in practice7_1 practice7_2 practice7_3 practice7_4; do
+  for e in gltf bin; do [ -f "$REF/hw7/examples/$f.$e" ] && cp -u "$REF/hw7/examples/$f.$e" "$OUT/scenes/hw7/"; done
+done
+echo "build_ref: example scenes staged -> $OUT/scenes" >&2

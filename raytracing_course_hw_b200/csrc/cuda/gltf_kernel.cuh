@@ -400,19 +400,33 @@ struct BounceOut {
     float absdot;           // |nd . n_shading|
 };
 
+// The per-triangle records shade_surface reads: intersection record (geometric normal, material id, tangent sign)
+// and shading record (normals, uv, tangents).  The megakernel fetches them from global memory; the wavefront's
+// shade stage has them staged in shared memory one item ahead (wavefront.cuh).
+struct SurfRec {
+    float4 tv0, te1, te2;
+    float4 s0, s1, s2, s3, s4, s5;     // s3..s5 only in hw8 mode
+};
+template <bool HW8>
+__device__ __forceinline__ void load_surf_rec(const DGltfScene &sc, int tri, SurfRec &r) {
+    const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + tri);
+    r.tv0 = __ldg(tq); r.te1 = __ldg(tq + 1); r.te2 = __ldg(tq + 2);
+    const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
+    r.s0 = __ldg(sq); r.s1 = __ldg(sq + 1); r.s2 = __ldg(sq + 2);
+    if (HW8) { r.s3 = __ldg(sq + 3); r.s4 = __ldg(sq + 4); r.s5 = __ldg(sq + 5); }
+}
+
 // Surface part: fetch the shading record, material and textures, add the emission to L, draw the
 // next direction from Mix{Cosine, Vndf, [lights]} and evaluate the BRDF.  Returns false when the
 // path ends here (BRDF below 1e-4 in every channel, scene.cpp:154-156).
 template <bool HW8, bool COUNT>
 __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float *lut_srgb, const float *lut_lin,
-                                              const V3 o, const V3 d, float t, float u, float v, int tri, bool inside,
+                                              const V3 o, const V3 d, float t, float u, float v, const SurfRec &rec, bool inside,
                                               V3 &L, const V3 T, const uint4 rnd, ThreadCounters &tc, BounceOut &out) {
-    const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + tri);
-    const float4 tv0 = __ldg(tq), te1 = __ldg(tq + 1), te2 = __ldg(tq + 2);
+    const float4 tv0 = rec.tv0, te1 = rec.te1, te2 = rec.te2;
     if (COUNT) tc.shaded++;
 
-    const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
-    const float4 s0 = __ldg(sq), s1 = __ldg(sq + 1), s2 = __ldg(sq + 2);
+    const float4 s0 = rec.s0, s1 = rec.s1, s2 = rec.s2;
     V3 ns = normalize(mk(s2.x + u * (s0.x - s2.x) + v * (s1.x - s2.x),
                          s2.y + u * (s0.y - s2.y) + v * (s1.y - s2.y),
                          s2.z + u * (s0.z - s2.z) + v * (s1.z - s2.z)));
@@ -428,7 +442,7 @@ __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float 
     V3 color = mk(1, 1, 1);
     float alpha, metallic = 1.f;
     if (HW8) {
-        const float4 s3 = __ldg(sq + 3), s4 = __ldg(sq + 4), s5 = __ldg(sq + 5);
+        const float4 s3 = rec.s3, s4 = rec.s4, s5 = rec.s5;
         // uv: data = (s0.w, s1.w), data2 = (s2.w, s3.w), data3 = (s4.w, s5.w)
         const float tx = s4.w + u * (s0.w - s4.w) + v * (s2.w - s4.w);
         const float ty = s5.w + u * (s1.w - s5.w) + v * (s3.w - s5.w);
@@ -520,7 +534,9 @@ __device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *
                                              const TraceHit &hit, V3 &o, V3 &d, V3 &L, V3 &T,
                                              const uint4 rnd, ThreadCounters &tc) {
     BounceOut bo;
-    if (!shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, hit.t, hit.u, hit.v, hit.tri, hit.det > 0.f, L, T, rnd, tc, bo)) return false;
+    SurfRec rec;
+    load_surf_rec<HW8>(sc, hit.tri, rec);
+    if (!shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, hit.t, hit.u, hit.v, rec, hit.det > 0.f, L, T, rnd, tc, bo)) return false;
     float ls = 0.f;
     if (sc.n_light_tris > 0) {
         tc.light_queries++;

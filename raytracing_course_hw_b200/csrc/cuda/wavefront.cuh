@@ -37,13 +37,31 @@ namespace b200rt {
 #define B200RT_WF_DEAD 0x7FFFFFFEu   /* written by wf_trace: the firefly clamp ended this path */
 #define B200RT_FULL 0xffffffffu
 
+// Path state is one 128-byte record per path slot (AoS): after the first bounce the stages visit slots in an
+// order scrambled by the persistent kernels, and ncu showed every scattered 16-byte field access of the former
+// six-array (SoA) layout costing a 64-byte DRAM burst (shade: 1.8 GB read per launch for 0.56 GB of state).  In
+// the record, the fields a stage touches together share a 32-byte sector: {ray_o, ray_d} {hit, thr} {rad, bsdf}.
+// B200RT_STATE_AOS=0 restores the separate arrays.
+#ifndef B200RT_STATE_AOS
+#define B200RT_STATE_AOS 1
+#endif
+#if B200RT_STATE_AOS
+#define B200RT_STATE_STRIDE 8      /* float4 units: 128 bytes per path slot */
+#else
+#define B200RT_STATE_STRIDE 1
+#endif
+struct StateField {
+    float4 *base;
+    __host__ __device__ __forceinline__ float4 &operator[](size_t slot) const { return base[slot * B200RT_STATE_STRIDE]; }
+};
 struct WaveBuffers {
-    float4 *ray_o;   // o.xyz, pixel index (int bits): the Philox key of the path
-    float4 *ray_d;   // d.xyz, |nd . n_s| of the bounce that produced this ray
-    float4 *thr;     // throughput T.xyz, partial pdf (cosine + vndf)
-    float4 *rad;     // radiance L.xyz, global sample index (int bits): the Philox counter of the path
-    float4 *bsdf;    // BRDF value of the pending bounce
-    float4 *hit;     // t, u, v, bits: triangle index | inside << 31 (B200RT_WF_MISS = no hit)
+    float4 *state;      // the one allocation behind the fields below
+    StateField ray_o;   // o.xyz, pixel index (int bits): the Philox key of the path
+    StateField ray_d;   // d.xyz, |nd . n_s| of the bounce that produced this ray
+    StateField hit;     // t, u, v, bits: triangle index | inside << 31 (B200RT_WF_MISS = no hit)
+    StateField thr;     // throughput T.xyz, partial pdf (cosine + vndf)
+    StateField rad;     // radiance L.xyz, global sample index (int bits): the Philox counter of the path
+    StateField bsdf;    // BRDF value of the pending bounce
     int *queue[3];
     // per bounce b: ctr[4b] = rays entering bounce b, ctr[4b+1] = extend cursor,
     //               ctr[4b+2] = light queries of bounce b, ctr[4b+3] = light cursor
@@ -276,16 +294,39 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 }
 
 // ---- shade --------------------------------------------------------------------------------------
-// The counting instantiation gets a looser register cap: squeezed to 128 registers it needs spills, and that
-// build was observed on B200 to shade ~0.1 % of the hits per bounce differently from the plain one (and not
-// reproducibly).  With the cap lifted both instantiations and the megakernel agree bit for bit
-// (test_counting_build_renders_the_same_image); the counting build is a measurement aid, its speed is irrelevant.
+// B200RT_SHADE_PIPE=1 (measured, off): the first three hops of an item's dependency chain (queue entry -> path state
+// -> triangle + shading record) as a software pipeline through shared memory with cp.async, one to three items
+// ahead, no registers held across iterations.  On B200 it LOSES 20 % (shade 8.2 -> 9.9 ms at the 1080p probe): the
+// long-scoreboard stall per issue stays at 10.4 (ncu, profiles/r01_ncu_shade_pipe.json) because the hops that remain
+// -- material, then texels, mostly L2 misses -- dominate, while the 31 KB of staging per block shrink L1 and
+// push the 128-register build into spills.
+#ifndef B200RT_SHADE_PIPE
+#define B200RT_SHADE_PIPE 0
+#endif
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async16_ca(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 template <bool HW8, bool COUNT>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
                                                 const float *__restrict__ lut_srgb_g, DCounters *counters) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
+#if B200RT_SHADE_PIPE
+    __shared__ float4 s_state[5][128];            // hit, ray_o, ray_d, thr, rad of the item shaded next
+    __shared__ float4 s_rec[HW8 ? 9 : 6][128];    // its triangle record and shading record
+    __shared__ int s_p[3][128];                   // queue entries of the next three items
+    __shared__ uint32_t s_hw[2][128];             // hit words of the next two items
+#endif
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         lut_srgb[i] = lut_srgb_g[i];
         lut_lin[i] = 0.00392156862745098f * (float)i;
@@ -296,17 +337,73 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
     const int lane = threadIdx.x & 31;
     const bool has_lights = sc.n_light_tris > 0;
     ThreadCounters tc = {};
-    unsigned answered = 0;      // light queries answered here by the root box (they stay light queries in the stats)
+    unsigned answered = 0;      // light queries answered here by the pre-filter (they stay light queries in the stats)
+#if B200RT_SHADE_PIPE
+    const int tid = threadIdx.x;
+    const int stride = warps * 32;
+    const int i0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32 + lane;
+    // item j of this thread is queue position i0 + j * stride
+    auto valid = [&](int j) { return (long long)i0 + (long long)j * stride < (long long)n; };
+    auto issue_p = [&](int j) { if (valid(j)) cp_async4(&s_p[j % 3][tid], q_in + ((long long)i0 + (long long)j * stride)); };
+    auto issue_hw = [&](int j) { if (valid(j)) cp_async4(&s_hw[j & 1][tid], &wb.hit[s_p[j % 3][tid]].w); };
+    auto issue_data = [&](int j) {
+        if (!valid(j)) return;
+        const int pj = s_p[j % 3][tid];
+        const uint32_t bj = s_hw[j & 1][tid];
+        cp_async16(&s_state[0][tid], &wb.hit[pj]);
+        cp_async16(&s_state[1][tid], &wb.ray_o[pj]);
+        cp_async16(&s_state[2][tid], &wb.ray_d[pj]);
+        cp_async16(&s_state[3][tid], &wb.thr[pj]);
+        cp_async16(&s_state[4][tid], &wb.rad[pj]);
+        if (bj != B200RT_WF_MISS && bj != B200RT_WF_DEAD) {
+            const uint32_t tri = bj & 0x7FFFFFFFu;
+            const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + tri);
+            const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
+#pragma unroll
+            for (int c = 0; c < 3; c++) cp_async16_ca(&s_rec[c][tid], tq + c);
+#pragma unroll
+            for (int c = 0; c < (HW8 ? 6 : 3); c++) cp_async16_ca(&s_rec[3 + c][tid], sq + c);
+        }
+    };
+    issue_p(0); issue_p(1); issue_p(2);
+    cp_async_commit(); cp_async_wait_all();
+    issue_hw(0); issue_hw(1);
+    cp_async_commit(); cp_async_wait_all();
+    issue_data(0);
+    cp_async_commit();
+    for (int k = 0; __any_sync(B200RT_FULL, valid(k)); k++) {
+        const bool live = valid(k);
+#else
     for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n; base += warps * 32) {
-        const int i = base + lane;
+        const bool live = base + lane < n;
+#endif
         bool cont = false, direct = false;
         int p = 0;
-        if (i < n) {
-            p = __ldcs(q_in + i);
+#if B200RT_SHADE_PIPE
+        cp_async_wait_all();
+        float4 h, ro, rd, th, ra;
+        SurfRec rec;
+        if (live) {
+            p = s_p[k % 3][tid];
+            h = s_state[0][tid]; ro = s_state[1][tid]; rd = s_state[2][tid]; th = s_state[3][tid]; ra = s_state[4][tid];
+            rec.tv0 = s_rec[0][tid]; rec.te1 = s_rec[1][tid]; rec.te2 = s_rec[2][tid];
+            rec.s0 = s_rec[3][tid]; rec.s1 = s_rec[4][tid]; rec.s2 = s_rec[5][tid];
+            if (HW8) { rec.s3 = s_rec[6][tid]; rec.s4 = s_rec[7][tid]; rec.s5 = s_rec[8][tid]; }
+        }
+        // the slots are free again (the reads above are ordered before these copies): refill the pipeline
+        issue_p(k + 3);
+        issue_hw(k + 2);
+        issue_data(k + 1);
+        cp_async_commit();
+#endif
+        if (live) {
+#if !B200RT_SHADE_PIPE
+            p = __ldcs(q_in + base + lane);
             const float4 h = ld_state(&wb.hit[p]);
             const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
             const float4 th = ld_state(&wb.thr[p]);
             float4 ra = ld_state(&wb.rad[p]);
+#endif
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
             const uint32_t bits = __float_as_uint(h.w);
@@ -324,12 +421,16 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                 // key = pixel, counter = (global sample index, block of this bounce); both ride in spare state lanes
                 const uint4 rnd = philox4x32_10(__float_as_uint(ra.w), 16u * (uint32_t)(bounce + 1), __float_as_uint(ro.w), wp.seed);
                 BounceOut bo;
-                cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, (int)(bits & 0x7FFFFFFFu), (bits >> 31) != 0, L, T, rnd, tc, bo);
+#if !B200RT_SHADE_PIPE
+                SurfRec rec;
+                load_surf_rec<HW8>(sc, (int)(bits & 0x7FFFFFFFu), rec);
+#endif
+                cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, rec, (bits >> 31) != 0, L, T, rnd, tc, bo);
                 if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
                 if (cont && has_lights && q_direct) {
-                    // A ray that misses the box around all emitters has a light pdf of exactly 0
-                    // (light_pdf_sum's root filter): the bounce is finished here and the path skips
-                    // the light stage (its queue entry, bsdf round trip and refill slot).
+                    // A ray that misses the boxes around the emitters has a light pdf of exactly 0
+                    // (light_boxes_hit): the bounce is finished here and the path skips the light stage
+                    // (its queue entry, bsdf round trip and refill slot).
                     if (!light_boxes_hit(sc, bo.xo, bo.nd)) {
                         if (COUNT) tc.light_node_tests++;
                         answered++;
@@ -350,6 +451,9 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
         queue_push(q_out, n_out, cont && !direct, p);
         if (q_direct) queue_push(q_direct, n_direct, cont && direct, p);
     }
+#if B200RT_SHADE_PIPE
+    cp_async_wait_all();
+#endif
     if (q_direct) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) answered += __shfl_down_sync(B200RT_FULL, answered, off);
