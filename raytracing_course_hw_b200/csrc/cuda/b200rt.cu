@@ -39,10 +39,6 @@ struct b200rt_ctx {
     // Both grow on demand and are reused by later uploads (no cudaMalloc / cudaFree per frame).
     char *arena_dev = nullptr, *arena_pin = nullptr;
     size_t arena_cap = 0;
-    struct TexSlot { int w = 0, h = 0; cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0; };
-    std::vector<TexSlot> tex_slots;          // reused when an upload brings images of the same sizes
-    uint32_t *tex_pin = nullptr;             // pinned RGBA8 staging for the RGB8 -> RGBA8 expansion
-    size_t tex_pin_cap = 0;
     float *lut_srgb = nullptr;
     RebuiltBvh own_bvh;                      // host scratch of the BVH rebuild (bvh_rebuild.h)
     std::vector<b200rt_triangle> own_tris;   // triangles in the rebuilt tree's order
@@ -158,19 +154,13 @@ int apply_l2_policy(b200rt_ctx *ctx, size_t bytes) {
     return B200RT_OK;
 }
 
-void free_textures(b200rt_ctx *c) {
-    for (auto &t : c->tex_slots) { if (t.tex) cudaDestroyTextureObject(t.tex); if (t.arr) cudaFreeArray(t.arr); }
-    c->tex_slots.clear();
-}
-
-// The arena and the texture slots stay allocated for the next upload; b200rt_destroy frees them.
+// The arena stays allocated for the next upload; b200rt_destroy frees it.
 void release_scene(b200rt_ctx *c) { c->has_scene = false; }
 
 void free_scene_memory(b200rt_ctx *c) {
-    free_textures(c);
-    cudaFree(c->arena_dev); cudaFreeHost(c->arena_pin); cudaFreeHost(c->tex_pin);
-    c->arena_dev = c->arena_pin = nullptr; c->tex_pin = nullptr;
-    c->arena_cap = c->tex_pin_cap = 0;
+    cudaFree(c->arena_dev); cudaFreeHost(c->arena_pin);
+    c->arena_dev = c->arena_pin = nullptr;
+    c->arena_cap = 0;
     c->has_scene = false;
 }
 
@@ -377,63 +367,6 @@ __global__ void resolve_kernel(const float *__restrict__ total, uint8_t *__restr
 
 namespace {
 
-// Textures of one upload: expand RGB8 -> RGBA8 into pinned staging on the host cores, then one async
-// 2D copy per image into a cudaArray.  Arrays and texture objects are kept in ctx->tex_slots and reused
-// when the next upload brings the same image sizes in the same order (a re-upload of the same scene).
-int upload_textures(b200rt_ctx *ctx, const std::vector<const b200rt_image *> &imgs, std::vector<cudaTextureObject_t> &out) {
-    out.assign(imgs.size(), 0);
-    size_t texels = 0;
-    bool same = imgs.size() == ctx->tex_slots.size();
-    for (size_t i = 0; i < imgs.size(); i++) {
-        const b200rt_image &img = *imgs[i];
-        if (!img.rgb || img.width <= 0 || img.height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
-        texels += (size_t)img.width * img.height;
-        if (same && (ctx->tex_slots[i].w != img.width || ctx->tex_slots[i].h != img.height)) same = false;
-    }
-    if (!same) {
-        CK(cudaStreamSynchronize(ctx->stream));
-        free_textures(ctx);
-        // texels are fetched as ONE 32-bit word (R | G << 8 | B << 16 | A << 24): one result register per tap
-        const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned int>();
-        for (size_t i = 0; i < imgs.size(); i++) {
-            b200rt_ctx::TexSlot t;
-            t.w = imgs[i]->width; t.h = imgs[i]->height;
-            CK(cudaMallocArray(&t.arr, &fmt, (size_t)t.w, (size_t)t.h));
-            cudaResourceDesc rd{};
-            rd.resType = cudaResourceTypeArray;
-            rd.res.array.array = t.arr;
-            cudaTextureDesc td{};
-            td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
-            td.filterMode = cudaFilterModePoint;          // the bilinear blend is done in the kernel
-            td.readMode = cudaReadModeElementType;
-            td.normalizedCoords = 0;
-            ctx->tex_slots.push_back(t);                  // owned from here on, also on a failure below
-            CK(cudaCreateTextureObject(&ctx->tex_slots.back().tex, &rd, &td, nullptr));
-        }
-    }
-    if (texels > ctx->tex_pin_cap) {
-        CK(cudaStreamSynchronize(ctx->stream));
-        cudaFreeHost(ctx->tex_pin); ctx->tex_pin = nullptr; ctx->tex_pin_cap = 0;
-        CK(cudaHostAlloc((void **)&ctx->tex_pin, texels * sizeof(uint32_t), cudaHostAllocDefault));
-        ctx->tex_pin_cap = texels;
-    }
-    size_t off = 0;
-    for (size_t i = 0; i < imgs.size(); i++) {
-        const b200rt_image &img = *imgs[i];
-        const size_t n = (size_t)img.width * img.height;
-        uint32_t *dst = ctx->tex_pin + off;
-        const uint8_t *src = img.rgb;
-        parallel_for(n, [&](size_t a, size_t b) {
-            for (size_t k = a; k < b; k++) dst[k] = (uint32_t)src[3 * k] | ((uint32_t)src[3 * k + 1] << 8) | ((uint32_t)src[3 * k + 2] << 16) | 0xFF000000u;
-        });
-        CK(cudaMemcpy2DToArrayAsync(ctx->tex_slots[i].arr, 0, 0, dst, (size_t)img.width * 4, (size_t)img.width * 4, (size_t)img.height,
-                                    cudaMemcpyHostToDevice, ctx->stream));
-        out[i] = ctx->tex_slots[i].tex;
-        off += n;
-    }
-    return B200RT_OK;
-}
-
 // Cut through the top of the light BVH: start at the root and keep replacing the inner node with the largest
 // surface area by its children until `want` boxes are open (or only leaves remain).
 void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, int want, DGltfScene &g) {
@@ -536,6 +469,18 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     const size_t o_lnodes = take(n_lpairs * sizeof(DPair)), o_ltris = take(nl * sizeof(DTri)), o_lnorm = take(nl * sizeof(DLightNormals));
     const size_t o_lsample = take(nl * sizeof(DTri));
     const size_t o_mats = take(nm * sizeof(DMaterial)), o_lut = take(256 * sizeof(float));
+    // images (hw8 only; the environment map is the last one): RGBA8 words, one array per image, in the same arena
+    std::vector<const b200rt_image *> imgs;
+    if (g.hw8) {
+        for (int i = 0; i < s->n_images; i++) imgs.push_back(&s->images[i]);
+        if (s->env_map) imgs.push_back(s->env_map);
+    }
+    std::vector<size_t> o_img(imgs.size());
+    for (size_t i = 0; i < imgs.size(); i++) {
+        if (!imgs[i]->rgb || imgs[i]->width <= 0 || imgs[i]->height <= 0) return fail(ctx, B200RT_ERR_INVALID, "empty image");
+        if ((long long)imgs[i]->width * imgs[i]->height > (1ll << 30)) return fail(ctx, B200RT_ERR_UNSUPPORTED, "image above 2^30 texels");
+        o_img[i] = take((size_t)imgs[i]->width * imgs[i]->height * sizeof(uint32_t));
+    }
     if ((rc = ensure_arena(ctx, off))) return rc;
     char *pin = ctx->arena_pin, *dev = ctx->arena_dev;
     // the staging buffer may still feed the copy of the previous upload
@@ -599,14 +544,17 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     }
     lap("light set");
 
-    // textures: one point-sampled texture object per image (hw8 only); the environment map is the last slot
-    std::vector<const b200rt_image *> imgs;
-    if (g.hw8) {
-        for (int i = 0; i < s->n_images; i++) imgs.push_back(&s->images[i]);
-        if (s->env_map) imgs.push_back(s->env_map);
+    // textures: RGB8 -> RGBA8 words straight into the staging arena, on all host cores
+    std::vector<DTexels> tex(imgs.size());
+    for (size_t i = 0; i < imgs.size(); i++) {
+        const size_t n = (size_t)imgs[i]->width * imgs[i]->height;
+        uint32_t *dst = reinterpret_cast<uint32_t *>(pin + o_img[i]);
+        const uint8_t *src = imgs[i]->rgb;
+        parallel_for(n, [&](size_t a, size_t b) {
+            for (size_t k = a; k < b; k++) dst[k] = (uint32_t)src[3 * k] | ((uint32_t)src[3 * k + 1] << 8) | ((uint32_t)src[3 * k + 2] << 16) | 0xFF000000u;
+        });
+        tex[i] = reinterpret_cast<DTexels>(dev + o_img[i]);
     }
-    std::vector<cudaTextureObject_t> tex;
-    if ((rc = upload_textures(ctx, imgs, tex))) return rc;
     if (g.hw8 && s->env_map) { g.env = tex.back(); g.env_w = s->env_map->width; g.env_h = s->env_map->height; }
     lap("textures");
 
@@ -618,7 +566,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         for (int k = 0; k < 3; k++) { d.base_color[k] = m.base_color[k]; d.emission[k] = m.emission[k]; }
         d.metallic_factor = m.metallic_factor; d.roughness_factor = m.roughness_factor;
         d.kind = m.kind; d.ior = m.ior;
-        auto bind = [&](int32_t idx, cudaTextureObject_t &t, int32_t &w, int32_t &h) -> bool {
+        auto bind = [&](int32_t idx, DTexels &t, int32_t &w, int32_t &h) -> bool {
             if (!g.hw8 || idx < 0) return true;
             if (idx >= s->n_images) return false;
             t = tex[(size_t)idx]; w = s->images[idx].width; h = s->images[idx].height;

@@ -53,12 +53,18 @@ struct DLightNormals {
     float4 n0, n1, n2;  // data, data2, data3
 };
 
+// An image on the device: row-major 32-bit texels (R | G << 8 | B << 16 | A << 24) in the scene arena, top row first
+// like the reference's Texture (hw8/src/include/gltf_structs.h).  Plain read-only loads, not texture objects: the
+// kernel needs the four integer taps of the reference's own bilinear blend, and per-lane texture HANDLES made every
+// fetch a loop over the distinct handles of a warp (28 % of the shade stage's stall samples, ncu).
+typedef const uint32_t *DTexels;
+
 struct DMaterial {
     float base_color[3];
     float emission[3];
     float metallic_factor;
     float roughness_factor;
-    cudaTextureObject_t tex_base, tex_emissive, tex_mr, tex_normal;  // 0 = absent
+    DTexels tex_base, tex_emissive, tex_mr, tex_normal;  // null = absent
     int32_t w_base, h_base, w_emissive, h_emissive, w_mr, h_mr, w_normal, h_normal;
     int32_t kind;        // hw6: B200RT_MAT_DIFFUSE / METALLIC / DIELECTRIC
     float ior;           // hw6 dielectric
@@ -90,7 +96,7 @@ struct DGltfScene {
     int32_t n_light_top;
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
     float bg[3];
-    cudaTextureObject_t env;     // 0 = absent
+    DTexels env;                 // null = absent
     int32_t env_w, env_h;
 };
 

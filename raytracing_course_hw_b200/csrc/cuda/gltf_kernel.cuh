@@ -260,7 +260,7 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
 }
 
 // ---- textures (hw8/src/scene.cpp:9-35): wrap, bilinear on the integer texel grid, sRGB decode
-// per texel BEFORE blending.  Texels are RGBA8 in a point-sampled texture object; decode goes
+// per texel BEFORE blending.  Texels are 32-bit RGBA8 words in linear memory (DTexels); decode goes
 // through a 256-entry table (host-computed with the reference's powf) in shared memory.
 // A sample is split into a fetch (4 point taps issued back to back) and a resolve, so that the taps
 // of all textures of a material are in flight together: ncu attributed half of the shade stage's
@@ -269,7 +269,7 @@ struct TexTaps {
     uint32_t c11, c12, c21, c22;      // packed RGBA8 texels (one register per tap)
     float dx, dy;
 };
-__device__ __forceinline__ void tex_fetch(cudaTextureObject_t tex, int w, int h, float tx, float ty, TexTaps &k) {
+__device__ __forceinline__ void tex_fetch(DTexels tex, int w, int h, float tx, float ty, TexTaps &k) {
     tx -= floorf(tx);
     ty -= floorf(ty);
     tx *= (float)w;
@@ -281,16 +281,16 @@ __device__ __forceinline__ void tex_fetch(cudaTextureObject_t tex, int w, int h,
     if (iy2 >= h) iy2 -= h;
     ix1 = min(ix1, w - 1); iy1 = min(iy1, h - 1);
     k.dx = tx - (float)ix1; k.dy = ty - (float)iy1;
-    const float x1 = (float)ix1 + 0.5f, x2 = (float)ix2 + 0.5f, y1 = (float)iy1 + 0.5f, y2 = (float)iy2 + 0.5f;
-    k.c11 = tex2D<unsigned int>(tex, x1, y1); k.c12 = tex2D<unsigned int>(tex, x1, y2);
-    k.c21 = tex2D<unsigned int>(tex, x2, y1); k.c22 = tex2D<unsigned int>(tex, x2, y2);
+    const uint32_t *r1 = tex + iy1 * w, *r2 = tex + iy2 * w;
+    k.c11 = __ldg(r1 + ix1); k.c12 = __ldg(r2 + ix1);
+    k.c21 = __ldg(r1 + ix2); k.c22 = __ldg(r2 + ix2);
 }
 __device__ __forceinline__ V3 texel(const uint32_t c, const float *lut) { return mk(lut[c & 255u], lut[(c >> 8) & 255u], lut[(c >> 16) & 255u]); }
 __device__ __forceinline__ V3 tex_resolve(const TexTaps &k, const float *lut) {
     const V3 p11 = texel(k.c11, lut), p12 = texel(k.c12, lut), p21 = texel(k.c21, lut), p22 = texel(k.c22, lut);
     return (1.f - k.dx) * ((1.f - k.dy) * p11 + k.dy * p12) + k.dx * ((1.f - k.dy) * p21 + k.dy * p22);
 }
-__device__ __forceinline__ V3 sample_texture(cudaTextureObject_t tex, int w, int h, float tx, float ty, const float *lut) {
+__device__ __forceinline__ V3 sample_texture(DTexels tex, int w, int h, float tx, float ty, const float *lut) {
     TexTaps k;
     tex_fetch(tex, w, h, tx, ty, k);
     return tex_resolve(k, lut);
@@ -446,7 +446,7 @@ __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float 
         // uv: data = (s0.w, s1.w), data2 = (s2.w, s3.w), data3 = (s4.w, s5.w)
         const float tx = s4.w + u * (s0.w - s4.w) + v * (s2.w - s4.w);
         const float ty = s5.w + u * (s1.w - s5.w) + v * (s3.w - s5.w);
-        const cudaTextureObject_t tb = m->tex_base, te = m->tex_emissive, tm = m->tex_mr, tn = m->tex_normal;
+        const DTexels tb = m->tex_base, te = m->tex_emissive, tm = m->tex_mr, tn = m->tex_normal;
         TexTaps kb, ke, km, kn;
         if (tb) tex_fetch(tb, m->w_base, m->h_base, tx, ty, kb);
         if (te) tex_fetch(te, m->w_emissive, m->h_emissive, tx, ty, ke);
