@@ -618,7 +618,7 @@ int ensure_buffers(b200rt_ctx *ctx, int w, int h, int n_slabs) {
 
 void free_wave(b200rt_ctx *c) {
     for (WaveBuffers &w : c->wave) {
-        cudaFree(w.state); cudaFree(w.ctr);
+        cudaFree(w.state); if (w.ctr) cudaFree(w.ctr - 4);
         for (int i = 0; i < 3; i++) cudaFree(w.queue[i]);
         w = WaveBuffers{};
     }
@@ -636,7 +636,8 @@ int ensure_wave(b200rt_ctx *ctx, size_t slots) {
         StateField *f[6] = {&w.ray_o, &w.ray_d, &w.hit, &w.thr, &w.rad, &w.bsdf};
         for (int k = 0; k < 6; k++) f[k]->base = w.state + (B200RT_STATE_AOS ? (size_t)k : (size_t)k * slots);
         for (int i = 0; i < 3; i++) CK(cudaMalloc(&w.queue[i], slots * sizeof(int)));
-        CK(cudaMalloc(&w.ctr, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int)));
+        CK(cudaMalloc(&w.ctr, 4 * (B200RT_MAX_DEPTH + 2) * sizeof(int)));
+        w.ctr += 4;      // ctr[-1] = rays entering bounce 0 (layout: wavefront.cuh, WaveBuffers::ctr)
     }
     ctx->wave_capacity = slots;
     return B200RT_OK;
@@ -692,41 +693,41 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         cudaStream_t st = ctx->pipe_stream[k];
         wp.s_begin = s0;
         wp.s_count = std::min<int>((int)s_w, rp.spp_end - s0);
-        CK(cudaMemsetAsync(wb.ctr, 0, 4 * (B200RT_MAX_DEPTH + 1) * sizeof(int), st));
+        CK(cudaMemsetAsync(wb.ctr - 4, 0, 4 * (B200RT_MAX_DEPTH + 2) * sizeof(int), st));
         wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters);
         (*launches)++;
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
-            int *c = wb.ctr + 4 * b;
+            int *c = wb.ctr + 4 * b;     // c[-1] rays in, c[0] extend cursor, c[1] light cursor, c[2] light queries, c[3] rays into b+1
             if (ctx->wf_fused && lights) {
                 // fused scheduling: the traversal of bounce b also answers the light-pdf query of
                 // bounce b-1 for the same ray and applies its weight / clamp (wavefront_trace.cuh)
                 ctx->stamp(true, 0, st);
-                wf_trace<COUNT><<<ctx->blocks_trace[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, b > 0 ? 1 : 0);
+                wf_trace<COUNT><<<ctx->blocks_trace[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, b > 0 ? 1 : 0);
                 ctx->stamp(false, 0, st);
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, c + 4, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
                 std::swap(qa, qb);
                 continue;
             }
             ctx->stamp(true, 0, st);
-            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c + 0, c + 1, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
+            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
             ctx->stamp(false, 0, st);
             const bool last = b == rp.ray_depth - 1;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 4, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 3, qb, c + 4, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c + 0, qb, lights ? c + 2 : c + 4, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }

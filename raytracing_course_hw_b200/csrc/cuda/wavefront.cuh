@@ -33,6 +33,9 @@ namespace b200rt {
 #ifndef B200RT_STACK_TNEAR
 #define B200RT_STACK_TNEAR 0     /* 1 = keep the entry distance with stacked nodes (prunes on pop; slower: doubles stack traffic) */
 #endif
+#ifndef B200RT_EXT_UNROLL
+#define B200RT_EXT_UNROLL 2      /* box steps per phase decision in wf_extend's inner phase */
+#endif
 #define B200RT_WF_MISS 0x7FFFFFFFu
 #define B200RT_WF_DEAD 0x7FFFFFFEu   /* written by wf_trace: the firefly clamp ended this path */
 #define B200RT_FULL 0xffffffffu
@@ -63,8 +66,10 @@ struct WaveBuffers {
     StateField rad;     // radiance L.xyz, global sample index (int bits): the Philox counter of the path
     StateField bsdf;    // BRDF value of the pending bounce
     int *queue[3];
-    // per bounce b: ctr[4b] = rays entering bounce b, ctr[4b+1] = extend cursor,
-    //               ctr[4b+2] = light queries of bounce b, ctr[4b+3] = light cursor
+    // per bounce b, c = ctr + 4b: c[-1] = rays entering bounce b, c[0] = extend cursor, c[1] = light cursor,
+    //               c[2] = light queries of bounce b, c[3] = rays entering bounce b+1.  (c[2], c[3]) is an aligned
+    //               64-bit word: the shade stage appends to both queues with ONE atomic (queue_push2).
+    //               ctr points 4 ints into its allocation, so ctr[-1] exists.
     int *ctr;
 };
 
@@ -118,6 +123,55 @@ __device__ __forceinline__ void queue_push(int *queue, int *counter, bool want, 
     if (want) __stcs(queue + base + __popc(m & ((1u << lane) - 1u)), value);
 }
 
+// Append to two queues whose counters are the low / high half of one aligned 64-bit word: one atomic round trip
+// per warp instead of two (ncu: the returning atomics were 10 % of wf_shade's stall samples).
+__device__ __forceinline__ void queue_push2(int *q_lo, int *q_hi, int *counter_lo, bool want_lo, bool want_hi, int value) {
+    const unsigned m_lo = __ballot_sync(B200RT_FULL, want_lo), m_hi = __ballot_sync(B200RT_FULL, want_hi);
+    if ((m_lo | m_hi) == 0) return;
+    const int lane = threadIdx.x & 31;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(reinterpret_cast<unsigned long long *>(counter_lo), (unsigned long long)__popc(m_lo) | ((unsigned long long)__popc(m_hi) << 32));
+    base = __shfl_sync(B200RT_FULL, base, 0);
+    const unsigned below = (1u << lane) - 1u;
+    if (want_lo) __stcs(q_lo + (int)(unsigned)base + __popc(m_lo & below), value);
+    if (want_hi) __stcs(q_hi + (int)(unsigned)(base >> 32) + __popc(m_hi & below), value);
+}
+
+// Prefetch one 32-byte sector into L2 (the wave state streams through DRAM; whoever knows a path index early
+// turns the later demand load into an L2 hit).
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+#ifndef B200RT_SHADE_PF
+#define B200RT_SHADE_PF 0        /* wf_shade: 1 = prefetch the state record of the item after next; 2 = also the hit triangle's records of the next item */
+#endif
+#ifndef B200RT_REFILL_PF
+#define B200RT_REFILL_PF 2048   /* wf_extend / wf_light: a lane that takes queue entry i prefetches the ray of entry i + this (0 = off) */
+#endif
+
+// Traversal stack of the persistent kernels.  ncu on wf_extend: the per-thread local-memory stack made 46 % of the
+// L1 requests and its write-through stores 20 % of the L2 sectors.  With B200RT_SMEM_STACK = N > 0 the first N
+// entries of every thread live in shared memory ([entry][thread]: conflict-free), deeper ones in local memory.
+#ifndef B200RT_SMEM_STACK
+#define B200RT_SMEM_STACK 0
+#endif
+struct TravStack {
+    uint32_t deep[B200RT_STACK];
+#if B200RT_SMEM_STACK
+    uint32_t *sh;      // &smem[threadIdx.x]
+    __device__ __forceinline__ void push(int &sp, uint32_t v) {
+        if (sp < B200RT_SMEM_STACK) sh[sp * 128] = v; else deep[sp - B200RT_SMEM_STACK] = v;
+        sp++;
+    }
+    __device__ __forceinline__ uint32_t pop(int &sp) {
+        --sp;
+        return sp < B200RT_SMEM_STACK ? sh[sp * 128] : deep[sp - B200RT_SMEM_STACK];
+    }
+#else
+    __device__ __forceinline__ void push(int &sp, uint32_t v) { deep[sp++] = v; }
+    __device__ __forceinline__ uint32_t pop(int &sp) { return deep[--sp]; }
+#endif
+};
+
 __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters) {
     const int n_slots = wp.n_tiles * 32 * wp.s_count;
     const int warps = (gridDim.x * blockDim.x) >> 5;
@@ -141,7 +195,7 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             st_state(&wb.rad[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl))));
             made++;
         }
-        queue_push(wb.queue[0], wb.ctr + 0, ok, slot);
+        queue_push(wb.queue[0], wb.ctr - 1, ok, slot);
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) made += __shfl_down_sync(B200RT_FULL, made, off);
@@ -168,7 +222,11 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 #if B200RT_STACK_TNEAR
     uint2 stack[B200RT_STACK];
 #else
-    uint32_t stack[B200RT_STACK];
+    TravStack stack;
+#if B200RT_SMEM_STACK
+    __shared__ uint32_t s_stack[B200RT_SMEM_STACK * 128];
+    stack.sh = s_stack + threadIdx.x;
+#endif
 #endif
     int sp = 0;
     bool active = false, exhausted = false;
@@ -193,7 +251,13 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
                     p = __ldcs(q_in + idx);
+#if B200RT_REFILL_PF
+                    const int ahead = idx + B200RT_REFILL_PF < n ? __ldcs(q_in + idx + B200RT_REFILL_PF) : -1;
+#endif
                     const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
+#if B200RT_REFILL_PF
+                    if (ahead >= 0) prefetch_l2(&wb.ray_o[ahead]);     // arrived together with p: no extra wait
+#endif
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.q, o, d);
                     tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
@@ -217,7 +281,23 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) { DBG_PHASE(2, 1); DBG_PHASE(3, __popc(leaf_mask)); }
             else { DBG_PHASE(0, 1); DBG_PHASE(1, __popc(inner_mask)); DBG_PHASE(6, __popc(leaf_mask)); DBG_PHASE(7, 32 - __popc(leaf_mask | inner_mask)); }
 #endif
-            bool pop = false;
+            // end of a subtree: next stacked node, or the ray is finished
+            auto do_pop = [&]() {
+                bool got = false;
+#if B200RT_STACK_TNEAR
+                while (sp > 0) {
+                    const uint2 e = stack[--sp];
+                    if (__uint_as_float(e.y) <= tbest) { cur = e.x; got = true; break; }
+                }
+#else
+                if (sp > 0) { cur = stack.pop(sp); got = true; }
+#endif
+                if (!got) {
+                    const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
+                    st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
+                    active = false;
+                }
+            };
             if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) {
                 if (at_leaf) {
                     const uint32_t first = cur & 0x07FFFFFFu, count = (cur >> 27) & 15u;
@@ -236,42 +316,32 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                         const float t = dot(E2, qv) * idet;
                         if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < tbest) { tbest = t; hu = u; hv = v; htri = i; hdet = det; }
                     }
-                    pop = true;
+                    do_pop();
                 }
-            } else if (at_inner) {
-                float tl, tr;
-                bool hl, hr;
-                uint32_t ml, mr;
-                pair_test(sc.nodes, cur, qr, tbest, hl, hr, tl, tr, ml, mr);
-                if (COUNT) node_tests += 2;
-                if (hl && hr) {
-                    const bool left_first = tl <= tr;
-                    // no bound check: b200rt_upload_scene rejects trees deeper than B200RT_STACK
+            } else {
+                // inner phase: B200RT_EXT_UNROLL box steps per phase decision (the ballots and the phase choice are
+                // a quarter of a step's instructions); lanes that reach a leaf or finish sit out the remaining ones
+#pragma unroll
+                for (int k = 0; k < B200RT_EXT_UNROLL; k++) {
+                    if (active && !(cur & B200RT_LEAF)) {
+                        float tl, tr;
+                        bool hl, hr;
+                        uint32_t ml, mr;
+                        pair_test(sc.nodes, cur, qr, tbest, hl, hr, tl, tr, ml, mr);
+                        if (COUNT) node_tests += 2;
+                        if (hl && hr) {
+                            const bool left_first = tl <= tr;
+                            // no bound check: b200rt_upload_scene rejects trees deeper than B200RT_STACK
 #if B200RT_STACK_TNEAR
-                    stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
+                            stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
 #else
-                    stack[sp++] = left_first ? mr : ml;
+                            stack.push(sp, left_first ? mr : ml);
 #endif
-                    cur = left_first ? ml : mr;
-                } else if (hl) cur = ml;
-                else if (hr) cur = mr;
-                else pop = true;
-            }
-            if (pop) {
-                // skip stacked subtrees that a closer hit has made irrelevant
-                bool got = false;
-#if B200RT_STACK_TNEAR
-                while (sp > 0) {
-                    const uint2 e = stack[--sp];
-                    if (__uint_as_float(e.y) <= tbest) { cur = e.x; got = true; break; }
-                }
-#else
-                if (sp > 0) { cur = stack[--sp]; got = true; }
-#endif
-                if (!got) {
-                    const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
-                    st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
-                    active = false;
+                            cur = left_first ? ml : mr;
+                        } else if (hl) cur = ml;
+                        else if (hr) cur = mr;
+                        else do_pop();
+                    }
                 }
             }
         }
@@ -374,6 +444,20 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
     for (int k = 0; __any_sync(B200RT_FULL, valid(k)); k++) {
         const bool live = valid(k);
 #else
+#if B200RT_SHADE_PF
+    // Queue entries are read ahead of their use, so that the state record of a LATER item can be prefetched without
+    // waiting for its index (its demand loads then hit L2 instead of DRAM).  Level 2 goes one hop further: the hit
+    // word of the next item is read early and its triangle / shading records are prefetched at the end of the body.
+    const long long pf_stride = (long long)warps * 32;
+    const long long pf_i0 = (long long)(((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32 + lane);
+    auto q_at = [&](long long i) { return i < n ? __ldcs(q_in + i) : -1; };
+    int p_next = q_at(pf_i0);
+    int p_next2 = q_at(pf_i0 + pf_stride);
+#if B200RT_SHADE_PF >= 2
+    int p_next3 = q_at(pf_i0 + 2 * pf_stride);
+    if (p_next >= 0) { prefetch_l2(&wb.ray_o[p_next]); prefetch_l2(&wb.hit[p_next]); prefetch_l2(&wb.rad[p_next]); }
+#endif
+#endif
     for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n; base += warps * 32) {
         const bool live = base + lane < n;
 #endif
@@ -396,9 +480,27 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
         issue_data(k + 1);
         cp_async_commit();
 #endif
+#if B200RT_SHADE_PF && !B200RT_SHADE_PIPE
+        const int p_cur = p_next;
+        p_next = p_next2;
+#if B200RT_SHADE_PF >= 2
+        p_next2 = p_next3;
+        p_next3 = q_at((long long)base + lane + 3 * pf_stride);
+        if (p_next2 >= 0) { prefetch_l2(&wb.ray_o[p_next2]); prefetch_l2(&wb.hit[p_next2]); prefetch_l2(&wb.rad[p_next2]); }
+        // state of p_next was prefetched one iteration ago: its hit word is an L2 hit now, used at the end of the body
+        const uint32_t hw_next = p_next >= 0 ? __float_as_uint(wb.hit[p_next].w) : B200RT_WF_MISS;
+#else
+        p_next2 = q_at((long long)base + lane + 2 * pf_stride);
+        if (p_next >= 0) { prefetch_l2(&wb.ray_o[p_next]); prefetch_l2(&wb.hit[p_next]); prefetch_l2(&wb.rad[p_next]); }
+#endif
+#endif
         if (live) {
 #if !B200RT_SHADE_PIPE
+#if B200RT_SHADE_PF
+            p = p_cur;
+#else
             p = __ldcs(q_in + base + lane);
+#endif
             const float4 h = ld_state(&wb.hit[p]);
             const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
             const float4 th = ld_state(&wb.thr[p]);
@@ -448,8 +550,16 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             }
             st_state(&wb.rad[p], make_float4(L.x, L.y, L.z, ra.w));
         }
-        queue_push(q_out, n_out, cont && !direct, p);
-        if (q_direct) queue_push(q_direct, n_direct, cont && direct, p);
+#if B200RT_SHADE_PF >= 2 && !B200RT_SHADE_PIPE
+        if (hw_next != B200RT_WF_MISS && hw_next != B200RT_WF_DEAD) {
+            const uint32_t tri = hw_next & 0x7FFFFFFFu;
+            const char *tq = reinterpret_cast<const char *>(sc.tris + tri), *sq = reinterpret_cast<const char *>(sc.shade + tri);
+            prefetch_l2(tq); prefetch_l2(tq + 32);
+            prefetch_l2(sq); prefetch_l2(sq + 32); prefetch_l2(sq + 64);
+        }
+#endif
+        if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, p);   // n_direct == n_out + 1
+        else queue_push(q_out, n_out, cont && !direct, p);
     }
 #if B200RT_SHADE_PIPE
     cp_async_wait_all();
@@ -469,7 +579,11 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                                                 const int batch, const int leaf_t, const bool filtered) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
-    uint32_t stack[B200RT_STACK];
+    TravStack stack;
+#if B200RT_SMEM_STACK
+    __shared__ uint32_t s_stack[B200RT_SMEM_STACK * 128];
+    stack.sh = s_stack + threadIdx.x;
+#endif
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
@@ -495,7 +609,14 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
                     p = __ldcs(q_in + idx);
+#if B200RT_REFILL_PF
+                    const int ahead = idx + B200RT_REFILL_PF < n ? __ldcs(q_in + idx + B200RT_REFILL_PF) : -1;
+#endif
                     const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
+#if B200RT_REFILL_PF
+                    if (ahead >= 0) prefetch_l2(&wb.ray_o[ahead]);
+                    prefetch_l2(&wb.thr[p]); prefetch_l2(&wb.bsdf[p]);   // read when this query ends
+#endif
                     o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.lq, o, d);
                     total = 0.f; sp = 0;
@@ -558,14 +679,14 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                 pair_test(sc.light_nodes, cur, qr, INFINITY, hl, hr, tl, tr, ml, mr);
                 if (COUNT) node_tests += 2;
                 if (hl && hr) {
-                    stack[sp++] = mr;
+                    stack.push(sp, mr);
                     cur = ml;
                 } else if (hl) cur = ml;
                 else if (hr) cur = mr;
                 else pop = true;
             }
             if (pop) {
-                if (sp > 0) cur = stack[--sp];
+                if (sp > 0) cur = stack.pop(sp);
                 else {
                     // end of the bounce: mean pdf, weight, firefly clamp (scene.cpp:158-163)
                     const float4 th = ld_state(&wb.thr[p]), bs = ld_state(&wb.bsdf[p]);
