@@ -149,6 +149,14 @@ typedef struct b200rt_scene_desc {
     const b200rt_material  *materials;    int32_t n_materials;
     const b200rt_image     *images;       int32_t n_images;
     const b200rt_image     *env_map;      /* NULL when absent (hw8 argv[6]) */
+
+    /* hw5 (text scenes with TRIANGLE figures, hw5/src/scene.cpp:18-45, hw5/src/include/distributions.h:172-199):
+     * `prims` holds Scene::figures after initBVH -- the n_bvh_prims non-plane figures in BVH order first, then the
+     * planes (scanned linearly); `nodes`/`root` are Scene::bvh over prims[0, n_bvh_prims); `light_prims` are
+     * FiguresMix::figures_ (copies of the emissive BOX / ELLIPSOID / TRIANGLE figures in the light BVH's order) and
+     * `light_nodes` FiguresMix::bvh over them.  Zero / NULL in every other mode. */
+    const b200rt_primitive *light_prims;  int32_t n_light_prims;
+    int32_t                 n_bvh_prims;
 } b200rt_scene_desc;
 
 /* ---- context ------------------------------------------------------------------------ */

@@ -22,7 +22,9 @@ int oracle_render(const b200rt_scene_desc *s, int rng_kind, uint32_t seed, int s
         case B200RT_MODE_HW2:
             port::render_deterministic(*s, rgb, primary_ids, accum_sum);
             return 0;
+        case B200RT_MODE_HW3:
         case B200RT_MODE_HW4:
+        case B200RT_MODE_HW5:
         case B200RT_MODE_HW6:
         case B200RT_MODE_HW7:
         case B200RT_MODE_HW8:

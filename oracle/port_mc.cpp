@@ -42,7 +42,7 @@ void quantise(const V &radiance, uint8_t *out) {
     out[2] = round(255 * o.z);
 }
 
-// =========================================== hw4 ============================================
+// ======================================== hw3 / hw4 =========================================
 // RNG plumbing of hw4: ONE global minstd_rand consumed in scan order, but every distribution
 // object owns its own normal_distribution (with its own cached second variate):
 // Cosine::n01 (hw4 distributions.h:48) and one per EllipsoidLight (:154).
@@ -80,10 +80,15 @@ struct Hw4 {
         }
     }
 
+    // hw3 (hw3/src/scene.cpp, hw3/src/primitives.cpp) is this integrator before importance sampling arrived:
+    // uniform-hemisphere diffuse bounce from ONE global normal_distribution, +0.5 in the camera ray, planes
+    // without T_MAX.  Everything else (metal, dielectric, scan-order intersect) is shared with hw4.
+    bool hw3() const { return s.mode == B200RT_MODE_HW3; }
+
     bool intersect(const Ray &ray, Hit &best, int &pos) const {
         pos = -1;
         for (int i = 0; i < s.n_prims; i++) {
-            Hit h = hit_figure(s.prims[i], ray, true);
+            Hit h = hit_figure(s.prims[i], ray, !hw3());
             if (h.valid && (pos == -1 || h.t < best.t)) { best = h; pos = i; }
         }
         return pos != -1;
@@ -133,9 +138,11 @@ struct Hw4 {
                 float wx = sy * sz, wy = sx * sz, wz = sx * sy;
                 float u = rng.u() * (wx + wy + wz);
                 float flipSign = rng.u() > 0.5 ? 1 : -1;
-                if (u < wx) { float a = rng.u(), b = rng.u(); point = V(flipSign * sx, (2 * a - 1) * sy, (2 * b - 1) * sz); }
-                else if (u < wx + wy) { float a = rng.u(), b = rng.u(); point = V((2 * a - 1) * sx, flipSign * sy, (2 * b - 1) * sz); }
-                else { float a = rng.u(), b = rng.u(); point = V((2 * a - 1) * sx, (2 * b - 1) * sy, flipSign * sz); }
+                // Vec3(...) is a constructor call: g++ evaluates its arguments right to left, so the LATER coordinate
+                // takes the earlier random number (pinned against the hw4 and hw5 binaries on box-light scenes)
+                if (u < wx) { float b = rng.u(), a = rng.u(); point = V(flipSign * sx, (2 * a - 1) * sy, (2 * b - 1) * sz); }
+                else if (u < wx + wy) { float b = rng.u(), a = rng.u(); point = V((2 * a - 1) * sx, flipSign * sy, (2 * b - 1) * sz); }
+                else { float b = rng.u(), a = rng.u(); point = V((2 * a - 1) * sx, (2 * b - 1) * sy, flipSign * sz); }
             } else {
                 point = V(f.data) * rng.light_sphere(li);
             }
@@ -175,7 +182,13 @@ struct Hw4 {
         float t = h.t; V norma = h.norma; bool is_inside = h.inside;
         V x = ray.o + t * ray.d;
         V emission(f.emission), fcolor(f.color);
-        if (f.material == B200RT_MAT_DIFFUSE) {
+        if (hw3() && f.material == B200RT_MAT_DIFFUSE) {
+            // hw3/src/scene.cpp:45-51; the global n01 (:7) is this policy's cosine_n01 (no other user in hw3)
+            V w = rng.cosine_sphere();
+            if (w.dot(norma) < 0) w = -1. * w;
+            Ray wRay(ray.o + t * ray.d + 0.0001 * w, w);
+            return emission + 2 * w.dot(norma) * fcolor * color(wRay, rec - 1);
+        } else if (f.material == B200RT_MAT_DIFFUSE) {
             V d = mix_sample(x + 0.0001 * norma, norma);
             if (d.dot(norma) < 0) return emission;
             float pdf = mix_pdf(x + 0.0001 * norma, norma, d);
@@ -224,6 +237,10 @@ struct Hw4 {
         float tanFovY = tanFovX * s.height / s.width;
         float nx = tanFovX * (2 * x / s.width - 1);
         float ny = tanFovY * (2 * y / s.height - 1);
+        if (hw3()) {   // hw3/src/scene.cpp:103-104: the 0.5 literal makes the expression double
+            nx = tanFovX * (2 * (x + 0.5) / s.width - 1);
+            ny = tanFovY * (2 * (y + 0.5) / s.height - 1);
+        }
         return {V(s.cam_pos), nx * V(s.cam_right) - ny * V(s.cam_up) + V(s.cam_forward)};
     }
     // Sum over samples [b, e) (hw4/src/scene.cpp:110-118 without the final 1/samples).
@@ -799,6 +816,255 @@ struct Hw6 {
     }
 };
 
+// =========================================== hw5 ============================================
+// Text scenes with TRIANGLE figures (hw5/src/*): planes are scanned, every other figure (ELLIPSOID, BOX, TRIANGLE,
+// each with its own position / rotation) sits in a BVH keyed by Figure::position; the light mixture takes all
+// three emissive kinds.  hw6 is this program with a glTF loader, so the integrator is Hw6's and the analytic
+// lights are Hw4's; only the plumbing over b200rt_primitive is new.
+//   Figure::intersect / intersectAsTriangle   hw5/src/primitives.cpp:13-33, 143-164
+//   Scene::intersect                          hw5/src/scene.cpp:25-45
+//   BVH::intersect_                           hw5/src/include/bvh.h:111-142
+//   Box / Triangle / Ellipsoid lights         hw5/src/include/distributions.h:61-172
+//   FiguresMix                                hw5/src/include/distributions.h:174-268
+static inline Hit hit_figure5(const b200rt_primitive &f, const Ray &ray) {
+    if (f.type != B200RT_PRIM_TRIANGLE) return hit_figure(f, ray, true);
+    Q rot(f.rotation);
+    Ray local = ray.shifted(V(f.position)).rotated(rot);
+    V a(f.data3);
+    V b = V(f.data) - a;
+    V c = V(f.data2) - a;
+    V n = b.cross(c);
+    Hit h = hit_plane(n, local.shifted(a), true);
+    if (!h.valid) return h;
+    V p = local.o - a + h.t * local.d;
+    h.valid = false;
+    if (b.cross(p).dot(n) < 0) return h;
+    if (p.cross(c).dot(n) < 0) return h;
+    if ((c - b).cross(p - b).dot(n) < 0) return h;
+    h.norma = rot.conjugate().transform(h.norma).normalize();
+    h.valid = true;
+    return h;
+}
+
+template <class Rng>
+struct Hw5 {
+    const b200rt_scene_desc &s;
+    Rng &rng;
+    Counters *cnt;
+
+    Hw5(const b200rt_scene_desc &s_, Rng &r, Counters *c) : s(s_), rng(r), cnt(c) {}
+
+    static bool hit_box_of(const b200rt_bvh_node &nd, const Ray &ray, float &t, bool &inside) { return hit_aabb(nd, ray, t, inside); }
+
+    bool closest_bvh(uint32_t pos, const Ray &ray, bool have, float cur_best, Hit &out, int &out_id) const {
+        const b200rt_bvh_node &nd = s.nodes[pos];
+        float tb; bool inside;
+        if (cnt) cnt->node_tests++;
+        if (!hit_aabb(nd, ray, tb, inside)) return false;
+        if (have && cur_best < tb && !inside) return false;
+        bool found = false;
+        if (nd.left == 0) {
+            for (uint32_t i = nd.first; i < nd.last; i++) {
+                if (cnt) cnt->tri_tests++;
+                Hit h = hit_figure5(s.prims[i], ray);
+                if (h.valid && (!found || h.t < out.t)) { out = h; out_id = (int)i; found = true; }
+            }
+            return found;
+        }
+        found = closest_bvh(nd.left, ray, have, cur_best, out, out_id);
+        if (found && (!have || out.t < cur_best)) { have = true; cur_best = out.t; }
+        Hit rh; int rid = -1;
+        if (closest_bvh(nd.right, ray, have, cur_best, rh, rid) && (!found || rh.t < out.t)) { out = rh; out_id = rid; found = true; }
+        return found;
+    }
+    // Scene::intersect: the planes first, then the BVH with the planes' best distance as the prune bound
+    bool intersect(const Ray &ray, Hit &best, int &pos) const {
+        pos = -1;
+        for (int i = s.n_bvh_prims; i < s.n_prims; i++) {
+            Hit h = hit_figure5(s.prims[i], ray);
+            if (h.valid && (pos == -1 || h.t < best.t)) { best = h; pos = i; }
+        }
+        Hit bh; int bid = -1;
+        if (closest_bvh((uint32_t)s.root, ray, pos != -1, pos != -1 ? best.t : 0.f, bh, bid) && (pos == -1 || bh.t < best.t)) { best = bh; pos = bid; }
+        return pos != -1;
+    }
+
+    V cosine_sample(V n) {
+        V d = rng.sphere();
+        d = d + n;
+        float len = d.len();
+        if (len <= 1e-9f || d.dot(n) <= 1e-9f || std::isnan(len)) return n;
+        return 1. / len * d;
+    }
+    static float cosine_pdf(V n, V d) { return std::max(0.f, d.dot(n) / PI); }
+
+    // pdfOne of the three light kinds
+    static float pdf_one(const b200rt_primitive &f, V x, V d, V y, V yn) {
+        if (f.type == B200RT_PRIM_BOX) {
+            float sx = f.data[0], sy = f.data[1], sz = f.data[2];
+            float sTotal = 8 * (sy * sz + sx * sz + sx * sy);
+            return (x - y).len2() / (sTotal * fabs(d.dot(yn)));
+        }
+        if (f.type == B200RT_PRIM_ELLIPSOID) {
+            V r(f.data);
+            V n = Q(f.rotation).transform(y - V(f.position)) / r;
+            float pointProb = 1. / (4 * PI * V{n.x * r.y * r.z, r.x * n.y * r.z, r.x * r.y * n.z}.len());
+            return pointProb * (x - y).len2() / fabs(d.dot(yn));
+        }
+        V a(f.data3); V b = V(f.data) - a; V c = V(f.data2) - a;
+        V n = b.cross(c);
+        float pointProb = 1.0 / (0.5 * n.len());
+        return pointProb * (x - y).len2() / fabs(d.dot(yn));
+    }
+    // FiguresMix::pdfOneFigureLight (distributions.h:218-250): triangles count their one hit, closed figures also
+    // the second hit from just behind the first
+    float light_pdf_one(const b200rt_primitive &f, V x, V d) const {
+        if (cnt) cnt->light_tri_tests++;
+        Hit h1 = hit_figure5(f, Ray(x, d));
+        if (!h1.valid) return 0.;
+        if (std::isnan(h1.t)) return INFINITY;
+        V y = x + h1.t * d;
+        float ans = pdf_one(f, x, d, y, h1.norma);
+        if (f.type == B200RT_PRIM_TRIANGLE) return ans;
+        Hit h2 = hit_figure5(f, Ray(x + (h1.t + eps) * d, d));
+        if (!h2.valid) return ans;
+        V y2 = x + (h1.t + eps + h2.t) * d;
+        return ans + pdf_one(f, x, d, y2, h2.norma);
+    }
+    float light_total(uint32_t pos, V x, V d) const {
+        const b200rt_bvh_node &nd = s.light_nodes[pos];
+        float tb; bool inside;
+        if (cnt) cnt->light_node_tests++;
+        if (!hit_aabb(nd, Ray(x, d), tb, inside)) return 0;
+        if (nd.left == 0) {
+            float result = 0;
+            for (uint32_t i = nd.first; i < nd.last; i++) result += light_pdf_one(s.light_prims[i], x, d);
+            return result;
+        }
+        return light_total(nd.left, x, d) + light_total(nd.right, x, d);
+    }
+    // FiguresMix::sample: index, then the kind's own sampler
+    V light_sample(V x) {
+        int which = rng.u() * (size_t)s.n_light_prims;
+        const b200rt_primitive &f = s.light_prims[which];
+        Q rot(f.rotation);
+        if (f.type == B200RT_PRIM_TRIANGLE) {
+            V a(f.data3); V b = V(f.data) - a; V c = V(f.data2) - a;
+            float u = rng.u();
+            float v = rng.u();
+            if (u + v > 1.) { u = 1 - u; v = 1 - v; }
+            V point = V(f.position) + rot.conjugate().transform(a + u * b + v * c);
+            return (point - x).normalize();
+        }
+        for (int iter = 0;; iter++) {
+            V point;
+            if (f.type == B200RT_PRIM_BOX) {
+                float sx = f.data[0], sy = f.data[1], sz = f.data[2];
+                float wx = sy * sz, wy = sx * sz, wz = sx * sy;
+                float u = rng.u() * (wx + wy + wz);
+                float flipSign = rng.u() > 0.5 ? 1 : -1;
+                // Vec3(...) is a constructor call: g++ evaluates its arguments right to left, so the LATER coordinate
+                // takes the earlier random number (pinned by the byte-equality test against the hw5 binary)
+                if (u < wx) { float b = rng.u(), a = rng.u(); point = V(flipSign * sx, (2 * a - 1) * sy, (2 * b - 1) * sz); }
+                else if (u < wx + wy) { float b = rng.u(), a = rng.u(); point = V((2 * a - 1) * sx, flipSign * sy, (2 * b - 1) * sz); }
+                else { float b = rng.u(), a = rng.u(); point = V((2 * a - 1) * sx, (2 * b - 1) * sy, flipSign * sz); }
+            } else {
+                point = V(f.data) * rng.sphere();
+            }
+            V actual = rot.conjugate().transform(point) + V(f.position);
+            V dir = (actual - x).normalize();
+            if (hit_figure5(f, Ray(x, dir)).valid) return dir;
+            if (Rng::kCounterBased && iter + 1 >= kMaxRejection) return dir;
+        }
+    }
+    size_t components() const { return s.n_light_prims > 0 ? 2 : 1; }
+    V mix_sample(V x, V n) {
+        int which = rng.u() * components();
+        if (which == 0) return cosine_sample(n);
+        return light_sample(x);
+    }
+    float mix_pdf(V x, V n, V d) const {
+        float ans = 0;
+        ans += cosine_pdf(n, d);
+        if (s.n_light_prims > 0) {
+            if (cnt) cnt->light_queries++;
+            ans += light_total(0, x, d) / (size_t)s.n_light_prims;
+        }
+        return ans / components();
+    }
+
+    // Scene::getColor (hw5/src/scene.cpp:47-105)
+    V color(const Ray &ray, int rec) {
+        if (rec == 0) return V(0., 0., 0.);
+        Hit h; int pos = -1;
+        if (cnt) cnt->rays++;
+        if (!intersect(ray, h, pos)) return V(s.bg_color);
+        rng.begin_bounce((uint32_t)(s.ray_depth - rec));
+        const b200rt_primitive &f = s.prims[pos];
+        float t = h.t; V norma = h.norma; bool is_inside = h.inside;
+        V x = ray.o + t * ray.d;
+        V emission(f.emission), fcolor(f.color);
+        if (f.material == B200RT_MAT_DIFFUSE) {
+            V d = mix_sample(x + eps * norma, norma);
+            if (d.dot(norma) < 0) return emission;
+            float pdf = mix_pdf(x + eps * norma, norma, d);
+            Ray dRay(x + eps * d, d);
+            return emission + 1. / (PI * pdf) * d.dot(norma) * fcolor * color(dRay, rec - 1);
+        } else if (f.material == B200RT_MAT_METALLIC) {
+            V reflectedDir = ray.d.normalize() - 2. * norma.dot(ray.d.normalize()) * norma;
+            Ray reflected(ray.o + t * ray.d + eps * reflectedDir, reflectedDir);
+            return emission + fcolor * color(reflected, rec - 1);
+        } else {
+            V reflectedDir = ray.d.normalize() - 2. * norma.dot(ray.d.normalize()) * norma;
+            Ray reflected(ray.o + t * ray.d + eps * reflectedDir, reflectedDir);
+            // reference: reflected branch traced before, and regardless of, the Fresnel coin (see Hw4::color)
+            V reflectedColor;
+            float coin = 0;
+            if (Rng::kCounterBased) coin = rng.u();
+            else reflectedColor = color(reflected, rec - 1);
+            float eta1 = 1., eta2 = f.ior;
+            if (is_inside) std::swap(eta1, eta2);
+            V l = -1. * ray.d.normalize();
+            float sinTheta2 = eta1 / eta2 * sqrt(1 - norma.dot(l) * norma.dot(l));
+            if (fabs(sinTheta2) > 1.) {
+                if (Rng::kCounterBased) reflectedColor = color(reflected, rec - 1);
+                return emission + reflectedColor;
+            }
+            float r0 = pow((eta1 - eta2) / (eta1 + eta2), 2.);
+            float r = r0 + (1 - r0) * pow(1 - norma.dot(l), 5.);
+            if (!Rng::kCounterBased) coin = rng.u();
+            if (coin < r) {
+                if (Rng::kCounterBased) reflectedColor = color(reflected, rec - 1);
+                return emission + reflectedColor;
+            }
+            float cosTheta2 = sqrt(1 - sinTheta2 * sinTheta2);
+            V refractedDir = eta1 / eta2 * (-1. * l) + (eta1 / eta2 * norma.dot(l) - cosTheta2) * norma;
+            Ray refracted(ray.o + t * ray.d + eps * refractedDir, refractedDir);
+            V refractedColor = color(refracted, rec - 1);
+            if (!is_inside) refractedColor = refractedColor * fcolor;
+            return emission + refractedColor;
+        }
+    }
+
+    Ray camera_ray(float x, float y) const {   // fovX based, jitter only (hw5/src/scene.cpp:119-126)
+        float tanFovX = tan(s.cam_fov / 2);
+        float tanFovY = tanFovX * s.height / s.width;
+        float nx = tanFovX * (2 * x / s.width - 1);
+        float ny = tanFovY * (2 * y / s.height - 1);
+        return {V(s.cam_pos), nx * V(s.cam_right) - ny * V(s.cam_up) + V(s.cam_forward)};
+    }
+    V pixel_sum(int x, int y, int b, int e) {
+        V c{0, 0, 0};
+        for (int k = b; k < e; k++) {
+            rng.begin_sample((uint32_t)k);
+            float nx = x + rng.u();
+            float ny = y + rng.u();
+            c = c + color(camera_ray(nx, ny), s.ray_depth);
+        }
+        return c;
+    }
+};
+
 }  // namespace mc
 
 // ------------------------------------------------------------------------------------------
@@ -841,7 +1107,7 @@ void render_mc(const b200rt_scene_desc &s, int rng_kind, uint32_t seed, int b, i
                uint64_t *counters) {
     mc::Counters cnt;
     mc::Counters *cp = counters ? &cnt : nullptr;
-    if (s.mode == B200RT_MODE_HW4) {
+    if (s.mode == B200RT_MODE_HW3 || s.mode == B200RT_MODE_HW4) {
         if (rng_kind == 0) {
             // hw4: one global generator consumed in scan order (hw4/src/scene.cpp:5-6) => serial.
             mc::Hw4Minstd rng;
@@ -857,6 +1123,9 @@ void render_mc(const b200rt_scene_desc &s, int rng_kind, uint32_t seed, int b, i
         } else {
             render_per_pixel_rng<Hw4Adapter<mc::Hw4Philox>, mc::Hw4Philox>(s, seed, b, e, accum, rgb, nullptr);
         }
+    } else if (s.mode == B200RT_MODE_HW5) {
+        if (rng_kind == 0) render_per_pixel_rng<mc::Hw5<RngMinstd>, RngMinstd>(s, seed, b, e, accum, rgb, cp);
+        else render_per_pixel_rng<mc::Hw5<RngPhilox>, RngPhilox>(s, seed, b, e, accum, rgb, cp);
     } else if (s.mode == B200RT_MODE_HW6) {
         if (rng_kind == 0) render_per_pixel_rng<mc::Hw6<RngMinstd>, RngMinstd>(s, seed, b, e, accum, rgb, cp);
         else render_per_pixel_rng<mc::Hw6<RngPhilox>, RngPhilox>(s, seed, b, e, accum, rgb, cp);

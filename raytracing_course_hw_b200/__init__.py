@@ -69,7 +69,8 @@ class SceneDesc(ctypes.Structure):
                 ("light_nodes", ctypes.c_void_p), ("n_light_nodes", ctypes.c_int32),
                 ("materials", ctypes.c_void_p), ("n_materials", ctypes.c_int32),
                 ("images", ctypes.POINTER(Image)), ("n_images", ctypes.c_int32),
-                ("env_map", ctypes.POINTER(Image))]
+                ("env_map", ctypes.POINTER(Image)),
+                ("light_prims", ctypes.c_void_p), ("n_light_prims", ctypes.c_int32), ("n_bvh_prims", ctypes.c_int32)]
 
 
 _host = None

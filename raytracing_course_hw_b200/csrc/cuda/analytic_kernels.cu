@@ -1,4 +1,4 @@
-// K1 (hw1 primary cast), K2 (hw2 Whitted), K3 (hw4 analytic path tracer) for sm_100a.
+// K1 (hw1 primary cast), K2 (hw2 Whitted), K3 (hw3 / hw4 analytic path tracers), K7 (hw5 mixed figures) for sm_100a.
 // Compiled with -fmad=false: every float operation below is written in the reference's own
 // order and with its float/double promotions, so that the deterministic configs (hw1, hw2)
 // reproduce primary-hit indices and radiance bit for bit (north_star).
@@ -8,6 +8,7 @@
 // Primitives and lights live in __constant__ memory (<= 64 + 16 entries, warp-uniform reads).
 #include "analytic_kernels.h"
 #include "rt_math.cuh"
+#include "gltf_kernel.cuh"      // hw5: the triangles of a text scene go through the glTF modes' BVH traversal
 
 namespace b200rt {
 
@@ -298,7 +299,9 @@ __device__ __forceinline__ V3 light_sample(const b200rt_primitive &f, V3 x, Rng 
             const float wx = sy * sz, wy = sx * sz, wz = sx * sy;
             const float u = rng.u() * (wx + wy + wz);
             const float flip = rng.u() > 0.5f ? 1.f : -1.f;
-            const float a = rng.u(), b = rng.u();
+            // the reference's Vec3(...) constructor call evaluates its arguments right to left: the LATER coordinate
+            // takes the earlier draw (oracle/port_mc.cpp, pinned against the hw4 / hw5 binaries)
+            const float b = rng.u(), a = rng.u();
             if (u < wx) point = mk(flip * sx, (2 * a - 1) * sy, (2 * b - 1) * sz);
             else if (u < wx + wy) point = mk((2 * a - 1) * sx, flip * sy, (2 * b - 1) * sz);
             else point = mk((2 * a - 1) * sx, (2 * b - 1) * sy, flip * sz);
@@ -314,6 +317,10 @@ __device__ __forceinline__ V3 light_sample(const b200rt_primitive &f, V3 x, Rng 
     return dir;
 }
 
+// HW3 = the uniform-hemisphere integrator of hw3 (hw3/src/scene.cpp:31-106): the diffuse bounce draws a uniform
+// direction on the hemisphere around the normal and weighs it by 2 (w . n) colour; planes have no T_MAX yet
+// (hw3/src/primitives.cpp:72); the camera adds 0.5 to the jittered pixel position (hw3/src/scene.cpp:103-104).
+template <bool HW3>
 __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp) {
     const int W = rp.cam.width, H = rp.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
@@ -340,8 +347,9 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                 // hw4 camera: jitter only, no +0.5, fovX based, NOT normalised (scene.cpp:113-128)
                 const float fx = (float)px + rng.u();
                 const float fy = (float)py + rng.u();
-                const float nx = rp.cam.tan_x * (2 * fx / W - 1);
-                const float ny = rp.cam.tan_y * (2 * fy / H - 1);
+                // hw3: 2 * (x + 0.5) / width - 1 is evaluated in double (the 0.5 literal), then rounded
+                const float nx = HW3 ? rp.cam.tan_x * (float)(2 * ((double)fx + 0.5) / W - 1) : rp.cam.tan_x * (2 * fx / W - 1);
+                const float ny = HW3 ? rp.cam.tan_y * (float)(2 * ((double)fy + 0.5) / H - 1) : rp.cam.tan_y * (2 * fy / H - 1);
                 V3 o = ld3(rp.cam.pos);
                 V3 d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
                 V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
@@ -349,13 +357,21 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                 for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
                     AHit h;
                     rays++;
-                    const int pos = closest_prim(o, d, INFINITY, true, h);
+                    const int pos = closest_prim(o, d, INFINITY, !HW3, h);
                     if (pos < 0) { L = L + T * ld3(g_scene.bg); break; }
                     rng.begin_bounce((uint32_t)bounce);
                     const b200rt_primitive &f = g_scene.prims[pos];
                     const V3 x = o + h.t * d;
                     L = L + T * ld3(f.emission);
-                    if (f.material == B200RT_MAT_DIFFUSE) {
+                    if (HW3 && f.material == B200RT_MAT_DIFFUSE) {
+                        // uniform direction on the sphere (the reference normalises three normals), mirrored into
+                        // the hemisphere of the normal; weight 2 (w . n) colour = colour/pi * cos / (1 / 2pi)
+                        const float u1 = rng.u(), u2 = rng.u();
+                        V3 w = sphere_dir(u1, u2);
+                        if (dot(w, h.n) < 0) w = -1.f * w;
+                        T = T * ((2 * dot(w, h.n)) * ld3(f.color));
+                        o = x + 0.0001f * w; d = w;
+                    } else if (f.material == B200RT_MAT_DIFFUSE) {
                         const V3 xs = x + 0.0001f * h.n;
                         // Mix::sample: uniform choice between Cosine and the light mixture
                         const int k = n_lights > 0 ? 2 : 1;
@@ -431,6 +447,153 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
     }
 }
 
+// ---- K7: hw5 -- text scenes with TRIANGLE figures ------------------------------------------------
+// hw5/src/scene.cpp:25-126 with hw5/src/include/distributions.h:61-302.  The reference keeps ellipsoids, boxes and
+// triangles in ONE BVH of Figures and scans the planes; here the analytic figures (planes, ellipsoids, boxes: a
+// handful) are scanned in constant memory like hw4's, and the triangles -- baked to world space at upload -- go
+// through the glTF modes' tree and traversal (closest hit and light-pdf sum do not depend on how the acceleration
+// structure is organised).  The light mixture is FiguresMix over all three emissive kinds in the reference's
+// order: `light_order[i]` >= 0 names an analytic figure, < 0 the emissive triangle ~light_order[i].
+// Integrator = hw4's / hw6's (diffuse with Mix{Cosine, lights}, mirror, dielectric with the Fresnel coin first).
+// Stream layout = oracle/port_mc.cpp Hw5<RngPhilox>, draw for draw (sequential Rng view).
+__global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, const DRenderParams rp, const int32_t *__restrict__ light_order,
+                                                       const int n_lights, const int has_tris) {
+    const int W = rp.cam.width, H = rp.cam.height;
+    const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
+    const long long n_tiles = (long long)tiles_x * tiles_y;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    ThreadCounters tc = {};
+    if (warp_id < n_tiles * rp.n_chunks) {
+        const int chunk = (int)(warp_id / n_tiles);
+        const long long tile = warp_id % n_tiles;
+        const int px = (int)(tile % tiles_x) * 8 + (lane & 7);
+        const int py = (int)(tile / tiles_x) * 4 + (lane >> 3);
+        if (px < W && py < H) {
+            const int total = rp.spp_end - rp.spp_begin;
+            const int per = (total + rp.n_chunks - 1) / rp.n_chunks;
+            const int s0 = rp.spp_begin + chunk * per;
+            const int s1 = min(rp.spp_end, s0 + per);
+            Rng rng;
+            rng.pixel = (uint32_t)(py * W + px); rng.seed = rp.seed;
+            V3 sum = mk(0, 0, 0);
+            for (int s = s0; s < s1; s++) {
+                rng.begin_sample((uint32_t)s);
+                // camera of hw4 / hw5: jitter only, fovX based, NOT normalised (hw5/src/scene.cpp:107-126)
+                const float fx = (float)px + rng.u();
+                const float fy = (float)py + rng.u();
+                const float nx = rp.cam.tan_x * (2 * fx / W - 1);
+                const float ny = rp.cam.tan_y * (2 * fy / H - 1);
+                V3 o = ld3(rp.cam.pos);
+                V3 d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
+                V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
+                tc.paths++;
+                for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
+                    // Scene::intersect: analytic figures by scan, triangles through the BVH, nearest wins
+                    AHit h;
+                    tc.rays++;
+                    const int pos = closest_prim(o, d, INFINITY, true, h);
+                    TraceHit th;
+                    th.tri = -1;
+                    if (has_tris) trace_closest<false>(sc, o, d, th, tc);
+                    const bool on_tri = th.tri >= 0 && (pos < 0 || th.t < h.t);
+                    if (pos < 0 && !on_tri) { L = L + T * ld3(sc.bg); break; }
+                    rng.begin_bounce((uint32_t)bounce);
+                    V3 emission, color;
+                    int material;
+                    float ior;
+                    if (on_tri) {
+                        const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + th.tri);
+                        const float4 tv0 = __ldg(tq), te1 = __ldg(tq + 1), te2 = __ldg(tq + 2);
+                        V3 n = normalize(cross(mk(te2.x, te2.y, te2.z), mk(te1.x, te1.y, te1.z)));
+                        h.inside = th.det > 0.f;
+                        h.n = h.inside ? -n : n;
+                        h.t = th.t;
+                        const DMaterial *m = sc.materials + __float_as_int(tv0.w);
+                        emission = mk(__ldg(&m->emission[0]), __ldg(&m->emission[1]), __ldg(&m->emission[2]));
+                        color = mk(__ldg(&m->base_color[0]), __ldg(&m->base_color[1]), __ldg(&m->base_color[2]));
+                        material = __ldg(&m->kind);
+                        ior = __ldg(&m->ior);
+                    } else {
+                        const b200rt_primitive &f = g_scene.prims[pos];
+                        emission = ld3(f.emission); color = ld3(f.color); material = f.material; ior = f.ior;
+                    }
+                    const V3 x = o + h.t * d;
+                    L = L + T * emission;
+                    if (material == B200RT_MAT_DIFFUSE) {
+                        const V3 xs = x + 0.0001f * h.n;
+                        const int k = n_lights > 0 ? 2 : 1;
+                        const int which = (int)(rng.u() * k);
+                        V3 nd;
+                        if (which == 0) {
+                            const float u1 = rng.u(), u2 = rng.u();
+                            V3 c = sphere_dir(u1, u2) + h.n;
+                            const float l = sqrtf(dot(c, c));
+                            nd = (l <= 1e-9f || dot(c, h.n) <= 1e-9f || isnan(l)) ? h.n : (1.f / l) * c;
+                        } else {
+                            // FiguresMix::sample: index, then the sampler of that light's kind
+                            const int li = min((int)(rng.u() * n_lights), n_lights - 1);
+                            const int32_t e = __ldg(light_order + li);
+                            if (e >= 0) {
+                                nd = light_sample(g_scene.prims[e], xs, rng);
+                            } else {
+                                const float4 *lq = reinterpret_cast<const float4 *>(sc.light_sample_tris + ~e);
+                                const float4 a = __ldg(lq), b = __ldg(lq + 1), c = __ldg(lq + 2);
+                                float lu = rng.u(), lv = rng.u();
+                                if (lu + lv > 1.f) { lu = 1.f - lu; lv = 1.f - lv; }
+                                const V3 point = mk(a.x + lu * b.x + lv * c.x, a.y + lu * b.y + lv * c.y, a.z + lu * b.z + lv * c.z);
+                                nd = rnorm(point - xs);
+                            }
+                        }
+                        if (dot(nd, h.n) < 0) break;
+                        float pdf = smax(0.f, dot(nd, h.n) / B200RT_PI_F);
+                        if (n_lights > 0) {
+                            // FiguresMix::pdf: every emissive figure the ray pierces contributes (both hits for closed ones)
+                            tc.light_queries++;
+                            float inner = 0;
+                            for (int li = 0; li < g_scene.n_light_prims; li++) inner += light_pdf(g_scene.prims[g_scene.light_prims[li]], xs, nd);
+                            if (sc.n_light_tris > 0) inner += light_pdf_sum<false>(sc, xs, nd, tc);
+                            pdf = (pdf + inner / n_lights) / 2;
+                        }
+                        const float w = (1.f / (B200RT_PI_F * pdf)) * dot(nd, h.n);
+                        T = T * (w * color);
+                        o = x + 0.0001f * nd; d = nd;
+                    } else {
+                        const V3 dn = rnorm(d);
+                        V3 nd = dn - (2.f * dot(h.n, dn)) * h.n;
+                        if (material == B200RT_MAT_METALLIC) {
+                            T = T * color;
+                        } else {
+                            const float coin = rng.u();      // Fresnel coin first (see K3)
+                            float eta1 = 1.f, eta2 = ior;
+                            if (h.inside) { const float sw = eta1; eta1 = eta2; eta2 = sw; }
+                            const V3 l = -1.f * dn;
+                            const float nl = dot(h.n, l);
+                            const float sin2 = eta1 / eta2 * sqrtf(1 - nl * nl);
+                            if (!(fabsf(sin2) > 1.f)) {
+                                const float q = (eta1 - eta2) / (eta1 + eta2);
+                                const float r0 = q * q;
+                                const float b1 = 1 - nl, b2 = b1 * b1;
+                                const float r = r0 + (1 - r0) * (b2 * b2 * b1);
+                                if (!(coin < r)) {
+                                    const float cos2 = sqrtf(1 - sin2 * sin2);
+                                    nd = (eta1 / eta2) * (-1.f * l) + (eta1 / eta2 * nl - cos2) * h.n;
+                                    if (!h.inside) T = T * color;
+                                }
+                            }
+                        }
+                        o = x + 0.0001f * nd; d = nd;
+                    }
+                }
+                sum = sum + L;
+            }
+            float *dst = rp.accum + ((size_t)chunk * W * H + (size_t)(py * W + px)) * 3;
+            dst[0] = sum.x; dst[1] = sum.y; dst[2] = sum.z;
+        }
+    }
+    flush_counters(rp.counters, tc);
+}
+
 }  // namespace
 
 cudaError_t launch_cast(const DCamera &cam, float *out, int32_t *ids, cudaStream_t stream) {
@@ -446,11 +609,20 @@ cudaError_t launch_whitted(const DCamera &cam, int ray_depth, float *out, int32_
     return cudaGetLastError();
 }
 
-cudaError_t launch_pt_analytic(const DRenderParams &rp, cudaStream_t stream) {
+cudaError_t launch_pt_analytic(const DRenderParams &rp, bool hw3, cudaStream_t stream) {
     const long long tiles = (long long)((rp.cam.width + 7) / 8) * ((rp.cam.height + 3) / 4);
     const long long warps = tiles * rp.n_chunks;
     const long long blocks = (warps * 32 + 127) / 128;
-    pt_analytic_kernel<<<(unsigned)blocks, 128, 0, stream>>>(rp);
+    if (hw3) pt_analytic_kernel<true><<<(unsigned)blocks, 128, 0, stream>>>(rp);
+    else pt_analytic_kernel<false><<<(unsigned)blocks, 128, 0, stream>>>(rp);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_hw5(const DGltfScene &sc, const DRenderParams &rp, const int32_t *light_order, int n_lights, bool has_tris, cudaStream_t stream) {
+    const long long tiles = (long long)((rp.cam.width + 7) / 8) * ((rp.cam.height + 3) / 4);
+    const long long warps = tiles * rp.n_chunks;
+    const long long blocks = (warps * 32 + 127) / 128;
+    hw5_path_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, rp, light_order, n_lights, has_tris ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -17,6 +17,38 @@
 #include "bvh_rebuild.h"
 #include <chrono>
 #include <thread>
+#ifdef B200RT_DBG_SORT
+// development experiment only (not in the product build): host-synchronised sort of a bounce's ray queue,
+// to measure what ray coherence is worth to the traversal before building a device-side counting sort
+#include <thrust/device_ptr.h>
+#include <thrust/sort.h>
+#include <thrust/execution_policy.h>
+namespace b200rt {
+__device__ __forceinline__ uint32_t dbg_spread3(uint32_t x) {   // 10 bits -> every third bit
+    x &= 0x3FFu;
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+__global__ void dbg_sort_keys(const DGltfScene sc, const WaveBuffers wb, const int *q, int n, uint32_t *keys, int mode, int obits) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int p = q[i];
+    const float4 ro = wb.ray_o[p], rd = wb.ray_d[p];
+    const float gmax = B200RT_QBITS == 15 ? 32768.f : 65536.f;
+    const float s = (float)(1 << obits) / gmax;
+    const int m = (1 << obits) - 1;
+    const uint32_t gx = (uint32_t)min(max((int)((ro.x - sc.q.base[0]) * sc.q.inv_scale[0] * s), 0), m);
+    const uint32_t gy = (uint32_t)min(max((int)((ro.y - sc.q.base[1]) * sc.q.inv_scale[1] * s), 0), m);
+    const uint32_t gz = (uint32_t)min(max((int)((ro.z - sc.q.base[2]) * sc.q.inv_scale[2] * s), 0), m);
+    const uint32_t mort = dbg_spread3(gx) | (dbg_spread3(gy) << 1) | (dbg_spread3(gz) << 2);
+    const uint32_t oct = (rd.x < 0.f ? 1u : 0u) | (rd.y < 0.f ? 2u : 0u) | (rd.z < 0.f ? 4u : 0u);
+    keys[i] = mode == 0 ? oct : mode == 1 ? ((oct << (3 * obits)) | mort) : mode == 2 ? ((mort << 3) | oct) : mort;
+}
+}
+#endif
 
 using namespace b200rt;
 
@@ -42,6 +74,11 @@ struct b200rt_ctx {
     float *lut_srgb = nullptr;
     RebuiltBvh own_bvh;                      // host scratch of the BVH rebuild (bvh_rebuild.h)
     std::vector<b200rt_triangle> own_tris;   // triangles in the rebuilt tree's order
+
+    // hw5: FiguresMix order over the mixed light kinds (>= 0 analytic figure, < 0 ~emissive-triangle index)
+    int32_t *hw5_light_order = nullptr;
+    int hw5_n_lights = 0, hw5_light_cap = 0;
+    bool hw5_has_tris = false;
 
     int acc_w = 0, acc_h = 0, n_slabs = 0;
     float *total = nullptr, *slabs = nullptr;
@@ -394,12 +431,13 @@ void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, 
     }
 }
 
-int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
+int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s, bool trees_absent = false) {
     if (s->n_tris < 0 || s->n_tris >= (1 << 27)) return fail(ctx, B200RT_ERR_INVALID, "triangle count out of range");
     if (s->n_tris > 0 && (!s->tris || !s->materials)) return fail(ctx, B200RT_ERR_INVALID, "missing triangle/material arrays");
     if (s->n_light_tris < 0 || s->n_materials < 0) return fail(ctx, B200RT_ERR_INVALID, "negative array size");
-    if (!validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
-    if (s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
+    // trees_absent: the caller has triangles but no trees over them (hw5); mode hw6 then rebuilds both anyway
+    if (!trees_absent && !validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
+    if (!trees_absent && s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
 
     DGltfScene g{};
     g.hw8 = s->mode == B200RT_MODE_HW8;
@@ -698,6 +736,20 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         (*launches)++;
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
+#ifdef B200RT_DBG_SORT
+            if (b > 0 && getenv("B200RT_DBG_SORT_MODE")) {
+                static uint32_t *keys = nullptr;
+                if (!keys) CK(cudaMalloc(&keys, ctx->wave_capacity * sizeof(uint32_t)));
+                int n_rays = 0;
+                CK(cudaMemcpyAsync(&n_rays, wb.ctr + 4 * b - 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                if (n_rays > 0) {
+                    const char *e = getenv("B200RT_DBG_SORT_BITS");
+                    dbg_sort_keys<<<(n_rays + 255) / 256, 256, 0, st>>>(ctx->gs, wb, qa, n_rays, keys, atoi(getenv("B200RT_DBG_SORT_MODE")), e ? atoi(e) : 5);
+                    thrust::sort_by_key(thrust::cuda::par.on(st), thrust::device_pointer_cast(keys), thrust::device_pointer_cast(keys) + n_rays, thrust::device_pointer_cast(qa));
+                }
+            }
+#endif
             int *c = wb.ctr + 4 * b;     // c[-1] rays in, c[0] extend cursor, c[1] light cursor, c[2] light queries, c[3] rays into b+1
             if (ctx->wf_fused && lights) {
                 // fused scheduling: the traversal of bounce b also answers the light-pdf query of
@@ -744,6 +796,98 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         CK(cudaEventRecord(ctx->ev_join[k], ctx->pipe_stream[k]));
         CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[k], 0));
     }
+    return B200RT_OK;
+}
+
+// hw5 (text scene with TRIANGLE figures): analytic figures -> constant memory like hw4; triangles -> baked to world
+// space (position + conj(rotation) applied, hw5/src/primitives.cpp:13-33 runs the same transform per ray) and uploaded
+// through the glTF path as an hw6-style scene with one material per triangle; the trees of the description (which
+// mix figure kinds) are not used: closest hits and light-pdf sums are tree-independent, the library builds its own.
+struct HQuat { float x, y, z, w; };
+inline HQuat hq_mul(const HQuat &a, const HQuat &b) {
+    // Quaternion::operator* with the reference's negated cross (hw5/src/include/quaternion.h:36-38)
+    return {a.w * b.x + b.w * a.x + (a.z * b.y - a.y * b.z), a.w * b.y + b.w * a.y + (a.x * b.z - a.z * b.x),
+            a.w * b.z + b.w * a.z + (a.y * b.x - a.x * b.y), a.w * b.w - (a.x * b.x + a.y * b.y + a.z * b.z)};
+}
+inline void hq_to_world(const b200rt_primitive &f, const float *v, float *out) {
+    const HQuat q{-f.rotation[0], -f.rotation[1], -f.rotation[2], f.rotation[3]};      // rotation.conjugate()
+    const HQuat r = hq_mul(hq_mul(q, HQuat{v[0], v[1], v[2], 0.f}), HQuat{-q.x, -q.y, -q.z, q.w});
+    out[0] = f.position[0] + r.x; out[1] = f.position[1] + r.y; out[2] = f.position[2] + r.z;
+}
+
+int upload_hw5(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
+    if (s->n_prims < 0 || (s->n_prims && !s->prims) || s->n_light_prims < 0 || (s->n_light_prims && !s->light_prims))
+        return fail(ctx, B200RT_ERR_INVALID, "missing figure / light arrays");
+    static DAnalyticScene a;
+    memset(&a, 0, sizeof(a));
+    std::vector<b200rt_triangle> tris, ltris;
+    std::vector<b200rt_material> mats;
+    auto bake = [](const b200rt_primitive &f, uint32_t material) {
+        b200rt_triangle t{};
+        hq_to_world(f, f.data, t.p[0]); hq_to_world(f, f.data2, t.p[1]); hq_to_world(f, f.data3, t.p[2]);
+        for (int v = 0; v < 3; v++) { t.n[v][2] = 1.f; t.tan[v][0] = 1.f; t.tan[v][3] = 1.f; }   // unused by the hw5 / hw6 integrator
+        t.material = material;
+        return t;
+    };
+    for (int i = 0; i < s->n_prims; i++) {
+        const b200rt_primitive &f = s->prims[i];
+        if (f.type == B200RT_PRIM_TRIANGLE) {
+            b200rt_material m{};
+            for (int k = 0; k < 3; k++) { m.base_color[k] = f.color[k]; m.emission[k] = f.emission[k]; }
+            m.base_color_image = m.emissive_image = m.metallic_roughness_image = m.normal_image = -1;
+            m.kind = f.material; m.ior = f.ior;
+            tris.push_back(bake(f, (uint32_t)mats.size()));
+            mats.push_back(m);
+        } else {
+            if (a.n_prims >= B200RT_MAX_PRIMS) return fail(ctx, B200RT_ERR_UNSUPPORTED, "too many analytic figures (planes / ellipsoids / boxes) for the constant-memory scan");
+            a.prims[a.n_prims++] = f;
+        }
+    }
+    // FiguresMix::figures_ order; analytic lights are found among the scanned figures by value (the list holds copies)
+    std::vector<int32_t> order((size_t)s->n_light_prims);
+    for (int i = 0; i < s->n_light_prims; i++) {
+        const b200rt_primitive &f = s->light_prims[i];
+        if (f.type == B200RT_PRIM_TRIANGLE) {
+            order[(size_t)i] = ~(int32_t)ltris.size();
+            ltris.push_back(bake(f, 0));
+        } else {
+            int found = -1;
+            for (int k = 0; k < a.n_prims && found < 0; k++)
+                if (memcmp(&a.prims[k], &f, sizeof(f)) == 0) found = k;
+            if (found < 0 || (f.type != B200RT_PRIM_BOX && f.type != B200RT_PRIM_ELLIPSOID)) return fail(ctx, B200RT_ERR_INVALID, "light figure not among the scene figures");
+            order[(size_t)i] = found;
+            bool seen = false;
+            for (int k = 0; k < a.n_light_prims; k++) seen = seen || a.light_prims[k] == found;
+            if (!seen) a.light_prims[a.n_light_prims++] = found;
+        }
+    }
+    a.mode = s->mode;
+    for (int k = 0; k < 3; k++) a.bg[k] = s->bg_color[k];
+    CK(analytic_upload(a, ctx->stream));
+    ctx->hw5_has_tris = !tris.empty();
+    ctx->gs = DGltfScene{};
+    for (int k = 0; k < 3; k++) ctx->gs.bg[k] = s->bg_color[k];
+    if (!tris.empty()) {
+        b200rt_scene_desc t = *s;
+        t.mode = B200RT_MODE_HW6;
+        t.prims = nullptr; t.n_prims = 0; t.light_prims = nullptr; t.n_light_prims = 0;
+        t.tris = tris.data(); t.n_tris = (int32_t)tris.size();
+        t.nodes = nullptr; t.n_nodes = 0; t.root = 0;
+        t.light_tris = ltris.data(); t.n_light_tris = (int32_t)ltris.size();
+        t.light_nodes = nullptr; t.n_light_nodes = 0;
+        t.materials = mats.data(); t.n_materials = (int32_t)mats.size();
+        t.images = nullptr; t.n_images = 0; t.env_map = nullptr;
+        const int rc = upload_gltf(ctx, &t, true);
+        if (rc) return rc;
+    }
+    if (s->n_light_prims > ctx->hw5_light_cap) {
+        cudaFree(ctx->hw5_light_order); ctx->hw5_light_order = nullptr; ctx->hw5_light_cap = 0;
+        CK(cudaMalloc(&ctx->hw5_light_order, (size_t)s->n_light_prims * sizeof(int32_t)));
+        ctx->hw5_light_cap = s->n_light_prims;
+    }
+    if (s->n_light_prims > 0) CK(cudaMemcpyAsync(ctx->hw5_light_order, order.data(), order.size() * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));      // `order` and the staging vectors die with this frame
+    ctx->hw5_n_lights = s->n_light_prims;
     return B200RT_OK;
 }
 
@@ -827,6 +971,7 @@ void b200rt_destroy(b200rt_ctx *ctx) {
         cudaEventDestroy(ctx->ev_join[k]); cudaEventDestroy(ctx->ev_acc[k]);
     }
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+    cudaFree(ctx->hw5_light_order);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -839,7 +984,7 @@ int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     release_scene(ctx);
     int rc = B200RT_OK;
     switch (s->mode) {
-        case B200RT_MODE_HW1: case B200RT_MODE_HW2: case B200RT_MODE_HW4: {
+        case B200RT_MODE_HW1: case B200RT_MODE_HW2: case B200RT_MODE_HW3: case B200RT_MODE_HW4: {
             if (s->n_prims < 0 || s->n_prims > B200RT_MAX_PRIMS || s->n_lights < 0 || s->n_lights > B200RT_MAX_LIGHTS)
                 return fail(ctx, B200RT_ERR_UNSUPPORTED, "too many primitives/lights for the analytic kernels");
             if ((s->n_prims && !s->prims) || (s->n_lights && !s->lights)) return fail(ctx, B200RT_ERR_INVALID, "missing primitive/light arrays");
@@ -859,17 +1004,20 @@ int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
             CK(analytic_upload(a, ctx->stream));
             break;
         }
+        case B200RT_MODE_HW5:
+            rc = upload_hw5(ctx, s);
+            break;
         case B200RT_MODE_HW6: case B200RT_MODE_HW7: case B200RT_MODE_HW8:
             rc = upload_gltf(ctx, s);
             break;
         default:
-            return fail(ctx, B200RT_ERR_UNSUPPORTED, "scene mode not implemented on the device path (hw3, hw5)");
+            return fail(ctx, B200RT_ERR_UNSUPPORTED, "unknown scene mode");
     }
     if (rc) { release_scene(ctx); return rc; }
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->desc = *s;
     ctx->desc.prims = nullptr; ctx->desc.lights = nullptr; ctx->desc.tris = nullptr; ctx->desc.nodes = nullptr;
-    ctx->desc.light_tris = nullptr; ctx->desc.light_nodes = nullptr; ctx->desc.materials = nullptr; ctx->desc.images = nullptr; ctx->desc.env_map = nullptr;
+    ctx->desc.light_tris = nullptr; ctx->desc.light_nodes = nullptr; ctx->desc.light_prims = nullptr; ctx->desc.materials = nullptr; ctx->desc.images = nullptr; ctx->desc.env_map = nullptr;
     ctx->has_scene = true;
     return b200rt_clear(ctx);
 }
@@ -917,7 +1065,11 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
     int launches = 0;
     if (d.mode == B200RT_MODE_HW1) { CK(launch_cast(rp.cam, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
     else if (d.mode == B200RT_MODE_HW2) { CK(launch_whitted(rp.cam, ray_depth, ctx->slabs, ctx->ids, ctx->stream)); launches++; }
-    else if (d.mode == B200RT_MODE_HW4) { CK(launch_pt_analytic(rp, ctx->stream)); launches++; }
+    else if (d.mode == B200RT_MODE_HW3 || d.mode == B200RT_MODE_HW4) { CK(launch_pt_analytic(rp, d.mode == B200RT_MODE_HW3, ctx->stream)); launches++; }
+    else if (d.mode == B200RT_MODE_HW5) {
+        CK(launch_hw5(ctx->gs, rp, ctx->hw5_light_order, ctx->hw5_n_lights, ctx->hw5_has_tris, ctx->stream));
+        launches++;
+    }
     else if (d.mode == B200RT_MODE_HW6) {
         const long long warps = (long long)((width + 7) / 8) * ((height + 3) / 4) * n_chunks;
         const long long blocks = (warps * 32 + 127) / 128;

@@ -6,6 +6,7 @@
 #include <fstream>
 #include <new>
 #include "bvh_build.h"
+#include "hmath.h"
 #include "host_scene.h"
 
 #if defined(B200RT_HAVE_STB)
@@ -90,6 +91,87 @@ void build_triangle_accel(b200rt_host_scene &s) {
     s.light_nodes.clear();
     if (n > 0) build_over(s.light_tris, (uint32_t)n, s.light_nodes, nullptr, hw6_key);
     // n == 0: the reference still builds a one-node BVH over nothing but never uses it.
+}
+
+// ---- hw5: figures of mixed type in the BVH -------------------------------------------------------------
+// Quaternion product / transform with the reference's operation order (hw5/src/include/quaternion.h:36-48;
+// its cross is the negated one, vec3.h:57-59) so that rotated boxes get bit-identical AABBs: the SAH build
+// compares scores with == (bvh.h:96-104), a last-ulp difference could pick another axis and reorder the lights.
+namespace {
+struct Quat { V3 v; float w; };
+inline V3 scale3(float k, const V3 &p) { return {k * p.x, k * p.y, k * p.z}; }
+inline Quat qmul(const Quat &a, const Quat &b) {
+    return {scale3(a.w, b.v) + scale3(b.w, a.v) + a.v.cross_ref(b.v), a.w * b.w - a.v.dot(b.v)};
+}
+inline Quat qconj(const Quat &q) { return {scale3(-1.f, q.v), q.w}; }
+inline V3 qtransform(const Quat &q, const V3 &p) { return qmul(qmul(q, Quat{p, 0.f}), qconj(q)).v; }
+
+// AABB::AABB(const Figure&) (hw5/src/primitives.cpp:166-196)
+BvhItem item_of_figure(const b200rt_primitive &f, uint32_t index) {
+    V3 mn, mx;
+    if (f.type == B200RT_PRIM_TRIANGLE) {
+        mn = V3(std::min(f.data3[0], std::min(f.data[0], f.data2[0])), std::min(f.data3[1], std::min(f.data[1], f.data2[1])),
+                std::min(f.data3[2], std::min(f.data[2], f.data2[2])));
+        mx = V3(std::max(f.data3[0], std::max(f.data[0], f.data2[0])), std::max(f.data3[1], std::max(f.data[1], f.data2[1])),
+                std::max(f.data3[2], std::max(f.data[2], f.data2[2])));
+    } else {
+        mx = V3(f.data[0], f.data[1], f.data[2]);
+        mn = scale3(-1.f, mx);
+    }
+    const Quat rot = qconj(Quat{V3(f.rotation[0], f.rotation[1], f.rotation[2]), f.rotation[3]});
+    const V3 u_mn = mn, u_mx = mx;
+    mn = mx = qtransform(rot, u_mn);
+    auto extend = [&](const V3 &p) {
+        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
+        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
+    };
+    extend(qtransform(rot, V3(u_mn.x, u_mn.y, u_mx.z)));
+    extend(qtransform(rot, V3(u_mn.x, u_mx.y, u_mn.z)));
+    extend(qtransform(rot, V3(u_mn.x, u_mx.y, u_mx.z)));
+    extend(qtransform(rot, V3(u_mx.x, u_mn.y, u_mn.z)));
+    extend(qtransform(rot, V3(u_mx.x, u_mn.y, u_mx.z)));
+    extend(qtransform(rot, V3(u_mx.x, u_mx.y, u_mn.z)));
+    extend(qtransform(rot, V3(u_mx.x, u_mx.y, u_mx.z)));
+    const V3 pos(f.position[0], f.position[1], f.position[2]);
+    mn = mn + pos; mx = mx + pos;
+    BvhItem it;
+    it.key[0] = pos.x; it.key[1] = pos.y; it.key[2] = pos.z;      // halfSplit sorts by Figure::position (bvh.h:60-65)
+    it.mn[0] = mn.x; it.mn[1] = mn.y; it.mn[2] = mn.z;
+    it.mx[0] = mx.x; it.mx[1] = mx.y; it.mx[2] = mx.z;
+    it.index = index;
+    return it;
+}
+
+void build_over_figures(std::vector<b200rt_primitive> &figs, uint32_t n, std::vector<b200rt_bvh_node> &nodes, int32_t *root) {
+    std::vector<BvhItem> items(n);
+    for (uint32_t i = 0; i < n; i++) items[i] = item_of_figure(figs[i], i);
+    BvhBuilder b;
+    b.build(items, n);
+    std::vector<b200rt_primitive> sorted(n);
+    for (uint32_t i = 0; i < n; i++) sorted[i] = figs[items[i].index];
+    std::copy(sorted.begin(), sorted.end(), figs.begin());
+    nodes = std::move(b.nodes);
+    if (root) *root = (int32_t)b.root;
+}
+}  // namespace
+
+void build_figure_accel(b200rt_host_scene &s) {
+    // Scene::initBVH: std::partition puts the non-planes first (same algorithm => same permutation)
+    const size_t non_planes = (size_t)(std::partition(s.prims.begin(), s.prims.end(),
+                                                      [](const b200rt_primitive &f) { return f.type != B200RT_PRIM_PLANE; }) - s.prims.begin());
+    build_over_figures(s.prims, (uint32_t)non_planes, s.nodes, &s.desc.root);
+    s.desc.n_bvh_prims = (int32_t)non_planes;
+    // FiguresMix ctor: copy of ALL figures, emissive BOX / ELLIPSOID / TRIANGLE partitioned to the front, second BVH
+    std::vector<b200rt_primitive> copy = s.prims;
+    const size_t n = (size_t)(std::partition(copy.begin(), copy.end(), [](const b200rt_primitive &f) {
+        if (f.emission[0] == 0 && f.emission[1] == 0 && f.emission[2] == 0) return false;
+        return f.type == B200RT_PRIM_BOX || f.type == B200RT_PRIM_ELLIPSOID || f.type == B200RT_PRIM_TRIANGLE;
+    }) - copy.begin());
+    s.light_nodes.clear();
+    // the reference builds this BVH over the partitioned full copy, i.e. the sorts run on the first n entries
+    if (n > 0) build_over_figures(copy, (uint32_t)n, s.light_nodes, nullptr);
+    copy.resize(n);
+    s.light_prims = std::move(copy);
 }
 
 }  // namespace b200rt_host

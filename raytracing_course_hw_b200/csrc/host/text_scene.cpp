@@ -169,6 +169,11 @@ int load_text_scene(const char *path, int32_t mode, b200rt_host_scene &s) {
             }
     if (s.desc.width <= 0 || s.desc.height <= 0) return B200RT_HOST_ERR_PARSE;
     s.parse_ms = now_ms() - t0;
+    if (mode == B200RT_MODE_HW5) {       // hw5/src/sceneio.cpp:92-93: initBVH, then initDistribution
+        double t1 = now_ms();
+        build_figure_accel(s);
+        s.bvh_ms = now_ms() - t1;
+    }
     s.sync();
     return B200RT_OK;
 }

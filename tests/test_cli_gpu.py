@@ -36,6 +36,28 @@ def test_cli_gltf_scene(tmp_path):
     assert abs(img.mean() - truth.mean()) <= 0.02 * truth.mean()
 
 
+def test_cli_hw5_and_hw3_text_scenes(tmp_path):
+    """Text scenes with triangles are hw5 by content; hw3 shares hw4's grammar and is picked with B200RT_MODE."""
+    out = tmp_path / "o.ppm"
+    src = open(os.path.join(ou.SCENES, "hw5/mixed.txt")).read().replace("SAMPLES 4", "SAMPLES 512")
+    scene = tmp_path / "hw5.txt"
+    scene.write_text(src)
+    r = subprocess.run([RUN, str(scene), str(out)], capture_output=True, text=True, env=dict(os.environ, B200RT_STATS="1"))
+    assert r.returncode == 0, r.stderr
+    assert '"mode": 5' in r.stderr
+    img = ou.inv_display(ou.parse_ppm(out.read_bytes()))
+    truth = ou.inv_display(ou.golden("hw5_mixed_spp4096"))
+    assert abs(img.mean() - truth.mean()) <= 0.02 * truth.mean()
+    src = open(os.path.join(ou.GOLDEN, "hw4_p3_1_spp4096.txt")).read().replace("SAMPLES 4096", "SAMPLES 512")
+    scene.write_text(src)
+    r = subprocess.run([RUN, str(scene), str(out)], capture_output=True, text=True, env=dict(os.environ, B200RT_STATS="1", B200RT_MODE="hw3"))
+    assert r.returncode == 0, r.stderr
+    assert '"mode": 3' in r.stderr
+    img = ou.inv_display(ou.parse_ppm(out.read_bytes()))
+    truth = ou.inv_display(ou.golden("hw3_p3_1_spp4096"))
+    assert abs(img.mean() - truth.mean()) <= 0.02 * truth.mean()
+
+
 def test_cli_multi_gpu_sample_split(tmp_path):
     if rt.device_lib().b200rt_device_count() < 2:
         pytest.skip("needs 2 GPUs")

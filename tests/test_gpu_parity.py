@@ -83,6 +83,45 @@ def test_hw4_matches_port_on_same_stream(renderer, k):
     assert abs(acc.mean() - port["accum"].mean()) <= 2e-3 * port["accum"].mean()
 
 
+@pytest.mark.parametrize("k", [1, 3, 4])
+def test_hw3_matches_port_on_same_stream(renderer, k):
+    """hw3 = the uniform-hemisphere integrator (hw3/src/scene.cpp:31-106); hw3 ships hw4's scenes, the mode is
+    explicit (text scenes with SAMPLES are inferred as hw4)."""
+    sc = rt.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16, mode=rt.MODE_HW3)
+    assert sc.mode == rt.MODE_HW3
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1)
+    ok, frac = _mean_close(acc, port["accum"], 16, 0.99)
+    assert ok, frac
+    assert abs(acc.mean() - port["accum"].mean()) <= 2e-3 * port["accum"].mean()
+    # not the hw4 estimator: same scene, same stream, different image
+    sc4 = rt.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16)
+    assert not np.allclose(_render(renderer, sc4), acc)
+
+
+def test_hw5_matches_port_on_same_stream(renderer):
+    """hw5: analytic figures scanned in constant memory + triangles through the library's own BVH (K7) against the
+    port, which walks the reference's mixed-figure BVH: same Philox stream, same image up to float rounding."""
+    sc = rt.load_scene(os.path.join(S, "hw5/mixed.txt"), samples=16)
+    assert sc.mode == rt.MODE_HW5
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1, want_counters=True)
+    ok, frac = _mean_close(acc, port["accum"], 16, 0.97, rel=5e-2)
+    assert ok, frac
+    assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+    st = renderer.stats()
+    assert abs(int(st["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    assert abs(int(st["light_queries"]) - int(port["counters"][3])) <= 2e-3 * int(port["counters"][3])
+
+
+def test_hw4_box_light_matches_port_on_same_stream(renderer):
+    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16)
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1)
+    ok, frac = _mean_close(acc, port["accum"], 16, 0.99)
+    assert ok, frac
+
+
 @pytest.mark.parametrize("path,frac", [("hw8/sphere_emissive.gltf", 0.99), ("hw7/practice7_1.gltf", 0.85),
                                        ("hw7/practice7_4.gltf", 0.90)])
 def test_gltf_matches_port_on_same_stream(renderer, path, frac):
@@ -150,6 +189,10 @@ def _linear(img8):
     ("hw4_p3_1", "hw4_p3_1_spp4096.txt", "text"),
     ("hw4_p3_3", "hw4_p3_3_spp4096.txt", "text"),
     ("hw4_p3_4", "hw4_p3_4_spp4096.txt", "text"),
+    ("hw3_p3_1", "hw4_p3_1_spp4096.txt", "text3"),
+    ("hw3_p3_3", "hw4_p3_3_spp4096.txt", "text3"),
+    ("hw3_p3_4", "hw4_p3_4_spp4096.txt", "text3"),
+    ("hw5_mixed", "hw5_mixed_spp4096.txt", "text"),
 ])
 def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind):
     spp = 64
@@ -157,6 +200,8 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
         sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp)
     elif kind == "gltf6":
         sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
+    elif kind == "text3":
+        sc = rt.load_scene(os.path.join(G, path), samples=spp, mode=rt.MODE_HW3)
     else:
         sc = rt.load_scene(os.path.join(G, path), samples=spp)
     truth = _linear(ou.golden(name + "_spp4096"))

@@ -50,6 +50,12 @@ def test_text_parser_modes_and_quirks(tmp_path, capfd):
     assert rt.load_scene(os.path.join(S, "hw2/sample.txt")).mode == rt.MODE_HW2
     sc4 = rt.load_scene(os.path.join(S, "hw4/practice3_3.txt"))
     assert (sc4.mode, sc4.samples, sc4.ray_depth, sc4.width) == (rt.MODE_HW4, 64, 6, 512)
+    # TRIANGLE figures make it hw5: non-planes first in BVH order, planes last, FiguresMix light list
+    sc5 = rt.load_scene(os.path.join(S, "hw5/mixed.txt"))
+    d5 = sc5.desc
+    assert (sc5.mode, d5.n_prims, d5.n_bvh_prims, d5.n_light_prims) == (rt.MODE_HW5, 36, 31, 4)
+    assert d5.n_nodes >= 2 * 31 - 1 - 31 and d5.n_light_nodes >= 1
+    assert rt.load_scene(os.path.join(S, "hw4/practice3_3.txt"), mode=rt.MODE_HW3).mode == rt.MODE_HW3
     # malformed ROTATION (comma) leaves the remaining fields at their defaults
     p = tmp_path / "q.txt"
     p.write_text("DIMENSIONS 4 4\nCAMERA_FOV_X 1\nNEW_PRIMITIVE\nBOX 1 1 1\nROTATION 0, 0.38 0 0.92\nCOLOR 1 0 0\nBOGUS 1\n")

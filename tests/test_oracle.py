@@ -41,6 +41,39 @@ def test_port_hw4_bytes_equal_reference(k):
     assert np.array_equal(o["rgb"], ou.golden(f"hw4_p3_{k}_spp4"))
 
 
+@pytest.mark.parametrize("k", [1, 3, 4])
+def test_port_hw3_bytes_equal_reference(k):
+    """hw3 ships hw4's scenes (only SAMPLES differs); the golden is the hw3 binary on the shrunk hw4 input."""
+    sc = rt.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"), mode=rt.MODE_HW3)
+    assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW3, 160, 120, 4, 6)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden(f"hw3_p3_{k}_spp4"))
+    assert not np.array_equal(o["rgb"], ou.golden(f"hw4_p3_{k}_spp4"))
+
+
+def test_port_hw5_bytes_equal_reference():
+    """hw5 = text scene with TRIANGLE figures: planes scanned, ellipsoids / boxes / triangles in one BVH keyed by
+    Figure::position, FiguresMix over emissive boxes, ellipsoids and triangles.  The reference ships no hw5 scene;
+    tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py) holds every figure kind, material and light kind, a
+    rotated box light and a triangle with its own POSITION / ROTATION.  Byte equality with the hw5 binary pins the
+    host's figure BVH (order of the lights) and the port's BoxLight draw order."""
+    sc = rt.load_scene(os.path.join(S, "hw5/mixed.txt"))
+    d = sc.desc
+    assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW5, 160, 120, 4, 6)
+    assert (d.n_prims, d.n_bvh_prims, d.n_light_prims) == (36, 31, 4)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden("hw5_mixed_spp4"))
+
+
+@pytest.mark.parametrize("hw,mode", [("hw4", 4), ("hw3", 3)])
+def test_port_box_light_bytes_equal_reference(hw, mode):
+    """None of the reference's hw3 / hw4 scenes has a BOX light; this subset of the hw5 fixture has a rotated one
+    (non-unit quaternion).  Pins BoxLight::sample's argument evaluation order (right to left under g++)."""
+    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), mode=mode)
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden(f"{hw}_boxlight_spp4"))
+
+
 @pytest.mark.parametrize("name,path", [("hw7_practice7_1", "hw7/practice7_1.gltf"),
                                        ("hw7_practice7_4", "hw7/practice7_4.gltf"),
                                        ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf")])

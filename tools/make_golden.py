@@ -7,6 +7,9 @@ Fixtures:
   hw1_sample.ppm.gz, hw2_sample.ppm.gz            deterministic configs, full size
   hw4_p3_{k}.txt + hw4_p3_{k}_spp4.ppm.gz         hw4 scenes shrunk to 160x120, SAMPLES 4 (minstd stream)
   hw4_p3_{k}_spp4096.ppm.gz                       ground truth for the RMSE tests (160x120, SAMPLES 4096)
+  hw4_boxlight_spp4 / hw3_boxlight_spp4           planes + rotated BOX light + analytic bodies (subset of the hw5 fixture)
+  hw5_mixed_spp{4,4096}.ppm.gz                    the hw5 binary on tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py)
+  hw3_p3_{k}_spp{4,4096}.ppm.gz                   the hw3 binary on the same shrunk inputs (hw3 ships the same scenes)
   hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
   hw8_sphere_emissive_128x96_spp4.ppm.gz / _spp4096
   hw6_{name}_128x96_spp4.ppm.gz / _spp4096        hw6 binary on practice7_1 (mirrors + diffuse) and on
@@ -44,6 +47,15 @@ def main():
             txt = os.path.join(GOLD, f"hw4_p3_{k}_spp{spp}.txt")
             open(txt, "w").write(re.sub(r"SAMPLES \d+", f"SAMPLES {spp}", src))
         run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4.txt"), "@OUT"], f"hw4_p3_{k}_spp4")
+        # hw3 ships the same scenes (only SAMPLES differs): the shrunk hw4 inputs feed the hw3 binary too
+        run("hw3", [os.path.join(GOLD, f"hw4_p3_{k}_spp4.txt"), "@OUT"], f"hw3_p3_{k}_spp4")
+    # box-light subset of the hw5 fixture under hw4 and hw3 rules; the hw5 fixture itself (tools/make_hw5_fixture.py)
+    run("hw4", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw4_boxlight_spp4")
+    run("hw3", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw3_boxlight_spp4")
+    hw5 = open(os.path.join(SC, "hw5/mixed.txt")).read()
+    open(os.path.join(GOLD, "hw5_mixed_spp4096.txt"), "w").write(re.sub(r"SAMPLES \d+", "SAMPLES 4096", hw5))
+    run("hw5", [os.path.join(SC, "hw5/mixed.txt"), "@OUT"], "hw5_mixed_spp4")
+    run("hw5", [os.path.join(GOLD, "hw5_mixed_spp4096.txt"), "@OUT"], "hw5_mixed_spp4096")
     for name, path, binary in (("hw7_practice7_1", "hw7/practice7_1.gltf", "hw7"),
                                ("hw7_practice7_4", "hw7/practice7_4.gltf", "hw7"),
                                ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf", "hw8"),
@@ -53,6 +65,7 @@ def main():
             run(binary, [os.path.join(SC, path), "128", "96", str(spp), "@OUT"], f"{name}_128x96_spp{spp}")
     for k in (1, 3, 4):  # slow (single-threaded reference): last
         run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw4_p3_{k}_spp4096")
+        run("hw3", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw3_p3_{k}_spp4096")
 
 
 if __name__ == "__main__":
