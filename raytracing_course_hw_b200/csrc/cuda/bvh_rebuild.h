@@ -21,6 +21,7 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <xmmintrin.h>      // host-side SSE for the binning loop (x86-64 hosts only, like the rest of the build)
 #include "b200rt.h"
 
 namespace b200rt {
@@ -43,6 +44,10 @@ inline unsigned host_threads() {
 namespace bvh_detail {
 
 constexpr int BINS = 16;
+// Nodes of up to Ctx::sweep_max triangles skip the bins: three 16-bin tables cost ~3000 operations per node whatever its
+// size, and most nodes of a tree are tiny (the rebuild spent 70 % of its time there).  They get the exact object-split
+// SAH instead -- sort by centroid on each axis, sweep prefix / suffix areas -- which is cheaper AND never worse.
+constexpr int SWEEP_MAX = 64;     // capacity; the threshold in use is Ctx::sweep_max (12: profiles/r01_sweep_bvh_sweep.log)
 
 struct B3 {
     float mn[3], mx[3];
@@ -55,14 +60,37 @@ struct B3 {
     }
 };
 
+// Bin tables of one node.  Minima / maxima are kept as 4-float vectors (lane 3 unused) so that binning one triangle
+// on one axis is four SSE min / max on memory instead of eighteen scalar ones: the binning passes are the bulk of
+// the build once the small nodes take the sweep path.
 struct Bins {
-    B3 box[3][BINS];       // triangle bounds per bin
-    B3 cbox[3][BINS];      // centroid bounds per bin (become the children's binning ranges)
+    // plain float storage (nvcc rejects vector types inside std::vector's element type); accessed with SSE loads
+    alignas(16) float mn[3][BINS][4], mx[3][BINS][4];       // triangle bounds per bin
+    alignas(16) float cmn[3][BINS][4], cmx[3][BINS][4];     // centroid bounds per bin (become the children's binning ranges)
     uint32_t cnt[3][BINS];
-    void reset() { for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) { box[a][b].reset(); cbox[a][b].reset(); cnt[a][b] = 0; } }
-    void merge(const Bins &o) {
-        for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) { box[a][b].grow(o.box[a][b]); cbox[a][b].grow(o.cbox[a][b]); cnt[a][b] += o.cnt[a][b]; }
+    void reset() {
+        const __m128 hi = _mm_set1_ps(FLT_MAX), lo = _mm_set1_ps(-FLT_MAX);
+        for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) {
+            _mm_store_ps(mn[a][b], hi); _mm_store_ps(cmn[a][b], hi); _mm_store_ps(mx[a][b], lo); _mm_store_ps(cmx[a][b], lo);
+            cnt[a][b] = 0;
+        }
     }
+    static void vmin(float *dst, __m128 v) { _mm_store_ps(dst, _mm_min_ps(_mm_load_ps(dst), v)); }
+    static void vmax(float *dst, __m128 v) { _mm_store_ps(dst, _mm_max_ps(_mm_load_ps(dst), v)); }
+    void merge(const Bins &o) {
+        for (int a = 0; a < 3; a++) for (int b = 0; b < BINS; b++) {
+            vmin(mn[a][b], _mm_load_ps(o.mn[a][b])); vmax(mx[a][b], _mm_load_ps(o.mx[a][b]));
+            vmin(cmn[a][b], _mm_load_ps(o.cmn[a][b])); vmax(cmx[a][b], _mm_load_ps(o.cmx[a][b]));
+            cnt[a][b] += o.cnt[a][b];
+        }
+    }
+    static B3 unpack(const float *l, const float *h) {
+        B3 r;
+        for (int k = 0; k < 3; k++) { r.mn[k] = l[k]; r.mx[k] = h[k]; }
+        return r;
+    }
+    B3 box(int a, int b) const { return unpack(mn[a][b], mx[a][b]); }
+    B3 cbox(int a, int b) const { return unpack(cmn[a][b], cmx[a][b]); }
 };
 
 // Bounds a node is created with: its triangles' box and its centroids' box (both known from the parent's bins).
@@ -73,6 +101,7 @@ struct Ctx {
     const float *cen;      // 3 per triangle
     uint32_t *order;
     int leaf_max;
+    int sweep_max;         // <= SWEEP_MAX
     float trav;
     unsigned threads;
 };
@@ -89,14 +118,21 @@ inline void bounds(const Ctx &c, uint32_t first, uint32_t last, B3 &nb, B3 &cb) 
     }
 }
 
+// The 4-float loads below read one float past a triangle's 3-float record: box[] and cen[] are allocated with a
+// float of slack after the last element (rebuild_bvh_binned_sah).
 inline void bin_range(const Ctx &c, uint32_t first, uint32_t last, const B3 &cb, const float *k, Bins &bins) {
     for (uint32_t i = first; i < last; i++) {
         const uint32_t t = c.order[i];
+        const __m128 lo = _mm_loadu_ps(c.box[t].mn), hi = _mm_loadu_ps(c.box[t].mx);
+        const float *cp = c.cen + (size_t)t * 3;
+        const __m128 cv = _mm_loadu_ps(cp);
         for (int a = 0; a < 3; a++) {
             if (!(k[a] > 0.f)) continue;
-            const int b = bin_of(c.cen[(size_t)t * 3 + a], cb.mn[a], k[a]);
-            bins.box[a][b].grow(c.box[t]);
-            bins.cbox[a][b].grow_point(c.cen + (size_t)t * 3);
+            const int b = bin_of(cp[a], cb.mn[a], k[a]);
+            Bins::vmin(bins.mn[a][b], lo);
+            Bins::vmax(bins.mx[a][b], hi);
+            Bins::vmin(bins.cmn[a][b], cv);
+            Bins::vmax(bins.cmx[a][b], cv);
             bins.cnt[a][b]++;
         }
     }
@@ -124,6 +160,44 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
         return m;
     };
     if (!any_axis) return count <= 15 ? 0 : halves(first + count / 2);      // identical centroids
+    if (count <= (uint32_t)c.sweep_max) {
+        uint32_t idx[3][SWEEP_MAX];
+        float best_cost = FLT_MAX;
+        int best_axis = -1;
+        uint32_t best_i = 0;
+        float left_area[SWEEP_MAX];
+        for (int a = 0; a < 3; a++) {
+            uint32_t *id = idx[a];
+            if (count <= 12) {
+                for (uint32_t i = 0; i < count; i++) {          // insertion sort by centroid
+                    const uint32_t t = c.order[first + i];
+                    const float key = c.cen[(size_t)t * 3 + a];
+                    uint32_t j = i;
+                    while (j > 0 && c.cen[(size_t)id[j - 1] * 3 + a] > key) { id[j] = id[j - 1]; j--; }
+                    id[j] = t;
+                }
+            } else {
+                for (uint32_t i = 0; i < count; i++) id[i] = c.order[first + i];
+                // ties broken by triangle index: the result does not depend on the sort algorithm
+                std::sort(id, id + count, [&](uint32_t x, uint32_t y) {
+                    const float kx = c.cen[(size_t)x * 3 + a], ky = c.cen[(size_t)y * 3 + a];
+                    return kx < ky || (kx == ky && x < y);
+                });
+            }
+            B3 acc;
+            acc.reset();
+            for (uint32_t i = 0; i + 1 < count; i++) { acc.grow(c.box[id[i]]); left_area[i + 1] = acc.area(); }
+            acc.reset();
+            for (uint32_t i = count - 1; i >= 1; i--) {
+                acc.grow(c.box[id[i]]);
+                const float cost = left_area[i] * (float)i + acc.area() * (float)(count - i);
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_i = i; }
+            }
+        }
+        if (count <= (uint32_t)c.leaf_max && best_cost + c.trav * nb.area() >= nb.area() * (float)count) return 0;
+        for (uint32_t i = 0; i < count; i++) c.order[first + i] = idx[best_axis][i];
+        return halves(first + best_i);
+    }
     Bins bins;
     bins.reset();
     if (nt > 1) {
@@ -149,10 +223,11 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
         B3 acc;
         acc.reset();
         uint32_t n = 0;
-        for (int b = BINS - 1; b > 0; b--) { acc.grow(bins.box[a][b]); n += bins.cnt[a][b]; right_area[b] = acc.area(); right_cnt[b] = n; }
+        for (int b = BINS - 1; b > 0; b--) { if (bins.cnt[a][b]) acc.grow(bins.box(a, b)); n += bins.cnt[a][b]; right_area[b] = acc.area(); right_cnt[b] = n; }
         acc.reset(); n = 0;
         for (int b = 0; b < BINS - 1; b++) {
-            acc.grow(bins.box[a][b]); n += bins.cnt[a][b];
+            if (bins.cnt[a][b]) acc.grow(bins.box(a, b));
+            n += bins.cnt[a][b];
             if (n == 0 || right_cnt[b + 1] == 0) continue;
             const float cost = acc.area() * (float)n + right_area[b + 1] * (float)right_cnt[b + 1];
             if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
@@ -169,8 +244,9 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
     for (int h = 0; h < 2; h++) { kids[h].nb.reset(); kids[h].cb.reset(); }
     for (int b = 0; b < BINS; b++) {
         NodeBounds &k2 = kids[b <= best_bin ? 0 : 1];
-        k2.nb.grow(bins.box[best_axis][b]);
-        k2.cb.grow(bins.cbox[best_axis][b]);
+        if (!bins.cnt[best_axis][b]) continue;
+        k2.nb.grow(bins.box(best_axis, b));
+        k2.cb.grow(bins.cbox(best_axis, b));
     }
     return mid;
 }
@@ -210,13 +286,15 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
     if (n <= 0) return;
     Ctx c{};
     c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
+    c.sweep_max = 12;
+    if (const char *e = getenv("B200RT_REBUILD_SWEEP")) c.sweep_max = std::max(0, std::min(SWEEP_MAX, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_LEAF_LIGHT" : "B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_TRAV_LIGHT" : "B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
     c.threads = host_threads();
     if (n < 65536) c.threads = 1;
     static_assert(sizeof(B3) == 6 * sizeof(float), "B3 is six floats");
-    out.scratch_box.resize((size_t)n * 6);
-    out.scratch_cen.resize((size_t)n * 3);
+    out.scratch_box.resize((size_t)n * 6 + 4);     // + slack for the 4-float loads of bin_range
+    out.scratch_cen.resize((size_t)n * 3 + 4);
     B3 *box = reinterpret_cast<B3 *>(out.scratch_box.data());
     float *cen = out.scratch_cen.data();
     {

@@ -46,7 +46,7 @@ def test_cli_hw5_and_hw3_text_scenes(tmp_path):
     assert r.returncode == 0, r.stderr
     assert '"mode": 5' in r.stderr
     img = ou.inv_display(ou.parse_ppm(out.read_bytes()))
-    truth = ou.inv_display(ou.golden("hw5_mixed_spp4096"))
+    truth = ou.inv_display(ou.golden("hw5_mixed_spp2048"))
     assert abs(img.mean() - truth.mean()) <= 0.02 * truth.mean()
     src = open(os.path.join(ou.GOLDEN, "hw4_p3_1_spp4096.txt")).read().replace("SAMPLES 4096", "SAMPLES 512")
     scene.write_text(src)

@@ -192,7 +192,7 @@ def _linear(img8):
     ("hw3_p3_1", "hw4_p3_1_spp4096.txt", "text3"),
     ("hw3_p3_3", "hw4_p3_3_spp4096.txt", "text3"),
     ("hw3_p3_4", "hw4_p3_4_spp4096.txt", "text3"),
-    ("hw5_mixed", "hw5_mixed_spp4096.txt", "text"),
+    ("hw5_mixed", "hw5_mixed_spp2048.txt", "text"),
 ])
 def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind):
     spp = 64
@@ -204,14 +204,22 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
         sc = rt.load_scene(os.path.join(G, path), samples=spp, mode=rt.MODE_HW3)
     else:
         sc = rt.load_scene(os.path.join(G, path), samples=spp)
-    truth = _linear(ou.golden(name + "_spp4096"))
+    # hw5: 2048 spp is as far as the reference binary gets on the fixture (tools/make_golden.py)
+    truth = _linear(ou.golden(name + ("_spp2048" if name.startswith("hw5") else "_spp4096")))
     renderer.upload(sc)
     renderer.render(0, spp)
     gpu = _linear(renderer.resolve(spp))
     ref_equal_spp = _linear(ou.port_render(sc, 0)["rgb"])     # == the reference binary's image (test_oracle)
     rmse_gpu = np.sqrt(((gpu - truth) ** 2).mean())
     rmse_ref = np.sqrt(((ref_equal_spp - truth) ** 2).mean())
-    assert rmse_gpu <= 1.05 * rmse_ref + 1e-4, (rmse_gpu, rmse_ref)
+    # The reference's equal-spp image is not independent of the ground truth: same per-pixel seed, so its `spp`
+    # samples are the first `spp` of the truth's S samples.  Its error against the truth is therefore smaller by
+    # sqrt(1 - spp/S) than against the true mean, while an independent estimator's is larger by sqrt(1 + spp/S)
+    # (the truth's own noise).  The bar "no worse than the reference at equal spp" is applied after that
+    # correction, with 5 % for the run-to-run spread of the RMSE itself.
+    S = 2048 if name.startswith("hw5") else 4096
+    shared = np.sqrt((1 + spp / S) / (1 - spp / S))
+    assert rmse_gpu <= 1.05 * shared * rmse_ref + 1e-4, (rmse_gpu, rmse_ref, shared)
     # mean luminance within 1 % of the 4096-spp reference (use 1024 spp to push MC noise well below 1 %)
     renderer.clear()
     renderer.render(0, 1024)

@@ -8,7 +8,7 @@ Fixtures:
   hw4_p3_{k}.txt + hw4_p3_{k}_spp4.ppm.gz         hw4 scenes shrunk to 160x120, SAMPLES 4 (minstd stream)
   hw4_p3_{k}_spp4096.ppm.gz                       ground truth for the RMSE tests (160x120, SAMPLES 4096)
   hw4_boxlight_spp4 / hw3_boxlight_spp4           planes + rotated BOX light + analytic bodies (subset of the hw5 fixture)
-  hw5_mixed_spp{4,4096}.ppm.gz                    the hw5 binary on tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py)
+  hw5_mixed_spp{4,2048}.ppm.gz                    the hw5 binary on tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py)
   hw3_p3_{k}_spp{4,4096}.ppm.gz                   the hw3 binary on the same shrunk inputs (hw3 ships the same scenes)
   hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
   hw8_sphere_emissive_128x96_spp4.ppm.gz / _spp4096
@@ -53,9 +53,12 @@ def main():
     run("hw4", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw4_boxlight_spp4")
     run("hw3", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw3_boxlight_spp4")
     hw5 = open(os.path.join(SC, "hw5/mixed.txt")).read()
-    open(os.path.join(GOLD, "hw5_mixed_spp4096.txt"), "w").write(re.sub(r"SAMPLES \d+", "SAMPLES 4096", hw5))
+    # 2048, not 4096: between 2048 and 3072 samples some pixel's generator reaches a state from which the reference's
+    # unbounded rejection loop (BoxLight / EllipsoidLight::sample, hw5/src/include/distributions.h:88-104) never
+    # returns -- the hw5 binary then spins forever on this scene (observed; the port caps the loop for the counter RNG)
+    open(os.path.join(GOLD, "hw5_mixed_spp2048.txt"), "w").write(re.sub(r"SAMPLES \d+", "SAMPLES 2048", hw5))
     run("hw5", [os.path.join(SC, "hw5/mixed.txt"), "@OUT"], "hw5_mixed_spp4")
-    run("hw5", [os.path.join(GOLD, "hw5_mixed_spp4096.txt"), "@OUT"], "hw5_mixed_spp4096")
+    run("hw5", [os.path.join(GOLD, "hw5_mixed_spp2048.txt"), "@OUT"], "hw5_mixed_spp2048")
     for name, path, binary in (("hw7_practice7_1", "hw7/practice7_1.gltf", "hw7"),
                                ("hw7_practice7_4", "hw7/practice7_4.gltf", "hw7"),
                                ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf", "hw8"),
