@@ -149,6 +149,29 @@ __device__ __forceinline__ void pair_test(const DPair *nodes, uint32_t idx, cons
     ml = b.z; mr = b.w;
 }
 
+// Moeller-Trumbore on a 48-byte record with the division deferred to the accepted hits: the barycentric and
+// distance tests run on the numerators against |det| (signs folded in with one XOR each), so a rejected triangle
+// -- three out of four at the leaves -- costs no reciprocal.  Accepts 0 <= u, 0 <= v, u + v <= 1, 0 < t < tmax
+// (intersectPlaneAndRay + the inside test of hw8/src/primitives.cpp:18-27, 85-108, up to rounding at the edges);
+// det = 0 or NaN rejects.  `det` keeps its sign: det > 0 means the ray runs along the reference's normal ("inside").
+__device__ __forceinline__ bool tri_hit(const float4 v0, const float4 e1, const float4 e2, const V3 o, const V3 d, const float tmax,
+                                        float &t, float &u, float &v, float &det) {
+    const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+    const V3 pv = cross(d, E2);
+    det = dot(E1, pv);
+    const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
+    const V3 qv = cross(tv, E1);
+    const uint32_t sb = __float_as_uint(det) & 0x80000000u;
+    const float ad = fabsf(det);
+    const float un = __uint_as_float(__float_as_uint(dot(tv, pv)) ^ sb);
+    const float vn = __uint_as_float(__float_as_uint(dot(d, qv)) ^ sb);
+    const float tn = __uint_as_float(__float_as_uint(dot(E2, qv)) ^ sb);
+    if (!(un >= 0.f && vn >= 0.f && un + vn <= ad && tn > 0.f && tn < tmax * ad)) return false;
+    const float idet = 1.f / ad;
+    t = tn * idet; u = un * idet; v = vn * idet;
+    return true;
+}
+
 // Closest hit over the scene BVH.  t in (0, 1e4) like intersectPlaneAndRay (primitives.cpp:20).
 template <bool COUNT>
 __device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, const V3 d, TraceHit &h, ThreadCounters &tc) {
@@ -178,16 +201,8 @@ __device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, 
                 const float4 *q = reinterpret_cast<const float4 *>(sc.tris + i);
                 const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                 if (COUNT) tc.tri_tests++;
-                const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-                const V3 pv = cross(d, E2);
-                const float det = dot(E1, pv);
-                const float idet = 1.f / det;
-                const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
-                const float u = dot(tv, pv) * idet;
-                const V3 qv = cross(tv, E1);
-                const float v = dot(d, qv) * idet;
-                const float t = dot(E2, qv) * idet;
-                if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < h.t) { h.t = t; h.u = u; h.v = v; h.tri = (int)i; h.det = det; }
+                float t, u, v, det;
+                if (tri_hit(v0, e1, e2, o, d, h.t, t, u, v, det)) { h.t = t; h.u = u; h.v = v; h.tri = (int)i; h.det = det; }
             }
         }
         if (sp == 0) break;
@@ -227,16 +242,9 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
                 const float4 *q = reinterpret_cast<const float4 *>(sc.light_tris + i);
                 const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                 if (COUNT) tc.light_tri_tests++;
-                const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-                const V3 pv = cross(d, E2);
-                const float det = dot(E1, pv);
-                const float idet = 1.f / det;
-                const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
-                const float u = dot(tv, pv) * idet;
-                const V3 qv = cross(tv, E1);
-                const float v = dot(d, qv) * idet;
-                const float t = dot(E2, qv) * idet;
-                if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f && t < B200RT_TMAX) {
+                float t, u, v, det;
+                if (tri_hit(v0, e1, e2, o, d, B200RT_TMAX, t, u, v, det)) {
+                    const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
                     V3 yn;
                     if (sc.hw8) {   // interpolated shading normal of the emitter (hw8 distributions.h:140-145)
                         const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);

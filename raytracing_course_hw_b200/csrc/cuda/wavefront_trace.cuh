@@ -70,19 +70,13 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_trace(const DGltfScen
                         const float4 *q = reinterpret_cast<const float4 *>(tris + i);
                         const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                         if (COUNT) { if (light) ltri_tests++; else tri_tests++; }
-                        const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-                        const V3 pv = cross(d, E2);
-                        const float det = dot(E1, pv);
-                        const float idet = 1.f / det;
-                        const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
-                        const float u = dot(tv, pv) * idet;
-                        const V3 qv = cross(tv, E1);
-                        const float v = dot(d, qv) * idet;
-                        const float t = dot(E2, qv) * idet;
-                        if (u >= 0.f && v >= 0.f && u + v <= 1.f && t > 0.f) {
+                        float t, u, v, det;
+                        if (tri_hit(v0, e1, e2, o, d, light ? B200RT_TMAX : tbest, t, u, v, det)) {
+                            const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
+
                             if (!light) {
-                                if (t < tbest) { tbest = t; hu = u; hv = v; htri = i; hdet = det; }
-                            } else if (t < B200RT_TMAX) {
+                                tbest = t; hu = u; hv = v; htri = i; hdet = det;
+                            } else {
                                 V3 yn;
                                 if (sc.hw8) {   // interpolated shading normal of the emitter (hw8 distributions.h:140-145)
                                     const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);

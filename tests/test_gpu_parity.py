@@ -217,8 +217,8 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
     # sqrt(1 - spp/S) than against the true mean, while an independent estimator's is larger by sqrt(1 + spp/S)
     # (the truth's own noise).  The bar "no worse than the reference at equal spp" is applied after that
     # correction, with 5 % for the run-to-run spread of the RMSE itself.
-    S = 2048 if name.startswith("hw5") else 4096
-    shared = np.sqrt((1 + spp / S) / (1 - spp / S))
+    truth_spp = 2048 if name.startswith("hw5") else 4096
+    shared = np.sqrt((1 + spp / truth_spp) / (1 - spp / truth_spp))
     assert rmse_gpu <= 1.05 * shared * rmse_ref + 1e-4, (rmse_gpu, rmse_ref, shared)
     # mean luminance within 1 % of the 4096-spp reference (use 1024 spp to push MC noise well below 1 %)
     renderer.clear()
