@@ -779,7 +779,8 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
+                if (last) wf_shade<HW8, COUNT, true><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
+                else wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }

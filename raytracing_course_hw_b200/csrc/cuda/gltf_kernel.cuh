@@ -521,6 +521,31 @@ __device__ __forceinline__ bool shade_surface(const DGltfScene &sc, const float 
     return true;
 }
 
+// The emission term of shade_surface alone (same arithmetic, same bits).  The last bounce of a path needs nothing
+// else: Scene::getColor(ray, 1) returns emission + weight * getColor(next, 0) and getColor(.., 0) is black
+// (hw8/src/scene.cpp:85-87), so the sampled direction, the BRDF and three of the four texture lookups are dead work.
+template <bool HW8, bool COUNT>
+__device__ __forceinline__ V3 surface_emission(const DGltfScene &sc, const float *lut_srgb, int tri, float u, float v, ThreadCounters &tc) {
+    if (COUNT) tc.shaded++;
+    const float mat = __ldg(&sc.tris[tri].v0.w);
+    const DMaterial *m = sc.materials + __float_as_int(mat);
+    V3 emission = mk(__ldg(&m->emission[0]), __ldg(&m->emission[1]), __ldg(&m->emission[2]));
+    if (HW8) {
+        const DTexels te = m->tex_emissive;
+        if (te) {
+            const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
+            const float s0w = __ldg(&sq[0].w), s1w = __ldg(&sq[1].w), s2w = __ldg(&sq[2].w), s3w = __ldg(&sq[3].w), s4w = __ldg(&sq[4].w), s5w = __ldg(&sq[5].w);
+            const float tx = s4w + u * (s0w - s4w) + v * (s2w - s4w);
+            const float ty = s5w + u * (s1w - s5w) + v * (s3w - s5w);
+            TexTaps ke;
+            tex_fetch(te, m->w_emissive, m->h_emissive, tx, ty, ke);
+            emission = emission * tex_resolve(ke, lut_srgb);
+            if (COUNT) tc.tex++;
+        }
+    }
+    return emission;
+}
+
 // Second part: mean of the component pdfs, path weight, firefly clamp (scene.cpp:158-163).
 // light_sum = FiguresMix::getTotalPdf for the ray (xo, nd); ignored when there are no emitters.
 __device__ __forceinline__ bool finish_bounce(const V3 brdf, float pdf_partial, float absdot, float light_sum,
@@ -627,6 +652,10 @@ __global__ void __launch_bounds__(128) gltf_path_kernel(const DGltfScene sc, con
                             bg = sample_texture(sc.env, sc.env_w, sc.env_h, tx, ty, lut_srgb);
                         }
                         L = L + T * bg;
+                        break;
+                    }
+                    if (bounce == rp.ray_depth - 1) {      // final bounce: emission only (see surface_emission)
+                        L = L + T * surface_emission<HW8, COUNT>(sc, lut_srgb, hit.tri, hit.u, hit.v, tc);
                         break;
                     }
                     const uint4 rnd = philox4x32_10((uint32_t)s, 16u * (uint32_t)(bounce + 1), pixel, rp.seed);

@@ -377,7 +377,8 @@ __device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <bool HW8, bool COUNT>
+// LAST = the path's final bounce: only the emission of the hit is added (surface_emission), nothing continues.
+template <bool HW8, bool COUNT, bool LAST = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
                                                 const float *__restrict__ lut_srgb_g, DCounters *counters) {
@@ -511,6 +512,8 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                     bg = sample_texture(sc.env, sc.env_w, sc.env_h, tx, ty, lut_srgb);
                 }
                 L = L + T * bg;
+            } else if (LAST) {
+                L = L + T * surface_emission<HW8, COUNT>(sc, lut_srgb, (int)(bits & 0x7FFFFFFFu), h.y, h.z, tc);
             } else {
                 // key = pixel, counter = (global sample index, block of this bounce); both ride in spare state lanes
                 const uint4 rnd = philox4x32_10(__float_as_uint(ra.w), 16u * (uint32_t)(bounce + 1), __float_as_uint(ro.w), wp.seed);
