@@ -97,6 +97,7 @@ struct b200rt_ctx {
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
     int light_top_max = B200RT_LIGHT_TOP;  // boxes of the light-BVH cut used as the light-pdf pre-filter (0/1 = root box only)
+    bool wf_drop_dark = true;    // paths whose last bounce cannot reach an emitter end one bounce early (black background only)
     bool wf_direct = true;       // shade finishes bounces whose ray misses the light root box (no light-stage entry)
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
     int wf_batch = B200RT_WF_BATCH, wf_leaf_t = B200RT_WF_LEAF_T, wf_leaf_t_light = B200RT_WF_LEAF_T_LIGHT, wf_blocks_cap = 0;
@@ -768,12 +769,15 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
             ctx->stamp(false, 0, st);
             const bool last = b == rp.ray_depth - 1;
+            // the bounce after this one is the last and a miss adds nothing: rays that cannot reach an emitter are dropped
+            const int drop = (ctx->wf_drop_dark && b == rp.ray_depth - 2 && !ctx->gs.env &&
+                              ctx->gs.bg[0] == 0.f && ctx->gs.bg[1] == 0.f && ctx->gs.bg[2] == 0.f) ? 1 : 0;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct, drop);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
@@ -935,6 +939,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_DIRECT")) ctx->wf_direct = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_DROP_DARK")) ctx->wf_drop_dark = atoi(e) != 0;
     if (const char *e = getenv("B200RT_LIGHT_TOP")) ctx->light_top_max = std::max(0, atoi(e));
     if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
     if (ctx->flags & B200RT_FLAG_SERIAL_WAVES) ctx->wf_pipe = 1;

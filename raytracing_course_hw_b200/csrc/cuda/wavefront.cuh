@@ -381,7 +381,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 template <bool HW8, bool COUNT, bool LAST = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
-                                                const float *__restrict__ lut_srgb_g, DCounters *counters) {
+                                                const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
 #if B200RT_SHADE_PIPE
@@ -534,6 +534,10 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                         direct = true;
                         cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T);
                         bo.pdf_partial = 0.f;
+                        // drop_dark (set when the NEXT bounce is the last one and the background is black): that
+                        // bounce only adds the emission of what it hits, and a ray that misses the emitters' boxes
+                        // cannot hit an emitter -- the path would add exactly zero, so it ends here
+                        if (drop_dark) cont = false;
                     }
                 }
                 if (cont) {
@@ -571,7 +575,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
 template <bool COUNT>
 __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters,
-                                                const int batch, const int leaf_t, const bool filtered) {
+                                                const int batch, const int leaf_t, const bool filtered, const int drop_dark = 0) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
     TravStack stack;
@@ -679,7 +683,9 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     // end of the bounce: mean pdf, weight, firefly clamp (scene.cpp:158-163)
                     const float4 th = ld_state(&wb.thr[p]), bs = ld_state(&wb.bsdf[p]);
                     V3 T = mk(th.x, th.y, th.z);
-                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T)) {
+                    // drop_dark: see wf_shade.  total == 0 means the ray pierces no emissive triangle within T_MAX (every
+                    // hit adds a positive term), so the last bounce would add nothing: the path ends here
+                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T) && !(drop_dark && total == 0.f)) {
                         st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, 0.f));
                         push_pending = true;
                         push_p = p;

@@ -133,11 +133,34 @@ def test_gltf_matches_port_on_same_stream(renderer, path, frac):
     assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
     st = renderer.stats()
     # same paths => (almost) the same number of closest-hit queries and light-pdf queries
-    assert abs(int(st["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    rays, rays_port = int(st["rays"]), int(port["counters"][0])
+    if renderer.megakernel:
+        assert abs(rays - rays_port) <= 2e-3 * rays_port
+    else:   # the wavefront does not trace last-bounce rays that cannot reach an emitter (test_dark_rays_are_dropped...)
+        assert 0.6 * rays_port <= rays <= 1.002 * rays_port
     lq, lq_port = int(st["light_queries"]), int(port["counters"][3])
     # every scheduling stops the last bounce at the emission term: its (unused) light-pdf query is not made
     assert 0.7 * lq_port <= lq <= lq_port
     assert st["paths"] == 128 * 96 * 16
+
+
+@pytest.mark.parametrize("path", ["hw8/sphere_emissive.gltf", "hw7/practice7_4.gltf"])
+def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
+    """With a black background the last bounce only adds the emission of what it hits, so the wavefront ends a path one
+    bounce early when its last ray pierces no emissive triangle (light stage: pdf sum == 0; shade: misses the emitters'
+    boxes).  Those paths would have added exactly zero: the image is bit-identical with the rule off, the ray count
+    with the rule off equals the port's, and fewer rays are traced with it on."""
+    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
+    port = ou.port_render(sc, 1, want_counters=True)
+    out = {}
+    for drop in ("1", "0"):
+        monkeypatch.setenv("B200RT_WF_DROP_DARK", drop)
+        r = rt.Renderer()
+        out[drop] = (_render(r, sc), int(r.stats()["rays"]))
+        r.close()
+    assert np.array_equal(out["1"][0], out["0"][0])
+    assert abs(out["0"][1] - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    assert out["1"][1] < out["0"][1]
 
 
 def test_reference_tree_and_rebuilt_tree_agree():
