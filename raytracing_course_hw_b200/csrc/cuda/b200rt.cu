@@ -733,7 +733,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         wp.s_begin = s0;
         wp.s_count = std::min<int>((int)s_w, rp.spp_end - s0);
         CK(cudaMemsetAsync(wb.ctr - 4, 0, 4 * (B200RT_MAX_DEPTH + 2) * sizeof(int), st));
-        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters);
+        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters, W % 8 == 0 && H % 4 == 0);
         (*launches)++;
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {

@@ -172,7 +172,7 @@ struct TravStack {
 #endif
 };
 
-__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters) {
+__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters, const bool dense) {
     const int n_slots = wp.n_tiles * 32 * wp.s_count;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -195,8 +195,12 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             st_state(&wb.rad[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl))));
             made++;
         }
-        queue_push(wb.queue[0], wb.ctr - 1, ok, slot);
+        // Frames whose width / height are multiples of the 8x4 tile have no dead slots: the first queue is the
+        // identity and its length is known, no atomics needed (260 k same-address atomics per 4K wave otherwise).
+        if (dense) { if (ok) __stcs(wb.queue[0] + slot, slot); }
+        else queue_push(wb.queue[0], wb.ctr - 1, ok, slot);
     }
+    if (dense && blockIdx.x == 0 && threadIdx.x == 0) wb.ctr[-1] = n_slots;
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) made += __shfl_down_sync(B200RT_FULL, made, off);
     if (lane == 0 && made) atomicAdd(&counters->paths, (unsigned long long)made);
