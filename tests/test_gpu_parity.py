@@ -144,6 +144,46 @@ def test_gltf_matches_port_on_same_stream(renderer, path, frac):
     assert st["paths"] == 128 * 96 * 16
 
 
+def test_hw8_environment_map_matches_port_on_same_stream(renderer):
+    """Misses sample the environment map (equirect lookup + sRGB decode on the device); with a non-black background
+    the dark-ray rule must stay off: the ray count equals the port's in every scheduling."""
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=16,
+                       env_map=os.path.join(S, "hw8/sphere_emission.png"))
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1, want_counters=True)
+    ok, got = _mean_close(acc, port["accum"], 16, 0.99, rel=5e-2)
+    assert ok, got
+    assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+    assert abs(int(renderer.stats()["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    spp = 64
+    renderer.clear()
+    renderer.render(0, spp)
+    gpu = _linear(renderer.resolve(spp))
+    truth = _linear(ou.golden("hw8_sphere_emissive_env_128x96_spp4096"))
+    sc.set_frame(samples=spp)
+    ref = _linear(ou.port_render(sc, 0)["rgb"])
+    shared = np.sqrt((1 + spp / 4096) / (1 - spp / 4096))       # see test_rmse_and_luminance_against_4096spp_reference
+    assert np.sqrt(((gpu - truth) ** 2).mean()) <= 1.05 * shared * np.sqrt(((ref - truth) ** 2).mean()) + 1e-4
+
+
+@pytest.mark.parametrize("path,w,h", [("hw8/sphere_emissive.gltf", 101, 67), ("hw7/practice7_4.gltf", 37, 1), ("hw7/practice7_1.gltf", 1, 1)])
+def test_ragged_frames_match_port(renderer, path, w, h):
+    """Frames that are not multiples of the 8x4 pixel tile (partial tiles leave dead slots in a wave; the first queue
+    is then compacted with atomics instead of being the identity), down to a single pixel."""
+    sc = rt.load_scene(os.path.join(S, path), width=w, height=h, samples=16)
+    acc = _render(renderer, sc)
+    assert acc.shape == (h, w, 3)
+    port = ou.port_render(sc, 1)
+    assert np.isfinite(acc).all()
+    assert renderer.stats()["paths"] == w * h * 16
+    if w * h > 64:
+        ok, got = _mean_close(acc, port["accum"], 16, 0.95, rel=5e-2)
+        assert ok, got
+        assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+    else:   # a handful of pixels: one path that rounds to another triangle moves the mean, so only a loose bound
+        assert abs(acc.mean() - port["accum"].mean()) <= 0.25 * port["accum"].mean() + 1e-3
+
+
 @pytest.mark.parametrize("path", ["hw8/sphere_emissive.gltf", "hw7/practice7_4.gltf"])
 def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
     """With a black background the last bounce only adds the emission of what it hits, so the wavefront ends a path one

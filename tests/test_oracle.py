@@ -83,6 +83,16 @@ def test_port_gltf_bytes_equal_reference(name, path):
     assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
 
 
+def test_port_hw8_environment_map_bytes_equal_reference():
+    """hw8's optional argv[6]: misses look the equirectangular image up instead of returning black
+    (hw8/src/scene.cpp:90-97, hw8/src/main.cpp:12-14)."""
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=4,
+                       env_map=os.path.join(S, "hw8/sphere_emission.png"))
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden("hw8_sphere_emissive_env_128x96_spp4"))
+    assert not np.array_equal(o["rgb"], ou.golden("hw8_sphere_emissive_128x96_spp4"))
+
+
 @pytest.mark.parametrize("name,path", [("hw6_practice7_1", "hw7/practice7_1.gltf"),
                                        ("hw6_practice7_1_glass", "hw6/practice7_1_glass.gltf")])
 def test_port_hw6_bytes_equal_reference(name, path):

@@ -8,6 +8,7 @@ Fixtures:
   hw4_p3_{k}.txt + hw4_p3_{k}_spp4.ppm.gz         hw4 scenes shrunk to 160x120, SAMPLES 4 (minstd stream)
   hw4_p3_{k}_spp4096.ppm.gz                       ground truth for the RMSE tests (160x120, SAMPLES 4096)
   hw4_boxlight_spp4 / hw3_boxlight_spp4           planes + rotated BOX light + analytic bodies (subset of the hw5 fixture)
+  hw8_sphere_emissive_env_128x96_spp{4,4096}      hw8 with sphere_emission.png as the environment map
   hw5_mixed_spp{4,2048}.ppm.gz                    the hw5 binary on tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py)
   hw3_p3_{k}_spp{4,4096}.ppm.gz                   the hw3 binary on the same shrunk inputs (hw3 ships the same scenes)
   hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
@@ -66,6 +67,11 @@ def main():
                                ("hw6_practice7_1_glass", "hw6/practice7_1_glass.gltf", "hw6")):
         for spp in (4, 4096):
             run(binary, [os.path.join(SC, path), "128", "96", str(spp), "@OUT"], f"{name}_128x96_spp{spp}")
+    # hw8 with an environment map (argv[6], hw8/src/main.cpp:12-14): the fixture's emission texture doubles as the
+    # equirectangular image -- misses then return texels instead of black
+    env = os.path.join(SC, "hw8/sphere_emission.png")
+    for spp in (4, 4096):
+        run("hw8", [os.path.join(SC, "hw8/sphere_emissive.gltf"), "128", "96", str(spp), "@OUT", env], f"hw8_sphere_emissive_env_128x96_spp{spp}")
     for k in (1, 3, 4):  # slow (single-threaded reference): last
         run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw4_p3_{k}_spp4096")
         run("hw3", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw3_p3_{k}_spp4096")
