@@ -50,7 +50,8 @@ def run_ref(hw, scene, width, height, samples, is_text):
             argv = [exe, scene, str(width), str(height), str(samples), out]
         t = time.perf_counter()
         subprocess.run(["bash", "-c", 'ulimit -s unlimited 2>/dev/null; exec "$0" "$@"'] + argv, check=True, env=env,
-                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=os.path.dirname(os.path.abspath(scene)))
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=os.path.dirname(os.path.abspath(scene)),
+                       timeout=600)      # the reference's rejection loops are unbounded (hw5 hangs on its fixture beyond 2048 spp)
         dt = time.perf_counter() - t
         if not os.path.exists(out) or os.path.getsize(out) < width * height * 3:
             raise RuntimeError(f"reference hw{hw} wrote no image for {scene}")
@@ -126,6 +127,10 @@ def main():
         C.append(("C3", f"hw4/practice3_{k}.txt", 4, os.path.join(SC, f"hw4/practice3_{k}.txt"), True, 0, 0, 0, 0, (160, 120, 4)))
     for k in (1, 3):
         C.append(("C3", f"hw4/practice3_{k}.txt", 4, os.path.join(SC, f"hw4/practice3_{k}.txt"), True, 0, 1920, 1080, 256, (160, 120, 4)))
+    # hw3 ships hw4's scenes (mode picks the integrator); hw5 has no shipped scene: the test fixture, up-res
+    for k in (1, 3):
+        C.append(("C3/hw3", f"hw4/practice3_{k}.txt as hw3", 3, os.path.join(SC, f"hw4/practice3_{k}.txt"), True, 3, 1920, 1080, 256, (160, 120, 4)))
+    C.append(("C3/hw5", "hw5/mixed.txt", 5, os.path.join(SC, "hw5/mixed.txt"), True, 5, 1920, 1080, 256, (160, 120, 4)))
     for n in ("practice6_1.gltf", "practice6_2.gltf"):
         if big(6, n):
             # the reference's hw6 tree is degenerate (all sort keys equal): practice6_2 takes minutes per 64 k paths on the CPU
