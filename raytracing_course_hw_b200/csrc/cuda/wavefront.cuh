@@ -191,8 +191,11 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             const V3 d = normalize(nx * cright - ny * cup + cfwd);
             st_state(&wb.ray_o[slot], make_float4(cpos.x, cpos.y, cpos.z, __uint_as_float(pixel)));
             st_state(&wb.ray_d[slot], make_float4(d.x, d.y, d.z, 0.f));
+            // whole 32-byte sectors ({hit, thr} and {rad, bsdf}): a half-written sector costs L2 a fill from DRAM first
+            st_state(&wb.hit[slot], make_float4(0.f, 0.f, 0.f, 0.f));
             st_state(&wb.thr[slot], make_float4(1.f, 1.f, 1.f, 0.f));
             st_state(&wb.rad[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl))));
+            st_state(&wb.bsdf[slot], make_float4(0.f, 0.f, 0.f, 0.f));
             made++;
         }
         // Frames whose width / height are multiples of the 8x4 tile have no dead slots: the first queue is the
