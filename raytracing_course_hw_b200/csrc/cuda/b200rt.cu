@@ -407,8 +407,9 @@ namespace {
 
 // Cut through the top of the light BVH: start at the root and keep replacing the inner node with the largest
 // surface area by its children until `want` boxes are open (or only leaves remain).
-void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, int want, DGltfScene &g) {
+void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, int want, DGltfScene &g, std::vector<int> &cut_nodes) {
     g.n_light_top = 0;
+    cut_nodes.clear();
     if (n_light_tris <= 0 || n_nodes <= 0 || want < 2) return;
     want = std::min(want, B200RT_LIGHT_TOP);
     auto area = [&](int i) {
@@ -426,6 +427,7 @@ void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, 
         open.push_back((int)nodes[id].right);
     }
     if (open.size() < 2) return;
+    cut_nodes = open;
     for (int id : open) {
         float *b = g.light_top[g.n_light_top++];
         for (int k = 0; k < 3; k++) { b[k] = nodes[id].aabb_min[k]; b[3 + k] = nodes[id].aabb_max[k]; }
@@ -561,7 +563,11 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s, bool trees_absent =
     else memcpy(lpairs, ll.out.data(), ll.out.size() * sizeof(DPair));
     g.light_root = ll.root_word; g.lq = ll.q;
     for (int k = 0; k < 3; k++) { g.light_min[k] = ll.root_box.mn[k]; g.light_max[k] = ll.root_box.mx[k]; }
-    light_top_cut(lnode_src, n_lnodes, s->n_light_tris, ctx->light_top_max, g);
+    std::vector<int> cut_nodes;
+    light_top_cut(lnode_src, n_lnodes, s->n_light_tris, ctx->light_top_max, g, cut_nodes);
+    // the traversal may start at the cut's nodes when the flattener kept the tree's shape (one record per inner node)
+    g.light_top_start = fast_light && !cut_nodes.empty() ? 1 : 0;
+    for (size_t k = 0; k < cut_nodes.size() && g.light_top_start; k++) g.light_top_word[k] = ll.word_of((uint32_t)cut_nodes[k]);
     DTri *ltris = reinterpret_cast<DTri *>(pin + o_ltris);
     DLightNormals *lnorm = reinterpret_cast<DLightNormals *>(pin + o_lnorm);
     DTri *lsample = reinterpret_cast<DTri *>(pin + o_lsample);

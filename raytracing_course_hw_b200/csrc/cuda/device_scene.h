@@ -76,7 +76,7 @@ struct DCamera {
     int32_t width, height;
 };
 
-#define B200RT_LIGHT_TOP 8
+#define B200RT_LIGHT_TOP 6      /* <= 6: the wavefront packs the hit mask into the top bits of a light-queue entry */
 struct DGltfScene {
     const DPair *nodes;
     const DTri *tris;
@@ -94,6 +94,10 @@ struct DGltfScene {
     // misses all of them has a light pdf of 0 -- the cheap pre-filter shade uses to skip the light stage
     float light_top[B200RT_LIGHT_TOP][6];
     int32_t n_light_top;
+    // child words of the cut's nodes: the light-pdf traversal starts at the boxes the pre-filter found pierced
+    // instead of walking down from the root again (light_top_start = 0: words unavailable, start at the root)
+    uint32_t light_top_word[B200RT_LIGHT_TOP];
+    int32_t light_top_start;
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
     float bg[3];
     DTexels env;                 // null = absent

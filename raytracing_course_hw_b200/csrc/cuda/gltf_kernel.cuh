@@ -45,16 +45,30 @@ __device__ __forceinline__ bool slab6(float lx, float ly, float lz, float hx, fl
 // through its top levels (then FiguresMix::getTotalPdf is exactly 0: no pierced leaf box, distributions.h:122-165).
 // Every light-pdf evaluation (megakernel, hw6, wavefront shade / light stages) starts with this same test, so all
 // schedulings see the same set of non-zero queries.
-__device__ __forceinline__ bool light_boxes_hit(const DGltfScene &sc, const V3 o, const V3 d) {
+// Returns the set of pierced cut boxes as a bit mask (bit k = box k); with no cut, bit 0 stands for the root box.
+__device__ __forceinline__ uint32_t light_boxes_mask(const DGltfScene &sc, const V3 o, const V3 d) {
     const V3 inv = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
     float tn;
-    if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2], o, inv, INFINITY, tn)) return false;
-    bool any = sc.n_light_top == 0;
+    if (!slab6(sc.light_min[0], sc.light_min[1], sc.light_min[2], sc.light_max[0], sc.light_max[1], sc.light_max[2], o, inv, INFINITY, tn)) return 0u;
+    if (sc.n_light_top == 0) return 1u;
+    uint32_t mask = 0u;
 #pragma unroll
     for (int k = 0; k < B200RT_LIGHT_TOP; k++)
-        if (k < sc.n_light_top)
-            any = any || slab6(sc.light_top[k][0], sc.light_top[k][1], sc.light_top[k][2], sc.light_top[k][3], sc.light_top[k][4], sc.light_top[k][5], o, inv, INFINITY, tn);
-    return any;
+        if (k < sc.n_light_top &&
+            slab6(sc.light_top[k][0], sc.light_top[k][1], sc.light_top[k][2], sc.light_top[k][3], sc.light_top[k][4], sc.light_top[k][5], o, inv, INFINITY, tn))
+            mask |= 1u << k;
+    return mask;
+}
+__device__ __forceinline__ bool light_boxes_hit(const DGltfScene &sc, const V3 o, const V3 d) { return light_boxes_mask(sc, o, d) != 0u; }
+// Start of a light-pdf traversal for a non-zero mask: the pierced cut nodes in ascending order (the first becomes
+// `cur`, the others are stacked so that they pop in order) -- every scheduling sums in this order.
+__device__ __forceinline__ void light_start(const DGltfScene &sc, uint32_t mask, uint32_t *stack, int &sp, uint32_t &cur) {
+    sp = 0;
+    if (!sc.light_top_start || sc.n_light_top == 0) { cur = sc.light_root; return; }
+#pragma unroll
+    for (int k = B200RT_LIGHT_TOP - 1; k >= 0; k--)
+        if (mask & (1u << k)) stack[sp++] = sc.light_top_word[k];
+    cur = stack[--sp];
 }
 
 // A ray expressed on the 16-bit grid of a tree.  With o' = (o - base) / scale and inv' = scale / d the
@@ -219,9 +233,11 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
     float total = 0.f;
     // unlike the scene root, the light root's box IS a real filter
     if (COUNT) tc.light_node_tests++;
-    if (!light_boxes_hit(sc, o, d)) return 0.f;
+    const uint32_t mask = light_boxes_mask(sc, o, d);
+    if (!mask) return 0.f;
     const QRay qr = make_qray(sc.lq, o, d);
-    uint32_t cur = sc.light_root;
+    uint32_t cur;
+    light_start(sc, mask, stack, sp, cur);
     while (true) {
         if (!(cur & B200RT_LEAF)) {
             float tl, tr;

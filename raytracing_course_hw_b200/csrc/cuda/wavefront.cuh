@@ -36,6 +36,7 @@ namespace b200rt {
 #ifndef B200RT_EXT_UNROLL
 #define B200RT_EXT_UNROLL 2      /* box steps per phase decision in wf_extend's inner phase */
 #endif
+#define B200RT_WF_MASK_SHIFT 26  /* light-queue entry = path slot | light-cut mask << 26 (slots < 2^26, <= 6 cut boxes) */
 #define B200RT_WF_MISS 0x7FFFFFFFu
 #define B200RT_WF_DEAD 0x7FFFFFFEu   /* written by wf_trace: the firefly clamp ended this path */
 #define B200RT_FULL 0xffffffffu
@@ -125,7 +126,7 @@ __device__ __forceinline__ void queue_push(int *queue, int *counter, bool want, 
 
 // Append to two queues whose counters are the low / high half of one aligned 64-bit word: one atomic round trip
 // per warp instead of two (ncu: the returning atomics were 10 % of wf_shade's stall samples).
-__device__ __forceinline__ void queue_push2(int *q_lo, int *q_hi, int *counter_lo, bool want_lo, bool want_hi, int value) {
+__device__ __forceinline__ void queue_push2(int *q_lo, int *q_hi, int *counter_lo, bool want_lo, bool want_hi, int value_lo, int value_hi) {
     const unsigned m_lo = __ballot_sync(B200RT_FULL, want_lo), m_hi = __ballot_sync(B200RT_FULL, want_hi);
     if ((m_lo | m_hi) == 0) return;
     const int lane = threadIdx.x & 31;
@@ -133,8 +134,8 @@ __device__ __forceinline__ void queue_push2(int *q_lo, int *q_hi, int *counter_l
     if (lane == 0) base = atomicAdd(reinterpret_cast<unsigned long long *>(counter_lo), (unsigned long long)__popc(m_lo) | ((unsigned long long)__popc(m_hi) << 32));
     base = __shfl_sync(B200RT_FULL, base, 0);
     const unsigned below = (1u << lane) - 1u;
-    if (want_lo) __stcs(q_lo + (int)(unsigned)base + __popc(m_lo & below), value);
-    if (want_hi) __stcs(q_hi + (int)(unsigned)(base >> 32) + __popc(m_hi & below), value);
+    if (want_lo) __stcs(q_lo + (int)(unsigned)base + __popc(m_lo & below), value_lo);
+    if (want_hi) __stcs(q_hi + (int)(unsigned)(base >> 32) + __popc(m_hi & below), value_hi);
 }
 
 // Prefetch one 32-byte sector into L2 (the wave state streams through DRAM; whoever knows a path index early
@@ -463,6 +464,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
 #endif
         bool cont = false, direct = false;
         int p = 0;
+        uint32_t light_mask = 0u;     // pierced boxes of the light cut: rides in the top bits of the light-queue entry
 #if B200RT_SHADE_PIPE
         cp_async_wait_all();
         float4 h, ro, rd, th, ra;
@@ -535,7 +537,8 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                     // A ray that misses the boxes around the emitters has a light pdf of exactly 0
                     // (light_boxes_hit): the bounce is finished here and the path skips the light stage
                     // (its queue entry, bsdf round trip and refill slot).
-                    if (!light_boxes_hit(sc, bo.xo, bo.nd)) {
+                    light_mask = light_boxes_mask(sc, bo.xo, bo.nd);
+                    if (!light_mask) {
                         if (COUNT) tc.light_node_tests++;
                         answered++;
                         direct = true;
@@ -564,7 +567,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             prefetch_l2(sq); prefetch_l2(sq + 32); prefetch_l2(sq + 64);
         }
 #endif
-        if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, p);   // n_direct == n_out + 1
+        if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, (int)((uint32_t)p | (light_mask << B200RT_WF_MASK_SHIFT)), p);   // n_direct == n_out + 1
         else queue_push(q_out, n_out, cont && !direct, p);
     }
 #if B200RT_SHADE_PIPE
@@ -614,9 +617,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
             if (!active) {
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
-                    p = __ldcs(q_in + idx);
+                    const uint32_t entry = (uint32_t)__ldcs(q_in + idx);
+                    p = (int)(entry & ((1u << B200RT_WF_MASK_SHIFT) - 1u));
 #if B200RT_REFILL_PF
-                    const int ahead = idx + B200RT_REFILL_PF < n ? __ldcs(q_in + idx + B200RT_REFILL_PF) : -1;
+                    const int ahead = idx + B200RT_REFILL_PF < n ? (int)((uint32_t)__ldcs(q_in + idx + B200RT_REFILL_PF) & ((1u << B200RT_WF_MASK_SHIFT) - 1u)) : -1;
 #endif
                     const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
 #if B200RT_REFILL_PF
@@ -630,7 +634,17 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     // the light root's box is a real filter (unlike the scene root); `filtered`: shade already
                     // applied light_boxes_hit to every query in this queue
                     if (COUNT) node_tests++;
-                    if (filtered || light_boxes_hit(sc, o, d)) cur = sc.light_root;
+                    // (the mask of pierced cut boxes came with the queue entry); the traversal starts at those boxes
+                    const uint32_t mask = filtered ? entry >> B200RT_WF_MASK_SHIFT : light_boxes_mask(sc, o, d);
+                    if (mask) {      // light_start() through this kernel's own stack type
+                        if (!sc.light_top_start || sc.n_light_top == 0) cur = sc.light_root;
+                        else {
+#pragma unroll
+                            for (int k = B200RT_LIGHT_TOP - 1; k >= 0; k--)
+                                if (mask & (1u << k)) stack.push(sp, sc.light_top_word[k]);
+                            cur = stack.pop(sp);
+                        }
+                    }
                     else cur = B200RT_LEAF;      // empty leaf: finishes on the next leaf phase
                 }
             }
