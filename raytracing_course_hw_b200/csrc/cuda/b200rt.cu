@@ -714,6 +714,16 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
     if (!ctx->blocks_extend[COUNT]) {
         int dev = ctx->device, nb = 0;
         CK(cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, dev));
+        // L1 / shared-memory split (percent of shared memory): development knobs, default = the driver's choice.
+        // Asking for the largest L1 outright is SLOWER here (shade +54 %, extend +5 %: profiles/r01_sweep_carveout.log).
+        if (const char *e = getenv("B200RT_CARVEOUT_TRAVERSE")) {
+            cudaFuncSetAttribute(wf_extend<COUNT>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+            cudaFuncSetAttribute(wf_light<COUNT>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+        }
+        if (const char *e = getenv("B200RT_CARVEOUT_SHADE")) {
+            cudaFuncSetAttribute(wf_shade<HW8, COUNT, false>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+            cudaFuncSetAttribute(wf_shade<HW8, COUNT, true>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+        }
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_extend<COUNT>, 128, 0));
         if (ctx->wf_blocks_cap) nb = std::min(nb, ctx->wf_blocks_cap);
         ctx->blocks_extend[COUNT] = std::max(1, nb) * ctx->num_sms;
