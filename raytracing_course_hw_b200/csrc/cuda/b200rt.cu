@@ -97,6 +97,7 @@ struct b200rt_ctx {
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
     int light_top_max = B200RT_LIGHT_TOP;  // boxes of the light-BVH cut used as the light-pdf pre-filter (0/1 = root box only)
+    bool wf_first_implicit = true;   // camera paths: only the direction is stored by generate (B200RT_WF_FIRST_IMPLICIT=0: whole record)
     bool wf_drop_dark = true;    // paths whose last bounce cannot reach an emitter end one bounce early (black background only)
     bool wf_direct = true;       // shade finishes bounces whose ray misses the light root box (no light-stage entry)
     bool wf_fused = false;       // one traversal kernel per bounce (wf_trace) instead of extend + light
@@ -749,7 +750,10 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         wp.s_begin = s0;
         wp.s_count = std::min<int>((int)s_w, rp.spp_end - s0);
         CK(cudaMemsetAsync(wb.ctr - 4, 0, 4 * (B200RT_MAX_DEPTH + 2) * sizeof(int), st));
-        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters, W % 8 == 0 && H % 4 == 0);
+        // camera paths carry implicit state through their first extend / shade unless the path is one bounce long
+        // or the fused scheduling (which reads the whole record) is on
+        const int first_implicit = (rp.ray_depth > 1 && !(ctx->wf_fused && lights) && ctx->wf_first_implicit) ? 1 : 0;
+        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters, W % 8 == 0 && H % 4 == 0, !first_implicit);
         (*launches)++;
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
@@ -782,7 +786,8 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                 continue;
             }
             ctx->stamp(true, 0, st);
-            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t);
+            const int first = (b == 0 && first_implicit) ? 1 : 0;
+            wf_extend<COUNT><<<ctx->blocks_extend[COUNT], 128, 0, st>>>(ctx->gs, wb, qa, c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, first, wp.cam.pos[0], wp.cam.pos[1], wp.cam.pos[2]);
             ctx->stamp(false, 0, st);
             const bool last = b == rp.ray_depth - 1;
             // the bounce after this one is the last and a miss adds nothing: rays that cannot reach an emitter are dropped
@@ -790,7 +795,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                               ctx->gs.bg[0] == 0.f && ctx->gs.bg[1] == 0.f && ctx->gs.bg[2] == 0.f) ? 1 : 0;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop, first);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
                 wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct, drop);
@@ -799,8 +804,8 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
                 ctx->stamp(true, 1, st);
-                if (last) wf_shade<HW8, COUNT, true><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
-                else wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters);
+                if (last) wf_shade<HW8, COUNT, true><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
+                else wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }
@@ -956,6 +961,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_DIRECT")) ctx->wf_direct = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_DROP_DARK")) ctx->wf_drop_dark = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_FIRST_IMPLICIT")) ctx->wf_first_implicit = atoi(e) != 0;
     if (const char *e = getenv("B200RT_LIGHT_TOP")) ctx->light_top_max = std::max(0, atoi(e));
     if (const char *e = getenv("B200RT_WF_PIPE")) ctx->wf_pipe = std::min(B200RT_PIPE, std::max(1, atoi(e)));
     if (ctx->flags & B200RT_FLAG_SERIAL_WAVES) ctx->wf_pipe = 1;

@@ -173,7 +173,9 @@ struct TravStack {
 #endif
 };
 
-__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters, const bool dense) {
+// full = 0: only the ray direction is stored -- the first extend / shade of the wave (`first`) know the rest of a
+// camera path's state without reading it (origin = camera, throughput 1, radiance 0, Philox key / counter from the slot).
+__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters, const bool dense, const bool full) {
     const int n_slots = wp.n_tiles * 32 * wp.s_count;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -190,13 +192,15 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             const float nx = wp.cam.tan_x * (2.f * fx / (float)wp.cam.width - 1.f);
             const float ny = wp.cam.tan_y * (2.f * fy / (float)wp.cam.height - 1.f);
             const V3 d = normalize(nx * cright - ny * cup + cfwd);
-            st_state(&wb.ray_o[slot], make_float4(cpos.x, cpos.y, cpos.z, __uint_as_float(pixel)));
             st_state(&wb.ray_d[slot], make_float4(d.x, d.y, d.z, 0.f));
+            if (full) {
+            st_state(&wb.ray_o[slot], make_float4(cpos.x, cpos.y, cpos.z, __uint_as_float(pixel)));
             // whole 32-byte sectors ({hit, thr} and {rad, bsdf}): a half-written sector costs L2 a fill from DRAM first
             st_state(&wb.hit[slot], make_float4(0.f, 0.f, 0.f, 0.f));
             st_state(&wb.thr[slot], make_float4(1.f, 1.f, 1.f, 0.f));
             st_state(&wb.rad[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl))));
             st_state(&wb.bsdf[slot], make_float4(0.f, 0.f, 0.f, 0.f));
+            }
             made++;
         }
         // Frames whose width / height are multiples of the 8x4 tile have no dead slots: the first queue is the
@@ -224,7 +228,8 @@ __device__ unsigned long long g_phase[8];
 template <bool COUNT>
 __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
                                                  const int *__restrict__ n_in, int *cursor, DCounters *counters,
-                                                 const int batch, const int leaf_t) {
+                                                 const int batch, const int leaf_t, const int first = 0,
+                                                 const float cam_x = 0.f, const float cam_y = 0.f, const float cam_z = 0.f) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
 #if B200RT_STACK_TNEAR
@@ -262,11 +267,13 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 #if B200RT_REFILL_PF
                     const int ahead = idx + B200RT_REFILL_PF < n ? __ldcs(q_in + idx + B200RT_REFILL_PF) : -1;
 #endif
-                    const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
+                    const float4 rd = ld_state(&wb.ray_d[p]);
+                    if (first) o = mk(cam_x, cam_y, cam_z);      // camera rays: the origin is not stored (wf_generate)
+                    else { const float4 ro = ld_state(&wb.ray_o[p]); o = mk(ro.x, ro.y, ro.z); }
 #if B200RT_REFILL_PF
                     if (ahead >= 0) prefetch_l2(&wb.ray_o[ahead]);     // arrived together with p: no extra wait
 #endif
-                    o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z);
+                    d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.q, o, d);
                     tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
                     sp = 0;
@@ -389,7 +396,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 template <bool HW8, bool COUNT, bool LAST = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
-                                                const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0) {
+                                                const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0, const int first = 0) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
 #if B200RT_SHADE_PIPE
@@ -504,9 +511,20 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             p = __ldcs(q_in + base + lane);
 #endif
             const float4 h = ld_state(&wb.hit[p]);
-            const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
-            const float4 th = ld_state(&wb.thr[p]);
-            float4 ra = ld_state(&wb.rad[p]);
+            const float4 rd = ld_state(&wb.ray_d[p]);
+            float4 ro, th, ra;
+            if (first) {
+                // camera paths: origin = camera, throughput 1, radiance 0; Philox key = pixel, counter = sample index
+                int px, py, sl;
+                slot_to_pixel(wp, p, px, py, sl);
+                ro = make_float4(wp.cam.pos[0], wp.cam.pos[1], wp.cam.pos[2], __uint_as_float((uint32_t)(py * wp.cam.width + px)));
+                th = make_float4(1.f, 1.f, 1.f, 0.f);
+                ra = make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)(wp.s_begin + sl)));
+            } else {
+                ro = ld_state(&wb.ray_o[p]);
+                th = ld_state(&wb.thr[p]);
+                ra = ld_state(&wb.rad[p]);
+            }
 #endif
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);

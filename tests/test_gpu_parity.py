@@ -203,6 +203,20 @@ def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
     assert out["1"][1] < out["0"][1]
 
 
+@pytest.mark.parametrize("w,h", [(128, 96), (101, 67)])
+def test_implicit_camera_state_is_the_stored_one(w, h, monkeypatch):
+    """The first extend / shade of a wave derive a camera path's state from its slot (origin = camera, throughput 1,
+    radiance 0, Philox key / counter) instead of reading what wf_generate would have stored: bit-identical image."""
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=w, height=h, samples=8)
+    out = {}
+    for v in ("1", "0"):
+        monkeypatch.setenv("B200RT_WF_FIRST_IMPLICIT", v)
+        r = rt.Renderer()
+        out[v] = (_render(r, sc), r.stats()["rays"])
+        r.close()
+    assert np.array_equal(out["1"][0], out["0"][0]) and out["1"][1] == out["0"][1]
+
+
 def test_reference_tree_and_rebuilt_tree_agree():
     """FLAG_REFERENCE_BVH traverses the description's SAH tree, the default the library's own binned-SAH
     tree over the same triangles: same closest hits (ties aside) => same image on the same stream."""
