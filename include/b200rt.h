@@ -223,6 +223,20 @@ int b200rt_upload_accum(b200rt_ctx *ctx, const float *rgb_in);
 /* Device pointer + element count of the accumulation buffer (for NCCL reduce by the host). */
 int b200rt_accum_device_ptr(b200rt_ctx *ctx, void **ptr, size_t *n_floats);
 
+/* Scene replication for multi-GPU runs (the scene is replicated on every GPU).  Instead of repeating the host
+ * side of b200rt_upload_scene (BVH rebuild, record building) once per GPU, the context that uploaded EXPORTS its
+ * device-resident scene -- one contiguous device blob + a fixed-size header -- and every peer IMPORTS a copy the
+ * caller delivers device to device (ncclBroadcast over NVLink in raytracing_course_hw_b200/dist.py, or a peer copy):
+ *     b200rt_export_scene(ctx0, &hdr, &src, &bytes);
+ *     b200rt_import_scene_begin(ctxK, &hdr, &dst);     -- sizes ctxK's arena, returns where the blob goes
+ *     <copy `bytes` bytes src -> dst on ctxK's stream (b200rt_stream)>
+ *     b200rt_import_scene_end(ctxK, &hdr);             -- rebases the pointers inside the copy; ctxK can render
+ * glTF modes (hw6-hw8) only; text scenes are a few hundred bytes, upload them per GPU. */
+typedef struct b200rt_scene_image { uint64_t opaque[256]; } b200rt_scene_image;
+int b200rt_export_scene(b200rt_ctx *ctx, b200rt_scene_image *hdr, void **device_blob, uint64_t *bytes);
+int b200rt_import_scene_begin(b200rt_ctx *ctx, const b200rt_scene_image *hdr, void **device_dst);
+int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr);
+
 /* hw1/hw2 parity aid: primitive index of the primary hit per pixel (-1 = miss), int32 W*H. */
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out);
 

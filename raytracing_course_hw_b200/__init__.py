@@ -118,6 +118,9 @@ def device_lib():
         L.b200rt_download_accum.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.b200rt_upload_accum.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.b200rt_accum_device_ptr.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
+        L.b200rt_export_scene.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint64)]
+        L.b200rt_import_scene_begin.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        L.b200rt_import_scene_end.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.b200rt_primary_ids.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
         L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
         L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
@@ -128,6 +131,7 @@ def device_lib():
 
 DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b200rt_render", "b200rt_clear",
                   "b200rt_resolve", "b200rt_download_accum", "b200rt_upload_accum", "b200rt_accum_device_ptr",
+                  "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
                   "b200rt_strerror", "b200rt_last_error", "b200rt_device_count"]
 HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_set_env_map", "b200rt_host_desc",
@@ -260,6 +264,29 @@ class Renderer:
         p, n = ctypes.c_void_p(), ctypes.c_size_t()
         self._ck(self._L.b200rt_accum_device_ptr(self._ctx, ctypes.byref(p), ctypes.byref(n)))
         return p.value, n.value
+
+    # scene replication (include/b200rt.h: b200rt_export_scene / b200rt_import_scene_*)
+    SCENE_IMAGE_BYTES = 2048
+
+    def export_scene(self):
+        """(header bytes, device pointer, byte count) of the uploaded glTF-mode scene."""
+        hdr = ctypes.create_string_buffer(self.SCENE_IMAGE_BYTES)
+        p, n = ctypes.c_void_p(), ctypes.c_uint64()
+        self._ck(self._L.b200rt_export_scene(self._ctx, hdr, ctypes.byref(p), ctypes.byref(n)))
+        return hdr.raw, p.value, n.value
+
+    def import_scene_begin(self, header):
+        """Sizes this context's arena for the exported scene; returns the device pointer the blob must be copied to."""
+        hdr = ctypes.create_string_buffer(bytes(header), self.SCENE_IMAGE_BYTES)
+        p = ctypes.c_void_p()
+        self._ck(self._L.b200rt_import_scene_begin(self._ctx, hdr, ctypes.byref(p)))
+        return p.value
+
+    def import_scene_end(self, header, scene):
+        """`scene` supplies the frame metadata (the same description every rank loaded; only its upload is skipped)."""
+        hdr = ctypes.create_string_buffer(bytes(header), self.SCENE_IMAGE_BYTES)
+        self._ck(self._L.b200rt_import_scene_end(self._ctx, hdr))
+        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
 
     def primary_ids(self):
         out = np.empty((self.height, self.width), np.int32)

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 #include "analytic_kernels.h"
 #include "b200rt.h"
@@ -70,7 +71,8 @@ struct b200rt_ctx {
     // builds the records in the staging buffer on all host cores and moves them with one async copy.
     // Both grow on demand and are reused by later uploads (no cudaMalloc / cudaFree per frame).
     char *arena_dev = nullptr, *arena_pin = nullptr;
-    size_t arena_cap = 0;
+    size_t arena_cap = 0, arena_used = 0;     // arena_used / n_materials: what b200rt_export_scene hands out
+    int n_materials = 0;
     float *lut_srgb = nullptr;
     RebuiltBvh own_bvh;                      // host scratch of the BVH rebuild (bvh_rebuild.h)
     std::vector<b200rt_triangle> own_tris;   // triangles in the rebuilt tree's order
@@ -639,6 +641,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s, bool trees_absent =
     g.materials = reinterpret_cast<const DMaterial *>(dev + o_mats);
     ctx->lut_srgb = reinterpret_cast<float *>(dev + o_lut);
     ctx->gs = g;
+    ctx->arena_used = off; ctx->n_materials = (int)nm;
     lap("materials, lut, copy");
     return B200RT_OK;
 }
@@ -1192,6 +1195,82 @@ int b200rt_accum_device_ptr(b200rt_ctx *ctx, void **ptr, size_t *n_floats) {
     *ptr = ctx->total;
     *n_floats = (size_t)ctx->acc_w * ctx->acc_h * 3;
     return B200RT_OK;
+}
+
+// ---- scene replication (include/b200rt.h) ----------------------------------------------------------------
+namespace {
+struct SceneImage {
+    uint64_t magic, base, bytes, lut;
+    int32_t n_materials, pad;
+    DGltfScene gs;
+    b200rt_scene_desc desc;      // scalars only (pointers nulled)
+};
+static_assert(sizeof(SceneImage) <= sizeof(b200rt_scene_image), "b200rt_scene_image too small");
+const uint64_t kSceneMagic = 0x6232303072743031ull;     // "b200rt01"
+
+// texel pointers live INSIDE the blob (DMaterial records): shift them by the distance between the two arenas
+__global__ void rebase_materials_kernel(DMaterial *m, int n, long long delta) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    auto fix = [delta](DTexels &t) { if (t) t = reinterpret_cast<DTexels>(reinterpret_cast<const char *>(t) + delta); };
+    fix(m[i].tex_base); fix(m[i].tex_emissive); fix(m[i].tex_mr); fix(m[i].tex_normal);
+}
+}  // namespace
+
+int b200rt_export_scene(b200rt_ctx *ctx, b200rt_scene_image *hdr, void **device_blob, uint64_t *bytes) {
+    if (!ctx || !hdr || !device_blob || !bytes) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "export before upload_scene");
+    if (ctx->desc.mode < B200RT_MODE_HW6 || !ctx->arena_dev) return fail(ctx, B200RT_ERR_UNSUPPORTED, "scene export exists for the glTF modes only");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    memset(hdr, 0, sizeof(*hdr));
+    SceneImage im{};
+    im.magic = kSceneMagic; im.base = (uint64_t)(uintptr_t)ctx->arena_dev; im.bytes = ctx->arena_used;
+    im.lut = (uint64_t)(uintptr_t)ctx->lut_srgb; im.n_materials = ctx->n_materials;
+    im.gs = ctx->gs; im.desc = ctx->desc;
+    memcpy(hdr, &im, sizeof(im));
+    *device_blob = ctx->arena_dev;
+    *bytes = ctx->arena_used;
+    return B200RT_OK;
+}
+
+int b200rt_import_scene_begin(b200rt_ctx *ctx, const b200rt_scene_image *hdr, void **device_dst) {
+    if (!ctx || !hdr || !device_dst) return B200RT_ERR_INVALID;
+    SceneImage im;
+    memcpy(&im, hdr, sizeof(im));
+    if (im.magic != kSceneMagic || im.bytes == 0) return fail(ctx, B200RT_ERR_INVALID, "not a scene image");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    release_scene(ctx);
+    int rc = ensure_arena(ctx, (size_t)im.bytes);
+    if (rc) return rc;
+    *device_dst = ctx->arena_dev;
+    return B200RT_OK;
+}
+
+int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr) {
+    if (!ctx || !hdr) return B200RT_ERR_INVALID;
+    SceneImage im;
+    memcpy(&im, hdr, sizeof(im));
+    if (im.magic != kSceneMagic || !ctx->arena_dev || ctx->arena_cap < im.bytes) return fail(ctx, B200RT_ERR_INVALID, "import_scene_end without a matching begin");
+    CK(cudaSetDevice(ctx->device));
+    const long long delta = (long long)((intptr_t)ctx->arena_dev - (intptr_t)im.base);
+    auto move = [delta](auto *&p) { if (p) p = reinterpret_cast<std::remove_reference_t<decltype(p)>>(reinterpret_cast<const char *>(p) + delta); };
+    DGltfScene g = im.gs;
+    move(g.nodes); move(g.tris); move(g.shade); move(g.light_nodes); move(g.light_tris); move(g.light_sample_tris);
+    move(g.light_normals); move(g.materials); move(g.env);
+    if (im.n_materials > 0) {
+        rebase_materials_kernel<<<(im.n_materials + 63) / 64, 64, 0, ctx->stream>>>(const_cast<DMaterial *>(g.materials), im.n_materials, delta);
+        CK(cudaGetLastError());
+    }
+    ctx->gs = g;
+    ctx->lut_srgb = reinterpret_cast<float *>(reinterpret_cast<char *>((uintptr_t)im.lut) + delta);
+    ctx->arena_used = (size_t)im.bytes; ctx->n_materials = im.n_materials;
+    ctx->hw5_has_tris = false; ctx->hw5_n_lights = 0;
+    apply_l2_policy(ctx, (size_t)im.bytes);
+    ctx->desc = im.desc;
+    ctx->has_scene = true;
+    return b200rt_clear(ctx);
 }
 
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out) {

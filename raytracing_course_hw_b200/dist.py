@@ -23,6 +23,45 @@ def accum_tensor(renderer, device):
     return torch.as_tensor(_CudaArray(ptr, n), device=device)
 
 
+class _CudaBytes:
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def device_bytes(ptr, n, device):
+    """Zero-copy uint8 torch view of `n` device bytes at `ptr`."""
+    import torch
+    return torch.as_tensor(_CudaBytes(ptr, n), device=device)
+
+
+def upload_replicated(renderer, scene, rank, world, device=None, src=0):
+    """Replicates the scene on every rank's GPU with ONE host-side upload: rank `src` runs b200rt_upload_scene (BVH
+    rebuild, record building, H2D) and broadcasts its device-resident scene blob over NCCL / NVLink; the other ranks
+    import the copy (b200rt_import_scene_*) instead of repeating the host work on cores they would have to share."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        renderer.upload(scene)
+        return
+    nb = renderer.SCENE_IMAGE_BYTES
+    hdr = torch.zeros(nb, dtype=torch.uint8, device=device)
+    ptr = n = None
+    if rank == src:
+        renderer.upload(scene)
+        h, ptr, n = renderer.export_scene()
+        hdr.copy_(torch.frombuffer(bytearray(h), dtype=torch.uint8))
+    ext = torch.cuda.ExternalStream(renderer.stream(), device=device)
+    with torch.cuda.stream(ext):
+        dist.broadcast(hdr, src=src)
+        h = hdr.cpu().numpy().tobytes()
+        if rank != src:
+            ptr = renderer.import_scene_begin(h)
+            n = int.from_bytes(h[16:24], "little")        # SceneImage::bytes
+        dist.broadcast(device_bytes(ptr, n, device), src=src)
+    if rank != src:
+        renderer.import_scene_end(h, scene)
+
+
 def reduce_to_rank0(buf, dst=0):
     """Sum-reduce a torch tensor (CUDA: NCCL over NVLink; CPU: gloo) in place on `dst`."""
     import torch.distributed as dist

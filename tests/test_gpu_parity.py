@@ -217,6 +217,36 @@ def test_implicit_camera_state_is_the_stored_one(w, h, monkeypatch):
     assert np.array_equal(out["1"][0], out["0"][0]) and out["1"][1] == out["0"][1]
 
 
+def test_exported_scene_renders_the_same_image_in_another_context():
+    """b200rt_export_scene / b200rt_import_scene_*: the device blob of one context, copied device to device into
+    another context's arena and rebased (textures, materials, both trees), renders bit-identical frames -- the path
+    raytracing_course_hw_b200.dist.upload_replicated takes over NCCL on several GPUs."""
+    torch = pytest.importorskip("torch")
+    from raytracing_course_hw_b200 import dist as rtdist
+    dev = torch.device("cuda", 0)
+    sc = rt.load_scene(_room(), width=160, height=96, samples=4)
+    a, b = rt.Renderer(), rt.Renderer()
+    a.upload(sc)
+    hdr, src, n = a.export_scene()
+    dst = b.import_scene_begin(hdr)
+    assert dst != src and n > 0
+    rtdist.device_bytes(dst, n, dev).copy_(rtdist.device_bytes(src, n, dev))
+    torch.cuda.synchronize()
+    b.import_scene_end(hdr, sc)
+    imgs = []
+    for r in (a, b):
+        r.render(0, 4)
+        imgs.append(r.download_accum())
+    assert np.array_equal(imgs[0], imgs[1]) and imgs[0].max() > 0
+    # text scenes are not exported (they are a few hundred bytes of constant memory)
+    a.upload(rt.load_scene(os.path.join(S, "hw4/practice3_1.txt")))
+    with pytest.raises(rt.B200rtError):
+        a.export_scene()
+    with pytest.raises(rt.B200rtError):
+        b.import_scene_begin(b"\0" * 64)
+    a.close(); b.close()
+
+
 def test_reference_tree_and_rebuilt_tree_agree():
     """FLAG_REFERENCE_BVH traverses the description's SAH tree, the default the library's own binned-SAH
     tree over the same triangles: same closest hits (ties aside) => same image on the same stream."""
