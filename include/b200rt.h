@@ -236,6 +236,8 @@ typedef struct b200rt_scene_image { uint64_t opaque[256]; } b200rt_scene_image;
 int b200rt_export_scene(b200rt_ctx *ctx, b200rt_scene_image *hdr, void **device_blob, uint64_t *bytes);
 int b200rt_import_scene_begin(b200rt_ctx *ctx, const b200rt_scene_image *hdr, void **device_dst);
 int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr);
+/* The three steps in one call for two contexts of the same process (cudaMemcpyPeerAsync between their devices). */
+int b200rt_replicate_scene(b200rt_ctx *src, b200rt_ctx *dst);
 
 /* hw1/hw2 parity aid: primitive index of the primary hit per pixel (-1 = miss), int32 W*H. */
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out);

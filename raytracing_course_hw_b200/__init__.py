@@ -121,6 +121,7 @@ def device_lib():
         L.b200rt_export_scene.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint64)]
         L.b200rt_import_scene_begin.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
         L.b200rt_import_scene_end.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_replicate_scene.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.b200rt_primary_ids.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
         L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
         L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
@@ -131,7 +132,7 @@ def device_lib():
 
 DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b200rt_render", "b200rt_clear",
                   "b200rt_resolve", "b200rt_download_accum", "b200rt_upload_accum", "b200rt_accum_device_ptr",
-                  "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end",
+                  "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end", "b200rt_replicate_scene",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
                   "b200rt_strerror", "b200rt_last_error", "b200rt_device_count"]
 HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_set_env_map", "b200rt_host_desc",
@@ -286,6 +287,11 @@ class Renderer:
         """`scene` supplies the frame metadata (the same description every rank loaded; only its upload is skipped)."""
         hdr = ctypes.create_string_buffer(bytes(header), self.SCENE_IMAGE_BYTES)
         self._ck(self._L.b200rt_import_scene_end(self._ctx, hdr))
+        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
+
+    def replicate_from(self, other, scene):
+        """Device-to-device copy of `other`'s uploaded scene into this context (same process, any two devices)."""
+        self._ck(self._L.b200rt_replicate_scene(other._ctx, self._ctx))
         self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
 
     def primary_ids(self):

@@ -70,7 +70,8 @@ int main(int argc, const char *argv[]) {
     for (int g = 0; g < n_gpus && !rc; g++) {
         opt.device = g;
         rc = b200rt_create(&ctx[g], &opt);
-        if (!rc) rc = b200rt_upload_scene(ctx[g], d);
+        // one host-side upload; the other GPUs get a device-to-device copy of the resident scene (glTF modes)
+        if (!rc) rc = (g > 0 && d->mode >= B200RT_MODE_HW6) ? b200rt_replicate_scene(ctx[0], ctx[g]) : b200rt_upload_scene(ctx[g], d);
         if (rc) fprintf(stderr, "b200rt: GPU %d: %s (%s)\n", g, b200rt_strerror(rc), ctx[g] ? b200rt_last_error(ctx[g]) : "");
     }
     double t_upload = now_ms() - t0;

@@ -1273,6 +1273,19 @@ int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr) {
     return b200rt_clear(ctx);
 }
 
+int b200rt_replicate_scene(b200rt_ctx *src, b200rt_ctx *dst) {
+    if (!src || !dst || src == dst) return B200RT_ERR_INVALID;
+    b200rt_scene_image hdr;
+    void *from = nullptr, *to = nullptr;
+    uint64_t bytes = 0;
+    int rc = b200rt_export_scene(src, &hdr, &from, &bytes);
+    if (rc) { dst->last_error = src->last_error; return rc; }
+    if ((rc = b200rt_import_scene_begin(dst, &hdr, &to))) return rc;
+    b200rt_ctx *ctx = dst;
+    CK(cudaMemcpyPeerAsync(to, dst->device, from, src->device, (size_t)bytes, dst->stream));
+    return b200rt_import_scene_end(dst, &hdr);
+}
+
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out) {
     if (!ctx || !ids_out) return B200RT_ERR_INVALID;
     if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "primary_ids before upload_scene");

@@ -238,6 +238,11 @@ def test_exported_scene_renders_the_same_image_in_another_context():
         r.render(0, 4)
         imgs.append(r.download_accum())
     assert np.array_equal(imgs[0], imgs[1]) and imgs[0].max() > 0
+    c = rt.Renderer()
+    c.replicate_from(a, sc)             # the same three steps in one call (what the CLI does for B200RT_GPUS > 1)
+    c.render(0, 4)
+    assert np.array_equal(c.download_accum(), imgs[0])
+    c.close()
     # text scenes are not exported (they are a few hundred bytes of constant memory)
     a.upload(rt.load_scene(os.path.join(S, "hw4/practice3_1.txt")))
     with pytest.raises(rt.B200rtError):
