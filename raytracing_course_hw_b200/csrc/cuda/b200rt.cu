@@ -142,13 +142,10 @@ void parallel_for(size_t n, const F &f) {
     const unsigned nt = (unsigned)std::min<size_t>((size_t)host_threads(), (n + 16383) / 16384);
     if (nt <= 1) { f((size_t)0, n); return; }
     const size_t chunk = (n + nt - 1) / nt;
-    std::vector<std::thread> pool;
-    for (unsigned t = 1; t < nt; t++) {
+    HostPool::get().run(nt, [&](unsigned t) {           // persistent workers (bvh_rebuild.h)
         const size_t a = t * chunk, b = std::min(n, a + chunk);
-        if (a < b) pool.emplace_back([a, b, &f] { f(a, b); });
-    }
-    f((size_t)0, std::min(n, chunk));
-    for (auto &th : pool) th.join();
+        if (a < b) f(a, b);
+    });
 }
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }

@@ -17,7 +17,12 @@
 #include <atomic>
 #include <cfloat>
 #include <cstdint>
+#include <chrono>
+#include <cstdio>
+#include <condition_variable>
 #include <cstdlib>
+#include <functional>
+#include <cstring>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -40,6 +45,75 @@ inline unsigned host_threads() {
     if (const char *e = getenv("B200RT_HOST_THREADS")) n = (unsigned)std::max(1, std::min(64, atoi(e)));
     return n;
 }
+
+// Persistent host workers for the upload path (BVH rebuild, record building).  A scene upload runs ~20 short
+// parallel sections; spawning 16 std::threads for each cost more than the work inside (measured on the GPU box's
+// virtualised cores: ~1 ms per round).  run(n, fn) executes fn(0) .. fn(n-1) on the pool plus the calling thread
+// and returns when all are done; one job at a time (contexts driven from different host threads take turns).
+class HostPool {
+public:
+    static HostPool &get() { static HostPool p; return p; }
+    void run(unsigned n, const std::function<void(unsigned)> &fn) {
+        if (n <= 1) { if (n) fn(0); return; }
+        std::lock_guard<std::mutex> serial(run_mu_);
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            while (workers_.size() + 1 < n) workers_.emplace_back([this] { loop(); });
+            job_ = &fn; n_tasks_ = n; next_ = 0; done_ = 0; gen_++;
+        }
+        cv_work_.notify_all();
+        work();
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [this] { return done_ == n_tasks_; });
+        job_ = nullptr;
+    }
+    ~HostPool() {
+        { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
+        cv_work_.notify_all();
+        for (auto &t : workers_) t.join();
+    }
+private:
+    void work() {
+        for (;;) {
+            unsigned t;
+            const std::function<void(unsigned)> *job;
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (!job_ || next_ >= n_tasks_) return;
+                t = next_++; job = job_;
+            }
+            (*job)(t);
+            std::lock_guard<std::mutex> lk(mu_);
+            if (++done_ == n_tasks_) cv_done_.notify_all();
+        }
+    }
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            // an upload issues its parallel sections back to back: spin briefly before going to sleep, a futex wake
+            // of a parked (virtual) core costs more than most sections
+            for (int spin = 0; spin < 20000 && gen_.load(std::memory_order_acquire) == seen && !stop_; spin++) {
+#if defined(__x86_64__) || defined(__i386__)
+                __builtin_ia32_pause();
+#endif
+            }
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_work_.wait(lk, [&] { return stop_ || gen_.load() != seen; });
+                if (stop_) return;
+                seen = gen_.load();
+            }
+            work();
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex mu_, run_mu_;
+    std::condition_variable cv_work_, cv_done_;
+    const std::function<void(unsigned)> *job_ = nullptr;
+    unsigned n_tasks_ = 0, next_ = 0, done_ = 0;
+    std::atomic<uint64_t> gen_{0};
+    std::atomic<bool> stop_{false};
+};
 
 namespace bvh_detail {
 
@@ -202,14 +276,11 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
     bins.reset();
     if (nt > 1) {
         std::vector<Bins> part(nt);
-        std::vector<std::thread> pool;
         const uint32_t chunk = (count + nt - 1) / nt;
-        for (unsigned t = 0; t < nt; t++)
-            pool.emplace_back([&, t] {
-                part[t].reset();
-                bin_range(c, std::min(last, first + t * chunk), std::min(last, first + (t + 1) * chunk), cb, k, part[t]);
-            });
-        for (auto &th : pool) th.join();
+        HostPool::get().run(nt, [&](unsigned t) {
+            part[t].reset();
+            bin_range(c, std::min(last, first + t * chunk), std::min(last, first + (t + 1) * chunk), cb, k, part[t]);
+        });
         for (unsigned t = 0; t < nt; t++) bins.merge(part[t]);
     } else {
         bin_range(c, first, last, cb, k, bins);
@@ -281,9 +352,8 @@ inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id
 
 inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBvh &out, bool light_set = false) {
     using namespace bvh_detail;
-    out.nodes.clear();
     out.order.resize((size_t)std::max(n, 0));
-    if (n <= 0) return;
+    if (n <= 0) { out.nodes.clear(); return; }      // (otherwise the node array keeps its size: no 21 MB value-initialisation per build)
     Ctx c{};
     c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
     c.sweep_max = 12;
@@ -310,29 +380,42 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
             }
         };
         if (c.threads > 1) {
-            std::vector<std::thread> pool;
             const size_t chunk = ((size_t)n + c.threads - 1) / c.threads;
-            for (unsigned t = 0; t < c.threads; t++) pool.emplace_back(prep, std::min((size_t)n, t * chunk), std::min((size_t)n, (t + 1) * chunk));
-            for (auto &th : pool) th.join();
+            HostPool::get().run(c.threads, [&](unsigned t) { prep(std::min((size_t)n, t * chunk), std::min((size_t)n, (t + 1) * chunk)); });
         } else prep(0, (size_t)n);
     }
     c.box = box; c.cen = cen; c.order = out.order.data();
+    const bool timing = !light_set && getenv("B200RT_UPLOAD_TIMING") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rebuild] %-20s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
+    lap("boxes, centroids");
 
     // Node slots: 0 = root; a node with `count` triangles owns at most 2 * count - 2 descendants.  The top of
     // the tree takes slots from a shared cursor; a subtree task gets a private range up front.
     std::vector<b200rt_bvh_node> &nodes = out.nodes;
     const uint32_t top_cap = c.threads > 1 ? 4096u : 1u;      // slots [0, top_cap): root and the nodes split in phases A / B
-    nodes.assign((size_t)top_cap + (size_t)n * 2 + 2, b200rt_bvh_node{});
+    {
+        // Unused slots must read as empty leaves.  Clearing all 21 MB (268 k triangles) up front cost 2 ms of a 12 ms
+        // build; instead the top slots are cleared here, every subtree task clears its own range right before it
+        // writes into it (parallel, and the lines are then warm), and the gap between the two is cleared at the end.
+        const size_t need = (size_t)top_cap + (size_t)n * 2 + 2;
+        if (nodes.capacity() < need) { nodes.clear(); nodes.reserve(need); }
+        nodes.resize(need);
+        memset((void *)nodes.data(), 0, (c.threads > 1 ? (size_t)top_cap : need) * sizeof(b200rt_bvh_node));
+    }
+    lap("zero node slots");
     nodes[0].first = 0; nodes[0].last = (uint32_t)n;
     // root bounds: the only full bounds pass (children get theirs from their parent's bins)
     NodeBounds rb;
     if (c.threads > 1) {
         std::vector<NodeBounds> part(c.threads);
-        std::vector<std::thread> pool;
         const uint32_t chunk = ((uint32_t)n + c.threads - 1) / c.threads;
-        for (unsigned t = 0; t < c.threads; t++)
-            pool.emplace_back([&, t] { bounds(c, std::min((uint32_t)n, t * chunk), std::min((uint32_t)n, (t + 1) * chunk), part[t].nb, part[t].cb); });
-        for (auto &th : pool) th.join();
+        HostPool::get().run(c.threads, [&](unsigned t) { bounds(c, std::min((uint32_t)n, t * chunk), std::min((uint32_t)n, (t + 1) * chunk), part[t].nb, part[t].cb); });
         rb.nb.reset(); rb.cb.reset();
         for (auto &pb : part) { rb.nb.grow(pb.nb); rb.cb.grow(pb.cb); }
     } else {
@@ -343,6 +426,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
         while (used > 1 && nodes[used - 1].left == 0 && nodes[used - 1].first == nodes[used - 1].last) used--;
         nodes.resize(used);
     };
+    lap("root bounds");
     if (c.threads == 1) { build_subtree(c, nodes.data(), 0, top_cap, rb); shrink(); return; }
 
     // phase A: the few very large nodes at the top, one by one, with the binning spread over the cores
@@ -374,6 +458,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
             break;
         }
     }
+    lap("phase A (top nodes)");
     // phase B: a shared work queue; a worker either splits a medium node (children go back to the queue)
     // or builds a small node's whole subtree into a slot range of its own.  Subtree ranges are handed out
     // from the END of the array downwards so that they never meet the cursor of the top nodes.
@@ -381,9 +466,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
     int inflight = 0;
     uint32_t tail = (uint32_t)nodes.size();
     {
-        std::vector<std::thread> pool;
-        for (unsigned t = 0; t < c.threads; t++)
-            pool.emplace_back([&] {
+        HostPool::get().run(c.threads, [&](unsigned) {
                 for (;;) {
                     uint32_t id, slot = 0;
                     NodeBounds mine;
@@ -406,6 +489,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
                     }
                     const uint32_t first = nodes[id].first, last = nodes[id].last;
                     if (whole) {
+                        memset((void *)(nodes.data() + slot), 0, (size_t)2 * (last - first) * sizeof(b200rt_bvh_node));
                         build_subtree(c, nodes.data(), id, slot, mine);
                         std::lock_guard<std::mutex> lk(mu);
                         inflight--;
@@ -420,9 +504,11 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
                     }
                 }
             });
-        for (auto &th : pool) th.join();
     }
+    if (tail > top_cap) memset((void *)(nodes.data() + top_cap), 0, (size_t)(tail - top_cap) * sizeof(b200rt_bvh_node));      // never handed out
+    lap("phase B (subtrees)");
     shrink();
+    lap("shrink");
 }
 
 }  // namespace b200rt
