@@ -18,3 +18,17 @@ def test_bvh_rebuild_invariants(tmp_path):
     r = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
     assert r.returncode == 0, r.stdout
     assert r.stdout.count(" ok") == 6
+
+
+def test_host_pool_stress(tmp_path):
+    """The persistent worker pool every parallel section of the upload runs on: 8000 short jobs from two caller
+    threads, each task exactly once (a lost wake-up here would hang an upload)."""
+    gxx = os.environ.get("B200RT_CXX", "/usr/bin/g++")
+    if not os.path.exists(gxx):
+        gxx = shutil.which("g++")
+    exe = str(tmp_path / "pool_check")
+    subprocess.run([gxx, "-O2", "-std=c++17", "-pthread", "-I", os.path.join(ROOT, "include"),
+                    "-I", os.path.join(ROOT, "raytracing_course_hw_b200", "csrc", "cuda"),
+                    os.path.join(ROOT, "tests", "native", "host_pool_check.cpp"), "-o", exe], check=True)
+    r = subprocess.run([exe], stdout=subprocess.PIPE, text=True, timeout=120)
+    assert r.returncode == 0 and "host pool ok" in r.stdout, r.stdout
