@@ -736,6 +736,9 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         ctx->blocks_trace[COUNT] = std::max(1, nb) * ctx->num_sms;
     }
     const bool lights = ctx->gs.n_light_tris > 0;
+    // a light-queue entry carries the light-cut mask above bit 26: waves of 2^26 slots or more (frames above 67 M
+    // pixels) leave it out and the light stage tests the cut boxes itself
+    const int pack_mask = per * s_w < (1ll << B200RT_WF_MASK_SHIFT) ? 1 : 0;
     const int flat_blocks = ctx->num_sms * 16;
     ctx->pipe_stream[0] = ctx->stream;
     if (n_pipe > 1) {      // fork: the side streams start after everything already queued on the main stream
@@ -795,10 +798,10 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                               ctx->gs.bg[0] == 0.f && ctx->gs.bg[1] == 0.f && ctx->gs.bg[2] == 0.f) ? 1 : 0;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop, first);
+                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop, first, pack_mask);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct, drop);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct && pack_mask, drop);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {

@@ -396,7 +396,8 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 template <bool HW8, bool COUNT, bool LAST = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
-                                                const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0, const int first = 0) {
+                                                const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0, const int first = 0,
+                                                const int pack_mask = 1) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
 #if B200RT_SHADE_PIPE
@@ -585,7 +586,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             prefetch_l2(sq); prefetch_l2(sq + 32); prefetch_l2(sq + 64);
         }
 #endif
-        if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, (int)((uint32_t)p | (light_mask << B200RT_WF_MASK_SHIFT)), p);   // n_direct == n_out + 1
+        if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, (int)((uint32_t)p | (pack_mask ? light_mask << B200RT_WF_MASK_SHIFT : 0u)), p);   // n_direct == n_out + 1
         else queue_push(q_out, n_out, cont && !direct, p);
     }
 #if B200RT_SHADE_PIPE

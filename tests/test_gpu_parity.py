@@ -426,6 +426,20 @@ def test_full_size_frame_properties(renderer):
     assert img.shape == (2160, 3840, 3)
 
 
+def test_wave_of_two_to_the_26_slots():
+    """8192 x 8192 = 2^26 pixels: the largest wave whose slot index leaves no room for the light-cut mask in a queue
+    entry (the light stage then tests the cut boxes itself).  Same camera => same mean radiance as a small frame."""
+    small = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=256, height=256, samples=64)
+    big = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=8192, height=8192, samples=1)
+    r = rt.Renderer()
+    ref = _render(r, small).mean() / 64
+    acc = _render(r, big)
+    st = r.stats()
+    r.close()
+    assert st["paths"] == 1 << 26 and np.isfinite(acc).all()
+    assert abs(acc.mean() - ref) <= 0.02 * ref, (acc.mean(), ref)
+
+
 def test_errors_are_reported_not_thrown(renderer):
     r = rt.Renderer()
     try:
