@@ -114,6 +114,18 @@ def test_hw5_matches_port_on_same_stream(renderer):
     assert abs(int(st["light_queries"]) - int(port["counters"][3])) <= 2e-3 * int(port["counters"][3])
 
 
+def test_hw5_without_triangles_matches_port_on_same_stream(renderer):
+    """hw5 rules on a scene with analytic figures only (planes, rotated box light, ellipsoids, box): the triangle side
+    of K7 is empty, the mixed-figure BVH of the description holds boxes and ellipsoids."""
+    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16, mode=rt.MODE_HW5)
+    assert sc.mode == rt.MODE_HW5 and sc.desc.n_light_prims == 1
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1)
+    ok, frac = _mean_close(acc, port["accum"], 16, 0.98, rel=5e-2)
+    assert ok, frac
+    assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+
+
 def test_hw4_box_light_matches_port_on_same_stream(renderer):
     sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16)
     acc = _render(renderer, sc)

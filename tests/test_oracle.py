@@ -65,7 +65,7 @@ def test_port_hw5_bytes_equal_reference():
     assert np.array_equal(o["rgb"], ou.golden("hw5_mixed_spp4"))
 
 
-@pytest.mark.parametrize("hw,mode", [("hw4", 4), ("hw3", 3)])
+@pytest.mark.parametrize("hw,mode", [("hw4", 4), ("hw3", 3), ("hw5", 5)])
 def test_port_box_light_bytes_equal_reference(hw, mode):
     """None of the reference's hw3 / hw4 scenes has a BOX light; this subset of the hw5 fixture has a rotated one
     (non-unit quaternion).  Pins BoxLight::sample's argument evaluation order (right to left under g++)."""

@@ -53,6 +53,7 @@ def main():
     # box-light subset of the hw5 fixture under hw4 and hw3 rules; the hw5 fixture itself (tools/make_hw5_fixture.py)
     run("hw4", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw4_boxlight_spp4")
     run("hw3", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw3_boxlight_spp4")
+    run("hw5", [os.path.join(GOLD, "hw4_boxlight_spp4.txt"), "@OUT"], "hw5_boxlight_spp4")      # hw5 rules, no triangle at all
     hw5 = open(os.path.join(SC, "hw5/mixed.txt")).read()
     # 2048, not 4096: between 2048 and 3072 samples some pixel's generator reaches a state from which the reference's
     # unbounded rejection loop (BoxLight / EllipsoidLight::sample, hw5/src/include/distributions.h:88-104) never
