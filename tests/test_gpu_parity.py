@@ -452,6 +452,45 @@ def test_wave_of_two_to_the_26_slots():
     assert abs(acc.mean() - ref) <= 0.02 * ref, (acc.mean(), ref)
 
 
+@pytest.mark.parametrize("mode_lines,mode", [("", rt.MODE_HW1), ("AMBIENT_LIGHT 0.2 0.2 0.2\nRAY_DEPTH 3\n", rt.MODE_HW2),
+                                             ("SAMPLES 4\nRAY_DEPTH 3\n", rt.MODE_HW4), ("SAMPLES 4\nRAY_DEPTH 3\n", rt.MODE_HW3)])
+def test_empty_text_scene_is_background(renderer, tmp_path, mode_lines, mode):
+    """No primitive at all: every ray misses, the frame is the background colour in every text mode (the reference
+    loops over an empty figure list, hw1/src/scene.cpp:9-19, hw4/src/scene.cpp:30-48)."""
+    p = tmp_path / "empty.txt"
+    p.write_text("DIMENSIONS 33 17\nBG_COLOR 0.25 0.5 0.75\nCAMERA_POSITION 0 0 0\nCAMERA_RIGHT 1 0 0\nCAMERA_UP 0 1 0\n"
+                 "CAMERA_FORWARD 0 0 -1\nCAMERA_FOV_X 1.0\n" + mode_lines)
+    sc = rt.load_scene(str(p), mode=mode if mode == rt.MODE_HW3 else 0)
+    assert sc.mode == mode and sc.desc.n_prims == 0
+    acc = _render(renderer, sc)
+    n = 1 if mode <= rt.MODE_HW2 else 4
+    assert np.allclose(acc / n, np.array([0.25, 0.5, 0.75], np.float32), rtol=1e-6)
+    port = ou.port_render(sc, 1 if mode > rt.MODE_HW2 else 0)
+    assert np.array_equal(renderer.resolve(n), port["rgb"])
+
+
+def test_gltf_scene_without_emitters_under_an_environment_map(renderer, tmp_path):
+    """No emissive triangle (FiguresMix is empty, Mix has two components, hw8/src/scene.cpp:64-74): the wavefront's
+    shade stage finishes every bounce itself and there is no light stage; all light comes from the environment map."""
+    import re
+    import shutil
+    for f in ("sphere_emissive.bin", "sphere_emission.png"):
+        shutil.copy(os.path.join(S, "hw8", f), tmp_path / f)
+    src = open(os.path.join(S, "hw8/sphere_emissive.gltf")).read()
+    dark, n = re.subn(r'"emissiveFactor"\s*:\s*\[[^\]]*\]', '"emissiveFactor": [0, 0, 0]', src)
+    assert n >= 1
+    (tmp_path / "dark.gltf").write_text(dark)
+    sc = rt.load_scene(str(tmp_path / "dark.gltf"), width=96, height=64, samples=16, env_map=os.path.join(S, "hw8/sphere_emission.png"))
+    assert sc.desc.n_light_tris == 0 and sc.desc.n_tris == 970
+    acc = _render(renderer, sc)
+    port = ou.port_render(sc, 1, want_counters=True)
+    assert port["accum"].mean() > 0
+    ok, got = _mean_close(acc, port["accum"], 16, 0.99, rel=5e-2)
+    assert ok, got
+    assert abs(int(renderer.stats()["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+    assert int(renderer.stats()["light_queries"]) == 0
+
+
 def test_errors_are_reported_not_thrown(renderer):
     r = rt.Renderer()
     try:
