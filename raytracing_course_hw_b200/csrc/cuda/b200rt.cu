@@ -99,6 +99,7 @@ struct b200rt_ctx {
     int blocks_extend[2] = {0, 0}, blocks_light[2] = {0, 0}, blocks_trace[2] = {0, 0};
     long long wf_wave_paths = 4ll << 20;
     int light_top_max = B200RT_LIGHT_TOP;  // boxes of the light-BVH cut used as the light-pdf pre-filter (0/1 = root box only)
+    int wf_flat_per_sm = 16;         // blocks per SM of the grid-stride kernels (generate, shade); B200RT_WF_FLAT_PER_SM
     bool wf_first_implicit = true;   // camera paths: only the direction is stored by generate (B200RT_WF_FIRST_IMPLICIT=0: whole record)
     bool wf_drop_dark = true;    // paths whose last bounce cannot reach an emitter end one bounce early (black background only)
     bool wf_direct = true;       // shade finishes bounces whose ray misses the light root box (no light-stage entry)
@@ -739,7 +740,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
     // a light-queue entry carries the light-cut mask above bit 26: waves of 2^26 slots or more (frames above 67 M
     // pixels) leave it out and the light stage tests the cut boxes itself
     const int pack_mask = per * s_w < (1ll << B200RT_WF_MASK_SHIFT) ? 1 : 0;
-    const int flat_blocks = ctx->num_sms * 16;
+    const int flat_blocks = ctx->num_sms * ctx->wf_flat_per_sm;
     ctx->pipe_stream[0] = ctx->stream;
     if (n_pipe > 1) {      // fork: the side streams start after everything already queued on the main stream
         CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
@@ -963,6 +964,7 @@ int b200rt_create(b200rt_ctx **out, const b200rt_options *opt) {
     if (const char *e = getenv("B200RT_WF_WAVE_PATHS")) ctx->wf_wave_paths = std::max(1ll, atoll(e));
     if (const char *e = getenv("B200RT_WF_FUSED")) ctx->wf_fused = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_DIRECT")) ctx->wf_direct = atoi(e) != 0;
+    if (const char *e = getenv("B200RT_WF_FLAT_PER_SM")) ctx->wf_flat_per_sm = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_WF_DROP_DARK")) ctx->wf_drop_dark = atoi(e) != 0;
     if (const char *e = getenv("B200RT_WF_FIRST_IMPLICIT")) ctx->wf_first_implicit = atoi(e) != 0;
     if (const char *e = getenv("B200RT_LIGHT_TOP")) ctx->light_top_max = std::max(0, atoi(e));
