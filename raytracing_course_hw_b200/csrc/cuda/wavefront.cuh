@@ -141,10 +141,6 @@ __device__ __forceinline__ void queue_push2(int *q_lo, int *q_hi, int *counter_l
 // Prefetch one 32-byte sector into L2 (the wave state streams through DRAM; whoever knows a path index early
 // turns the later demand load into an L2 hit).
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
-#ifndef B200RT_SHADE_PF
-#define B200RT_SHADE_PF 0        /* wf_shade: 1 = prefetch the state record of the item after next; 2 = also the hit triangle's records of the next item */
-#endif
 #ifndef B200RT_REFILL_PF
 #define B200RT_REFILL_PF 2048   /* wf_extend / wf_light: a lane that takes queue entry i prefetches the ray of entry i + this (0 = off) */
 #endif
@@ -371,27 +367,11 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 }
 
 // ---- shade --------------------------------------------------------------------------------------
-// B200RT_SHADE_PIPE=1 (measured, off): the first three hops of an item's dependency chain (queue entry -> path state
-// -> triangle + shading record) as a software pipeline through shared memory with cp.async, one to three items
-// ahead, no registers held across iterations.  On B200 it LOSES 20 % (shade 8.2 -> 9.9 ms at the 1080p probe): the
-// long-scoreboard stall per issue stays at 10.4 (ncu, profiles/r01_ncu_shade_pipe.json) because the hops that remain
-// -- material, then texels, mostly L2 misses -- dominate, while the 31 KB of staging per block shrink L1 and
-// push the 128-register build into spills.
-#ifndef B200RT_SHADE_PIPE
-#define B200RT_SHADE_PIPE 0
-#endif
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async16_ca(void *smem, const void *gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
+// Two latency-hiding variants of this kernel were built, measured slower and removed from the source (numbers in
+// DESIGN.md section 4): a cp.async software pipeline of the queue entry -> path state -> triangle / shading record
+// hops through shared memory (+20 % shade time: the material -> texel hops that remain dominate, the staging shrinks
+// L1 and pushes the 128-register build into spills), and prefetch.global.L2 of the next items' state records and hit
+// records (+8 % / +24 %).
 // LAST = the path's final bounce: only the emission of the hit is added (surface_emission), nothing continues.
 template <bool HW8, bool COUNT, bool LAST = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
@@ -400,12 +380,6 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                                                 const int pack_mask = 1) {
     __shared__ float lut_srgb[256];
     __shared__ float lut_lin[256];
-#if B200RT_SHADE_PIPE
-    __shared__ float4 s_state[5][128];            // hit, ray_o, ray_d, thr, rad of the item shaded next
-    __shared__ float4 s_rec[HW8 ? 9 : 6][128];    // its triangle record and shading record
-    __shared__ int s_p[3][128];                   // queue entries of the next three items
-    __shared__ uint32_t s_hw[2][128];             // hit words of the next two items
-#endif
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         lut_srgb[i] = lut_srgb_g[i];
         lut_lin[i] = 0.00392156862745098f * (float)i;
@@ -417,100 +391,13 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
     const bool has_lights = sc.n_light_tris > 0;
     ThreadCounters tc = {};
     unsigned answered = 0;      // light queries answered here by the pre-filter (they stay light queries in the stats)
-#if B200RT_SHADE_PIPE
-    const int tid = threadIdx.x;
-    const int stride = warps * 32;
-    const int i0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32 + lane;
-    // item j of this thread is queue position i0 + j * stride
-    auto valid = [&](int j) { return (long long)i0 + (long long)j * stride < (long long)n; };
-    auto issue_p = [&](int j) { if (valid(j)) cp_async4(&s_p[j % 3][tid], q_in + ((long long)i0 + (long long)j * stride)); };
-    auto issue_hw = [&](int j) { if (valid(j)) cp_async4(&s_hw[j & 1][tid], &wb.hit[s_p[j % 3][tid]].w); };
-    auto issue_data = [&](int j) {
-        if (!valid(j)) return;
-        const int pj = s_p[j % 3][tid];
-        const uint32_t bj = s_hw[j & 1][tid];
-        cp_async16(&s_state[0][tid], &wb.hit[pj]);
-        cp_async16(&s_state[1][tid], &wb.ray_o[pj]);
-        cp_async16(&s_state[2][tid], &wb.ray_d[pj]);
-        cp_async16(&s_state[3][tid], &wb.thr[pj]);
-        cp_async16(&s_state[4][tid], &wb.rad[pj]);
-        if (bj != B200RT_WF_MISS && bj != B200RT_WF_DEAD) {
-            const uint32_t tri = bj & 0x7FFFFFFFu;
-            const float4 *tq = reinterpret_cast<const float4 *>(sc.tris + tri);
-            const float4 *sq = reinterpret_cast<const float4 *>(sc.shade + tri);
-#pragma unroll
-            for (int c = 0; c < 3; c++) cp_async16_ca(&s_rec[c][tid], tq + c);
-#pragma unroll
-            for (int c = 0; c < (HW8 ? 6 : 3); c++) cp_async16_ca(&s_rec[3 + c][tid], sq + c);
-        }
-    };
-    issue_p(0); issue_p(1); issue_p(2);
-    cp_async_commit(); cp_async_wait_all();
-    issue_hw(0); issue_hw(1);
-    cp_async_commit(); cp_async_wait_all();
-    issue_data(0);
-    cp_async_commit();
-    for (int k = 0; __any_sync(B200RT_FULL, valid(k)); k++) {
-        const bool live = valid(k);
-#else
-#if B200RT_SHADE_PF
-    // Queue entries are read ahead of their use, so that the state record of a LATER item can be prefetched without
-    // waiting for its index (its demand loads then hit L2 instead of DRAM).  Level 2 goes one hop further: the hit
-    // word of the next item is read early and its triangle / shading records are prefetched at the end of the body.
-    const long long pf_stride = (long long)warps * 32;
-    const long long pf_i0 = (long long)(((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32 + lane);
-    auto q_at = [&](long long i) { return i < n ? __ldcs(q_in + i) : -1; };
-    int p_next = q_at(pf_i0);
-    int p_next2 = q_at(pf_i0 + pf_stride);
-#if B200RT_SHADE_PF >= 2
-    int p_next3 = q_at(pf_i0 + 2 * pf_stride);
-    if (p_next >= 0) { prefetch_l2(&wb.ray_o[p_next]); prefetch_l2(&wb.hit[p_next]); prefetch_l2(&wb.rad[p_next]); }
-#endif
-#endif
     for (int base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < n; base += warps * 32) {
         const bool live = base + lane < n;
-#endif
         bool cont = false, direct = false;
         int p = 0;
         uint32_t light_mask = 0u;     // pierced boxes of the light cut: rides in the top bits of the light-queue entry
-#if B200RT_SHADE_PIPE
-        cp_async_wait_all();
-        float4 h, ro, rd, th, ra;
-        SurfRec rec;
         if (live) {
-            p = s_p[k % 3][tid];
-            h = s_state[0][tid]; ro = s_state[1][tid]; rd = s_state[2][tid]; th = s_state[3][tid]; ra = s_state[4][tid];
-            rec.tv0 = s_rec[0][tid]; rec.te1 = s_rec[1][tid]; rec.te2 = s_rec[2][tid];
-            rec.s0 = s_rec[3][tid]; rec.s1 = s_rec[4][tid]; rec.s2 = s_rec[5][tid];
-            if (HW8) { rec.s3 = s_rec[6][tid]; rec.s4 = s_rec[7][tid]; rec.s5 = s_rec[8][tid]; }
-        }
-        // the slots are free again (the reads above are ordered before these copies): refill the pipeline
-        issue_p(k + 3);
-        issue_hw(k + 2);
-        issue_data(k + 1);
-        cp_async_commit();
-#endif
-#if B200RT_SHADE_PF && !B200RT_SHADE_PIPE
-        const int p_cur = p_next;
-        p_next = p_next2;
-#if B200RT_SHADE_PF >= 2
-        p_next2 = p_next3;
-        p_next3 = q_at((long long)base + lane + 3 * pf_stride);
-        if (p_next2 >= 0) { prefetch_l2(&wb.ray_o[p_next2]); prefetch_l2(&wb.hit[p_next2]); prefetch_l2(&wb.rad[p_next2]); }
-        // state of p_next was prefetched one iteration ago: its hit word is an L2 hit now, used at the end of the body
-        const uint32_t hw_next = p_next >= 0 ? __float_as_uint(wb.hit[p_next].w) : B200RT_WF_MISS;
-#else
-        p_next2 = q_at((long long)base + lane + 2 * pf_stride);
-        if (p_next >= 0) { prefetch_l2(&wb.ray_o[p_next]); prefetch_l2(&wb.hit[p_next]); prefetch_l2(&wb.rad[p_next]); }
-#endif
-#endif
-        if (live) {
-#if !B200RT_SHADE_PIPE
-#if B200RT_SHADE_PF
-            p = p_cur;
-#else
             p = __ldcs(q_in + base + lane);
-#endif
             const float4 h = ld_state(&wb.hit[p]);
             const float4 rd = ld_state(&wb.ray_d[p]);
             float4 ro, th, ra;
@@ -526,7 +413,6 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                 th = ld_state(&wb.thr[p]);
                 ra = ld_state(&wb.rad[p]);
             }
-#endif
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
             const uint32_t bits = __float_as_uint(h.w);
@@ -546,10 +432,8 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                 // key = pixel, counter = (global sample index, block of this bounce); both ride in spare state lanes
                 const uint4 rnd = philox4x32_10(__float_as_uint(ra.w), 16u * (uint32_t)(bounce + 1), __float_as_uint(ro.w), wp.seed);
                 BounceOut bo;
-#if !B200RT_SHADE_PIPE
                 SurfRec rec;
                 load_surf_rec<HW8>(sc, (int)(bits & 0x7FFFFFFFu), rec);
-#endif
                 cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, rec, (bits >> 31) != 0, L, T, rnd, tc, bo);
                 if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
                 if (cont && has_lights && q_direct) {
@@ -578,20 +462,9 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             }
             st_state(&wb.rad[p], make_float4(L.x, L.y, L.z, ra.w));
         }
-#if B200RT_SHADE_PF >= 2 && !B200RT_SHADE_PIPE
-        if (hw_next != B200RT_WF_MISS && hw_next != B200RT_WF_DEAD) {
-            const uint32_t tri = hw_next & 0x7FFFFFFFu;
-            const char *tq = reinterpret_cast<const char *>(sc.tris + tri), *sq = reinterpret_cast<const char *>(sc.shade + tri);
-            prefetch_l2(tq); prefetch_l2(tq + 32);
-            prefetch_l2(sq); prefetch_l2(sq + 32); prefetch_l2(sq + 64);
-        }
-#endif
         if (q_direct) queue_push2(q_out, q_direct, n_out, cont && !direct, cont && direct, (int)((uint32_t)p | (pack_mask ? light_mask << B200RT_WF_MASK_SHIFT : 0u)), p);   // n_direct == n_out + 1
         else queue_push(q_out, n_out, cont && !direct, p);
     }
-#if B200RT_SHADE_PIPE
-    cp_async_wait_all();
-#endif
     if (q_direct) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) answered += __shfl_down_sync(B200RT_FULL, answered, off);
