@@ -30,9 +30,6 @@ namespace b200rt {
 #ifndef B200RT_SHADE_MINB
 #define B200RT_SHADE_MINB 4
 #endif
-#ifndef B200RT_STACK_TNEAR
-#define B200RT_STACK_TNEAR 0     /* 1 = keep the entry distance with stacked nodes (prunes on pop; slower: doubles stack traffic) */
-#endif
 #ifndef B200RT_EXT_UNROLL
 #define B200RT_EXT_UNROLL 2      /* box steps per phase decision in wf_extend's inner phase */
 #endif
@@ -81,25 +78,13 @@ struct WaveParams {
     uint32_t seed;
 };
 
-// Wave state accessors.  B200RT_STATE_CS=1 makes them evict-first (.cs) so that the 0.9 GB of state
-// streamed per stage does not push the scene out of L2; measured: extend and light gain 1 %, shade
-// loses 15 % (it re-reads what the previous stage just wrote), so the default is plain caching.
-#ifndef B200RT_STATE_CS
-#define B200RT_STATE_CS 0
-#endif
+// Wave state accessors: plain caching.  Evict-first (.cs) accesses were measured: extend and light gain 1 %, shade
+// loses 15 % (it re-reads what the previous stage just wrote).
 __device__ __forceinline__ float4 ld_state(const float4 *p) {
-#if B200RT_STATE_CS
-    return __ldcs(p);
-#else
     return *p;
-#endif
 }
 __device__ __forceinline__ void st_state(float4 *p, const float4 v) {
-#if B200RT_STATE_CS
-    __stcs(p, v);
-#else
     *p = v;
-#endif
 }
 
 __device__ __forceinline__ bool slot_to_pixel(const WaveParams &wp, int slot, int &px, int &py, int &s_local) {
@@ -145,28 +130,13 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 #define B200RT_REFILL_PF 2048   /* wf_extend / wf_light: a lane that takes queue entry i prefetches the ray of entry i + this (0 = off) */
 #endif
 
-// Traversal stack of the persistent kernels.  ncu on wf_extend: the per-thread local-memory stack made 46 % of the
-// L1 requests and its write-through stores 20 % of the L2 sectors.  With B200RT_SMEM_STACK = N > 0 the first N
-// entries of every thread live in shared memory ([entry][thread]: conflict-free), deeper ones in local memory.
-#ifndef B200RT_SMEM_STACK
-#define B200RT_SMEM_STACK 0
-#endif
+// Traversal stack of the persistent kernels: per-thread local memory.  ncu on wf_extend: it makes 46 % of the L1
+// requests and its write-through stores 20 % of the L2 sectors -- yet keeping the first 8-32 entries in shared memory
+// was 7 % SLOWER (profiles/r01_sweep_smem_stack.log), as was storing the entry distance for pruning on pop.
 struct TravStack {
     uint32_t deep[B200RT_STACK];
-#if B200RT_SMEM_STACK
-    uint32_t *sh;      // &smem[threadIdx.x]
-    __device__ __forceinline__ void push(int &sp, uint32_t v) {
-        if (sp < B200RT_SMEM_STACK) sh[sp * 128] = v; else deep[sp - B200RT_SMEM_STACK] = v;
-        sp++;
-    }
-    __device__ __forceinline__ uint32_t pop(int &sp) {
-        --sp;
-        return sp < B200RT_SMEM_STACK ? sh[sp * 128] : deep[sp - B200RT_SMEM_STACK];
-    }
-#else
     __device__ __forceinline__ void push(int &sp, uint32_t v) { deep[sp++] = v; }
     __device__ __forceinline__ uint32_t pop(int &sp) { return deep[--sp]; }
-#endif
 };
 
 // full = 0: only the ray direction is stored -- the first extend / shade of the wave (`first`) know the rest of a
@@ -228,15 +198,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                                                  const float cam_x = 0.f, const float cam_y = 0.f, const float cam_z = 0.f) {
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
-#if B200RT_STACK_TNEAR
-    uint2 stack[B200RT_STACK];
-#else
     TravStack stack;
-#if B200RT_SMEM_STACK
-    __shared__ uint32_t s_stack[B200RT_SMEM_STACK * 128];
-    stack.sh = s_stack + threadIdx.x;
-#endif
-#endif
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
@@ -295,14 +257,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             // end of a subtree: next stacked node, or the ray is finished
             auto do_pop = [&]() {
                 bool got = false;
-#if B200RT_STACK_TNEAR
-                while (sp > 0) {
-                    const uint2 e = stack[--sp];
-                    if (__uint_as_float(e.y) <= tbest) { cur = e.x; got = true; break; }
-                }
-#else
                 if (sp > 0) { cur = stack.pop(sp); got = true; }
-#endif
                 if (!got) {
                     const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
                     st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
@@ -335,11 +290,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                         if (hl && hr) {
                             const bool left_first = tl <= tr;
                             // no bound check: b200rt_upload_scene rejects trees deeper than B200RT_STACK
-#if B200RT_STACK_TNEAR
-                            stack[sp++] = make_uint2(left_first ? mr : ml, __float_as_uint(left_first ? tr : tl));
-#else
                             stack.push(sp, left_first ? mr : ml);
-#endif
                             cur = left_first ? ml : mr;
                         } else if (hl) cur = ml;
                         else if (hr) cur = mr;
@@ -481,10 +432,6 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
     const int n = *n_in;
     const int lane = threadIdx.x & 31;
     TravStack stack;
-#if B200RT_SMEM_STACK
-    __shared__ uint32_t s_stack[B200RT_SMEM_STACK * 128];
-    stack.sh = s_stack + threadIdx.x;
-#endif
     int sp = 0;
     bool active = false, exhausted = false;
     int p = 0;
