@@ -338,6 +338,15 @@ static inline bool hit_aabb(const b200rt_bvh_node &nd, const Ray &ray, float &t,
 
 struct Counters { uint64_t rays = 0, node_tests = 0, tri_tests = 0, light_queries = 0, light_node_tests = 0, light_tri_tests = 0; };
 
+// Descriptions WITHOUT trees (the product's default load: b200rt_host_load_gltf skips the reference's SAH build).
+// render_mc then traverses private trees over permuted COPIES of the triangles (closest hits and light-pdf sums do
+// not depend on the tree) while FiguresMix::sample keeps picking from the description's own light order:
+// g_light_sample points at it for the duration of a render (test infrastructure, one render at a time).
+static const b200rt_triangle *g_light_sample = nullptr;
+static inline const b200rt_triangle &light_sample_tri(const b200rt_scene_desc &s, int which) {
+    return (g_light_sample ? g_light_sample : s.light_tris)[which];
+}
+
 template <class Rng>
 struct Gltf {
     const b200rt_scene_desc &s;
@@ -515,7 +524,7 @@ struct Gltf {
     }
     V light_sample(V x) {
         int which = rng.u() * (size_t)s.n_light_tris;
-        const b200rt_triangle &f = s.light_tris[which];
+        const b200rt_triangle &f = light_sample_tri(s, which);
         V a(f.p[2]); V b = V(f.p[0]) - a; V c = V(f.p[1]) - a;
         float u = rng.u();
         float v = rng.u();
@@ -697,7 +706,7 @@ struct Hw6 {
     // FiguresMix::sample -> TriangleLight::sample (distributions.h:127-141, 222-231)
     V light_sample(V x) {
         int which = rng.u() * (size_t)s.n_light_tris;
-        const b200rt_triangle &f = s.light_tris[which];
+        const b200rt_triangle &f = light_sample_tri(s, which);
         V a(f.p[2]); V b = V(f.p[0]) - a; V c = V(f.p[1]) - a;
         float u = rng.u();
         float v = rng.u();
@@ -1103,8 +1112,52 @@ struct Hw4Adapter : mc::Hw4<Rng> {
     Hw4Adapter(const b200rt_scene_desc &s, Rng &r, mc::Counters *) : mc::Hw4<Rng>(s, r) {}
 };
 
-void render_mc(const b200rt_scene_desc &s, int rng_kind, uint32_t seed, int b, int e, float *accum, uint8_t *rgb,
+// Median-split tree in the reference's node format (parents before children, leaves of <= 4 triangles) over
+// tris[first, last), permuting them in place.  Only for descriptions that carry no tree of their own.
+static uint32_t private_tree(std::vector<b200rt_triangle> &tris, std::vector<b200rt_bvh_node> &nodes, uint32_t first, uint32_t last) {
+    b200rt_bvh_node nd{};
+    nd.first = first; nd.last = last;
+    float cmn[3] = {INFINITY, INFINITY, INFINITY}, cmx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int a = 0; a < 3; a++) { nd.aabb_min[a] = INFINITY; nd.aabb_max[a] = -INFINITY; }
+    auto centroid = [](const b200rt_triangle &t, int a) { return t.p[0][a] + t.p[1][a] + t.p[2][a]; };
+    for (uint32_t i = first; i < last; i++)
+        for (int a = 0; a < 3; a++) {
+            for (int v = 0; v < 3; v++) { nd.aabb_min[a] = std::min(nd.aabb_min[a], tris[i].p[v][a]); nd.aabb_max[a] = std::max(nd.aabb_max[a], tris[i].p[v][a]); }
+            cmn[a] = std::min(cmn[a], centroid(tris[i], a)); cmx[a] = std::max(cmx[a], centroid(tris[i], a));
+        }
+    const uint32_t pos = (uint32_t)nodes.size();
+    nodes.push_back(nd);
+    if (last - first <= 4) return pos;
+    int axis = 0;
+    for (int a = 1; a < 3; a++) if (cmx[a] - cmn[a] > cmx[axis] - cmn[axis]) axis = a;
+    const uint32_t mid = first + (last - first) / 2;
+    std::nth_element(tris.begin() + first, tris.begin() + mid, tris.begin() + last,
+                     [&](const b200rt_triangle &l, const b200rt_triangle &r) { return centroid(l, axis) < centroid(r, axis); });
+    const uint32_t l = private_tree(tris, nodes, first, mid);
+    const uint32_t r = private_tree(tris, nodes, mid, last);
+    nodes[pos].left = l; nodes[pos].right = r;
+    return pos;
+}
+
+void render_mc(const b200rt_scene_desc &s_in, int rng_kind, uint32_t seed, int b, int e, float *accum, uint8_t *rgb,
                uint64_t *counters) {
+    b200rt_scene_desc s = s_in;
+    std::vector<b200rt_triangle> own_tris, own_ltris;
+    std::vector<b200rt_bvh_node> own_nodes, own_lnodes;
+    mc::g_light_sample = nullptr;
+    if (s.mode >= B200RT_MODE_HW6) {
+        if (s.n_tris > 0 && !s.nodes) {
+            own_tris.assign(s.tris, s.tris + s.n_tris);
+            s.root = (int32_t)private_tree(own_tris, own_nodes, 0, (uint32_t)s.n_tris);
+            s.tris = own_tris.data(); s.nodes = own_nodes.data(); s.n_nodes = (int32_t)own_nodes.size();
+        }
+        if (s.n_light_tris > 0 && !s.light_nodes) {
+            own_ltris.assign(s.light_tris, s.light_tris + s.n_light_tris);
+            private_tree(own_ltris, own_lnodes, 0, (uint32_t)s.n_light_tris);      // root = node 0
+            mc::g_light_sample = s_in.light_tris;
+            s.light_tris = own_ltris.data(); s.light_nodes = own_lnodes.data(); s.n_light_nodes = (int32_t)own_lnodes.size();
+        }
+    }
     mc::Counters cnt;
     mc::Counters *cp = counters ? &cnt : nullptr;
     if (s.mode == B200RT_MODE_HW3 || s.mode == B200RT_MODE_HW4) {

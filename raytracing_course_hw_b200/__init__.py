@@ -93,6 +93,8 @@ def host_lib():
         L.b200rt_host_set_env_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
         L.b200rt_host_timings.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
         L.b200rt_host_write_ppm.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_host_write_png.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_host_write_pfm.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32]
         _host = L
     return _host
 
@@ -135,9 +137,9 @@ DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b20
                   "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end", "b200rt_replicate_scene",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
                   "b200rt_strerror", "b200rt_last_error", "b200rt_device_count"]
-HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_set_env_map", "b200rt_host_desc",
-                "b200rt_host_set_frame", "b200rt_host_free", "b200rt_host_write_ppm", "b200rt_host_timings",
-                "b200rt_host_strerror"]
+HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_load_gltf_ex", "b200rt_host_set_env_map",
+                "b200rt_host_desc", "b200rt_host_set_frame", "b200rt_host_free", "b200rt_host_write_ppm",
+                "b200rt_host_write_png", "b200rt_host_write_pfm", "b200rt_host_timings", "b200rt_host_strerror"]
 
 
 class Scene:
@@ -189,16 +191,21 @@ class Scene:
             pass
 
 
-def load_scene(path, width=None, height=None, samples=None, mode=0, env_map=None):
+HOST_FLAG_REFERENCE_BVH = 1
+
+
+def load_scene(path, width=None, height=None, samples=None, mode=0, env_map=None, reference_bvh=False):
     """sceneio::loadScene: text scenes take everything from the file; glTF scenes take
-    width/height/samples from the caller (argv in the reference, hw8/src/main.cpp:9-11)."""
+    width/height/samples from the caller (argv in the reference, hw8/src/main.cpp:9-11).
+    reference_bvh: glTF only -- also run the reference's SAH build (triangles in its order + both trees); the
+    default description carries no trees, b200rt_upload_scene builds its own."""
     L = host_lib()
     h = ctypes.c_void_p()
     p = os.fsencode(path)
     if str(path).lower().endswith((".gltf",)):
         if not (width and height and samples):
             raise ValueError("glTF scenes need width, height and samples")
-        rc = L.b200rt_host_load_gltf(p, mode, width, height, samples, ctypes.byref(h))
+        rc = L.b200rt_host_load_gltf_ex(p, mode, width, height, samples, HOST_FLAG_REFERENCE_BVH if reference_bvh else 0, ctypes.byref(h))
     else:
         rc = L.b200rt_host_load_text(p, mode, ctypes.byref(h))
     if rc:
@@ -324,6 +331,20 @@ class Renderer:
 def write_ppm(path, rgb):
     rgb = np.ascontiguousarray(rgb, np.uint8)
     rc = host_lib().b200rt_host_write_ppm(os.fsencode(path), rgb.shape[1], rgb.shape[0], rgb.ctypes.data_as(ctypes.c_void_p))
+    if rc:
+        raise B200rtError(rc, host_lib().b200rt_host_strerror(rc).decode())
+
+
+def write_png(path, rgb):
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    rc = host_lib().b200rt_host_write_png(os.fsencode(path), rgb.shape[1], rgb.shape[0], rgb.ctypes.data_as(ctypes.c_void_p))
+    if rc:
+        raise B200rtError(rc, host_lib().b200rt_host_strerror(rc).decode())
+
+
+def write_pfm(path, accum_sum, total_spp):
+    a = np.ascontiguousarray(accum_sum, np.float32)
+    rc = host_lib().b200rt_host_write_pfm(os.fsencode(path), a.shape[1], a.shape[0], a.ctypes.data_as(ctypes.c_void_p), total_spp)
     if rc:
         raise B200rtError(rc, host_lib().b200rt_host_strerror(rc).decode())
 

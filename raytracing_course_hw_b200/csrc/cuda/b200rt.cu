@@ -435,13 +435,20 @@ void light_top_cut(const b200rt_bvh_node *nodes, int n_nodes, int n_light_tris, 
     }
 }
 
-int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s, bool trees_absent = false) {
+int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     if (s->n_tris < 0 || s->n_tris >= (1 << 27)) return fail(ctx, B200RT_ERR_INVALID, "triangle count out of range");
     if (s->n_tris > 0 && (!s->tris || !s->materials)) return fail(ctx, B200RT_ERR_INVALID, "missing triangle/material arrays");
     if (s->n_light_tris < 0 || s->n_materials < 0) return fail(ctx, B200RT_ERR_INVALID, "negative array size");
-    // trees_absent: the caller has triangles but no trees over them (hw5); mode hw6 then rebuilds both anyway
-    if (!trees_absent && !validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
-    if (!trees_absent && s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
+    if (s->n_light_tris > 0 && !s->light_tris) return fail(ctx, B200RT_ERR_INVALID, "missing light triangle array");
+    // The description's trees are optional (b200rt_host_load_gltf delivers none): by default the library builds the
+    // trees it traverses itself.  They are validated only when they are actually used (B200RT_FLAG_REFERENCE_BVH;
+    // hw6 always rebuilds, its reference tree is a SAH split of an arbitrary order).
+    const bool use_ref_trees = (ctx->flags & B200RT_FLAG_REFERENCE_BVH) && s->mode != B200RT_MODE_HW6;
+    if (use_ref_trees) {
+        if (s->n_tris > 0 && !s->nodes) return fail(ctx, B200RT_ERR_INVALID, "B200RT_FLAG_REFERENCE_BVH needs the description's scene BVH");
+        if (!validate_tree(s->nodes, s->n_nodes, s->root, s->n_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed scene BVH");
+        if (s->n_light_tris > 0 && !validate_tree(s->light_nodes, s->n_light_nodes, 0, s->n_light_tris)) return fail(ctx, B200RT_ERR_INVALID, "malformed light BVH");
+    }
 
     DGltfScene g{};
     g.hw8 = s->mode == B200RT_MODE_HW8;
@@ -461,7 +468,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s, bool trees_absent =
     RebuiltBvh &own = ctx->own_bvh;                        // buffers reused by the next upload
     std::vector<b200rt_triangle> &own_tris = ctx->own_tris;
     b200rt_scene_desc local;
-    const bool rebuild = s->mode == B200RT_MODE_HW6 || !(ctx->flags & B200RT_FLAG_REFERENCE_BVH);
+    const bool rebuild = !use_ref_trees;
     if (rebuild && s->n_tris > 0) {
         rebuild_bvh_binned_sah(s->tris, s->n_tris, own);
         own_tris.resize((size_t)s->n_tris);
@@ -907,7 +914,7 @@ int upload_hw5(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
         t.light_nodes = nullptr; t.n_light_nodes = 0;
         t.materials = mats.data(); t.n_materials = (int32_t)mats.size();
         t.images = nullptr; t.n_images = 0; t.env_map = nullptr;
-        const int rc = upload_gltf(ctx, &t, true);
+        const int rc = upload_gltf(ctx, &t);
         if (rc) return rc;
     }
     if (s->n_light_prims > ctx->hw5_light_cap) {

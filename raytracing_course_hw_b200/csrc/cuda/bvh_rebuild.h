@@ -28,6 +28,7 @@
 #include <vector>
 #include <xmmintrin.h>      // host-side SSE for the binning loop (x86-64 hosts only, like the rest of the build)
 #include "b200rt.h"
+#include "../common/host_pool.h"
 
 namespace b200rt {
 
@@ -36,83 +37,6 @@ struct RebuiltBvh {
     std::vector<uint32_t> order;     // order[i] = index of the input triangle stored at position i
     // scratch kept between builds (a context re-uploading a scene does not page-fault fresh memory again)
     std::vector<float> scratch_box, scratch_cen;
-};
-
-// Host threads one context may use for record building and the BVH rebuild: min(16, cores), or
-// B200RT_HOST_THREADS (one process per GPU on a shared host: cores / GPUs avoids oversubscription).
-inline unsigned host_threads() {
-    unsigned n = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
-    if (const char *e = getenv("B200RT_HOST_THREADS")) n = (unsigned)std::max(1, std::min(64, atoi(e)));
-    return n;
-}
-
-// Persistent host workers for the upload path (BVH rebuild, record building).  A scene upload runs ~20 short
-// parallel sections; spawning 16 std::threads for each cost more than the work inside (measured on the GPU box's
-// virtualised cores: ~1 ms per round).  run(n, fn) executes fn(0) .. fn(n-1) on the pool plus the calling thread
-// and returns when all are done; one job at a time (contexts driven from different host threads take turns).
-class HostPool {
-public:
-    static HostPool &get() { static HostPool p; return p; }
-    void run(unsigned n, const std::function<void(unsigned)> &fn) {
-        if (n <= 1) { if (n) fn(0); return; }
-        std::lock_guard<std::mutex> serial(run_mu_);
-        {
-            std::lock_guard<std::mutex> lk(mu_);
-            while (workers_.size() + 1 < n) workers_.emplace_back([this] { loop(); });
-            job_ = &fn; n_tasks_ = n; next_ = 0; done_ = 0; gen_++;
-        }
-        cv_work_.notify_all();
-        work();
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_done_.wait(lk, [this] { return done_ == n_tasks_; });
-        job_ = nullptr;
-    }
-    ~HostPool() {
-        { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
-        cv_work_.notify_all();
-        for (auto &t : workers_) t.join();
-    }
-private:
-    void work() {
-        for (;;) {
-            unsigned t;
-            const std::function<void(unsigned)> *job;
-            {
-                std::lock_guard<std::mutex> lk(mu_);
-                if (!job_ || next_ >= n_tasks_) return;
-                t = next_++; job = job_;
-            }
-            (*job)(t);
-            std::lock_guard<std::mutex> lk(mu_);
-            if (++done_ == n_tasks_) cv_done_.notify_all();
-        }
-    }
-    void loop() {
-        uint64_t seen = 0;
-        for (;;) {
-            // an upload issues its parallel sections back to back: spin briefly before going to sleep, a futex wake
-            // of a parked (virtual) core costs more than most sections
-            for (int spin = 0; spin < 20000 && gen_.load(std::memory_order_acquire) == seen && !stop_; spin++) {
-#if defined(__x86_64__) || defined(__i386__)
-                __builtin_ia32_pause();
-#endif
-            }
-            {
-                std::unique_lock<std::mutex> lk(mu_);
-                cv_work_.wait(lk, [&] { return stop_ || gen_.load() != seen; });
-                if (stop_) return;
-                seen = gen_.load();
-            }
-            work();
-        }
-    }
-    std::vector<std::thread> workers_;
-    std::mutex mu_, run_mu_;
-    std::condition_variable cv_work_, cv_done_;
-    const std::function<void(unsigned)> *job_ = nullptr;
-    unsigned n_tasks_ = 0, next_ = 0, done_ = 0;
-    std::atomic<uint64_t> gen_{0};
-    std::atomic<bool> stop_{false};
 };
 
 namespace bvh_detail {
@@ -178,6 +102,7 @@ struct Ctx {
     int sweep_max;         // <= SWEEP_MAX
     float trav;
     unsigned threads;
+    int sah_depth;         // nodes at this depth or below are split at the median (bounds the tree depth, see split_node)
 };
 
 inline int bin_of(float c, float lo, float k) { return std::min(BINS - 1, (int)((c - lo) * k)); }
@@ -215,7 +140,11 @@ inline void bin_range(const Ctx &c, uint32_t first, uint32_t last, const B3 &cb,
 // Chooses the split of one node and partitions order[first, last).  Returns mid, or 0 for "make a leaf".
 // `in` holds the node's bounds (from its parent's bins); `kids` receives the children's.
 // `parallel` spreads the binning over the host cores (used for the large nodes at the top).
-inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds &in, NodeBounds kids[2], bool parallel) {
+// `depth` (root = 0): SAH splits can be arbitrarily lopsided, and the traversal kernels keep a fixed stack of
+// B200RT_STACK entries without bound checks.  From depth Ctx::sah_depth on, a node is therefore cut at the median of
+// its centroids on their widest axis: at most ceil(log2 N) more levels, so any triangle soup uploads (the
+// reference's recursive traversal accepts any depth, hw8/src/include/bvh.h:111-142).
+inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds &in, NodeBounds kids[2], bool parallel, int depth) {
     const uint32_t first = node.first, last = node.last, count = last - first;
     const B3 &nb = in.nb, &cb = in.cb;
     const unsigned nt = parallel ? c.threads : 1;
@@ -234,6 +163,17 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
         return m;
     };
     if (!any_axis) return count <= 15 ? 0 : halves(first + count / 2);      // identical centroids
+    if (depth >= c.sah_depth) {
+        if (count <= (uint32_t)c.leaf_max) return 0;
+        int axis = 0;
+        for (int a = 1; a < 3; a++) if (cb.mx[a] - cb.mn[a] > cb.mx[axis] - cb.mn[axis]) axis = a;
+        const uint32_t m = first + count / 2;
+        std::nth_element(c.order + first, c.order + m, c.order + last, [&](uint32_t x, uint32_t y) {
+            const float kx = c.cen[(size_t)x * 3 + axis], ky = c.cen[(size_t)y * 3 + axis];
+            return kx < ky || (kx == ky && x < y);
+        });
+        return halves(m);
+    }
     if (count <= (uint32_t)c.sweep_max) {
         uint32_t idx[3][SWEEP_MAX];
         float best_cost = FLT_MAX;
@@ -325,16 +265,16 @@ inline uint32_t split_node(const Ctx &c, b200rt_bvh_node &node, const NodeBounds
 // Serial build of the subtree under nodes[root_id] (first/last set, bounds in `root`).  Descendants are
 // written to nodes[slot, slot + 2 * count): the caller reserves that range, so workers never touch the
 // same elements; unused slots stay zero (empty leaves nobody points to).
-inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id, uint32_t slot, const NodeBounds &root) {
-    struct Item { uint32_t id; NodeBounds b; };
+inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id, uint32_t slot, const NodeBounds &root, int root_depth) {
+    struct Item { uint32_t id; NodeBounds b; int depth; };
     std::vector<Item> todo;
-    todo.push_back({root_id, root});
+    todo.push_back({root_id, root, root_depth});
     while (!todo.empty()) {
         const Item it = todo.back();
         todo.pop_back();
         const uint32_t first = nodes[it.id].first, last = nodes[it.id].last;
         NodeBounds kids[2];
-        const uint32_t mid = split_node(c, nodes[it.id], it.b, kids, false);
+        const uint32_t mid = split_node(c, nodes[it.id], it.b, kids, false, it.depth);
         if (!mid) continue;
         const uint32_t l = slot;
         slot += 2;
@@ -343,8 +283,8 @@ inline void build_subtree(const Ctx &c, b200rt_bvh_node *nodes, uint32_t root_id
         nodes[l + 1] = b200rt_bvh_node{};
         nodes[l + 1].first = mid; nodes[l + 1].last = last;
         nodes[it.id].left = l; nodes[it.id].right = l + 1;
-        todo.push_back({l + 1, kids[1]});
-        todo.push_back({l, kids[0]});
+        todo.push_back({l + 1, kids[1], it.depth + 1});
+        todo.push_back({l, kids[0], it.depth + 1});
     }
 }
 
@@ -357,6 +297,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
     Ctx c{};
     c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
     c.sweep_max = 12;
+    c.sah_depth = 32;      // + ceil(log2(2^27 / leaf)) median levels < B200RT_STACK (64)
     if (const char *e = getenv("B200RT_REBUILD_SWEEP")) c.sweep_max = std::max(0, std::min(SWEEP_MAX, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_LEAF_LIGHT" : "B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_TRAV_LIGHT" : "B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
@@ -427,19 +368,21 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
         nodes.resize(used);
     };
     lap("root bounds");
-    if (c.threads == 1) { build_subtree(c, nodes.data(), 0, top_cap, rb); shrink(); return; }
+    if (c.threads == 1) { build_subtree(c, nodes.data(), 0, top_cap, rb, 0); shrink(); return; }
 
     // phase A: the few very large nodes at the top, one by one, with the binning spread over the cores
     const uint32_t big = 65536, task_size = (uint32_t)std::max(1024, n / (int)(c.threads * 16));
     // the bounds of the nodes created in phases A and B live in `nbs` (same index as `nodes`)
     uint32_t cursor = 1;
     std::vector<NodeBounds> nbs((size_t)top_cap, rb);
+    std::vector<int> ndepth((size_t)top_cap, 0);
     std::vector<uint32_t> queue(1, 0u);
     auto add_children = [&](uint32_t id, uint32_t first, uint32_t mid, uint32_t last, const NodeBounds kids[2]) {
         const uint32_t l = cursor;
         cursor += 2;
         nodes[l].first = first; nodes[l].last = mid; nbs[l] = kids[0];
         nodes[l + 1].first = mid; nodes[l + 1].last = last; nbs[l + 1] = kids[1];
+        ndepth[l] = ndepth[l + 1] = ndepth[id] + 1;
         nodes[id].left = l; nodes[id].right = l + 1;
         queue.push_back(l + 1);
         queue.push_back(l);
@@ -452,7 +395,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
             queue.erase(queue.begin() + (long)q);
             const uint32_t first = nodes[id].first, last = nodes[id].last;
             NodeBounds kids[2];
-            const uint32_t mid = split_node(c, nodes[id], nbs[id], kids, true);
+            const uint32_t mid = split_node(c, nodes[id], nbs[id], kids, true, ndepth[id]);
             if (mid) add_children(id, first, mid, last, kids);
             again = true;
             break;
@@ -470,6 +413,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
                 for (;;) {
                     uint32_t id, slot = 0;
                     NodeBounds mine;
+                    int my_depth;
                     bool whole;
                     {
                         std::unique_lock<std::mutex> lk(mu);
@@ -482,6 +426,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
                         id = queue.back();
                         queue.pop_back();
                         mine = nbs[id];
+                        my_depth = ndepth[id];
                         const uint32_t count = nodes[id].last - nodes[id].first;
                         whole = count <= task_size || cursor + 2 > top_cap;     // top slots exhausted: finish serially
                         if (whole) { tail -= 2 * count; slot = tail; }
@@ -490,13 +435,13 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
                     const uint32_t first = nodes[id].first, last = nodes[id].last;
                     if (whole) {
                         memset((void *)(nodes.data() + slot), 0, (size_t)2 * (last - first) * sizeof(b200rt_bvh_node));
-                        build_subtree(c, nodes.data(), id, slot, mine);
+                        build_subtree(c, nodes.data(), id, slot, mine, my_depth);
                         std::lock_guard<std::mutex> lk(mu);
                         inflight--;
                     } else {
                         b200rt_bvh_node nd = nodes[id];
                         NodeBounds kids[2];
-                        const uint32_t mid = split_node(c, nd, mine, kids, false);
+                        const uint32_t mid = split_node(c, nd, mine, kids, false, my_depth);
                         std::lock_guard<std::mutex> lk(mu);
                         for (int a = 0; a < 3; a++) { nodes[id].aabb_min[a] = nd.aabb_min[a]; nodes[id].aabb_max[a] = nd.aabb_max[a]; }
                         if (mid) add_children(id, first, mid, last, kids);

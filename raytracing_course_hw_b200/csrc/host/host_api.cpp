@@ -28,6 +28,7 @@ double now_ms() {
 }
 
 bool decode_png_rgb8(const std::vector<uint8_t> &file, int32_t &w, int32_t &h, std::vector<uint8_t> &rgb);
+void encode_png_rgb8(int32_t w, int32_t h, const uint8_t *rgb, std::vector<uint8_t> &out);
 
 int load_image_rgb8(const std::string &path, int32_t &w, int32_t &h, std::vector<uint8_t> &rgb) {
     std::ifstream f(path, std::ios::binary);
@@ -91,6 +92,16 @@ void build_triangle_accel(b200rt_host_scene &s) {
     s.light_nodes.clear();
     if (n > 0) build_over(s.light_tris, (uint32_t)n, s.light_nodes, nullptr, hw6_key);
     // n == 0: the reference still builds a one-node BVH over nothing but never uses it.
+}
+
+void collect_lights(b200rt_host_scene &s) {
+    s.nodes.clear(); s.light_nodes.clear();
+    s.desc.root = 0;
+    s.light_tris.clear();
+    for (const b200rt_triangle &t : s.tris) {
+        const float *e = s.materials[t.material].emission;      // emissiveFactor only; textures ignored
+        if (!(e[0] == 0 && e[1] == 0 && e[2] == 0)) s.light_tris.push_back(t);
+    }
 }
 
 // ---- hw5: figures of mixed type in the BVH -------------------------------------------------------------
@@ -191,23 +202,32 @@ int b200rt_host_load_text(const char *path, int32_t mode, b200rt_host_scene **ou
     return B200RT_OK;
 }
 
-int b200rt_host_load_gltf(const char *path, int32_t mode, int32_t width, int32_t height, int32_t samples, b200rt_host_scene **out) {
+int b200rt_host_load_gltf_ex(const char *path, int32_t mode, int32_t width, int32_t height, int32_t samples, int32_t flags,
+                             b200rt_host_scene **out) {
     if (!path || !out || width <= 0 || height <= 0 || samples <= 0) return B200RT_ERR_INVALID;
+    *out = nullptr;
     auto *s = new (std::nothrow) b200rt_host_scene();
     if (!s) return B200RT_ERR_INVALID;
     int rc = B200RT_ERR_INVALID;
-    try { rc = load_gltf_scene(path, mode, *s); } catch (...) { rc = B200RT_HOST_ERR_PARSE; }
+    try { rc = load_gltf_scene(path, mode, flags, *s); }
+    catch (const std::bad_alloc &) { rc = B200RT_HOST_ERR_IO; }
+    catch (...) { rc = B200RT_HOST_ERR_PARSE; }
     if (rc) { delete s; return rc; }
     s->desc.width = width; s->desc.height = height; s->desc.samples = samples;
     *out = s;
     return B200RT_OK;
 }
 
+int b200rt_host_load_gltf(const char *path, int32_t mode, int32_t width, int32_t height, int32_t samples, b200rt_host_scene **out) {
+    return b200rt_host_load_gltf_ex(path, mode, width, height, samples, 0, out);
+}
+
 int b200rt_host_set_env_map(b200rt_host_scene *s, const char *image_path) {
     if (!s || !image_path) return B200RT_ERR_INVALID;
     int32_t w, h;
     std::vector<uint8_t> rgb;
-    int rc = load_image_rgb8(image_path, w, h, rgb);
+    int rc;
+    try { rc = load_image_rgb8(image_path, w, h, rgb); } catch (...) { rc = B200RT_HOST_ERR_IMAGE; }
     if (rc) return rc;
     s->env_data = std::move(rgb);
     s->env.width = w; s->env.height = h;
@@ -237,6 +257,39 @@ int b200rt_host_write_ppm(const char *path, int32_t width, int32_t height, const
     size_t w = fwrite(rgb, 1, n, f);
     fclose(f);
     return w == n ? B200RT_OK : B200RT_HOST_ERR_IO;
+}
+
+// Lossless RGB8 PNG of the same frame (the reference's tree vendors stb_image_write for this and never calls it).
+int b200rt_host_write_png(const char *path, int32_t width, int32_t height, const uint8_t *rgb) {
+    if (!path || !rgb || width <= 0 || height <= 0) return B200RT_ERR_INVALID;
+    try {
+        std::vector<uint8_t> png;
+        encode_png_rgb8(width, height, rgb, png);
+        FILE *f = fopen(path, "wb");
+        if (!f) return B200RT_HOST_ERR_IO;
+        const size_t w = fwrite(png.data(), 1, png.size(), f);
+        fclose(f);
+        return w == png.size() ? B200RT_OK : B200RT_HOST_ERR_IO;
+    } catch (...) { return B200RT_HOST_ERR_IO; }
+}
+
+// Float radiance (mean over `total_spp` samples of the accumulated SUM buffer, before tonemapping) as a binary PFM:
+// "PF\n<W> <H>\n-1.0\n" + little-endian float RGB, BOTTOM row first (the format's convention).
+int b200rt_host_write_pfm(const char *path, int32_t width, int32_t height, const float *rgb_sum, int32_t total_spp) {
+    if (!path || !rgb_sum || width <= 0 || height <= 0 || total_spp <= 0) return B200RT_ERR_INVALID;
+    FILE *f = fopen(path, "wb");
+    if (!f) return B200RT_HOST_ERR_IO;
+    fprintf(f, "PF\n%d %d\n-1.0\n", width, height);
+    const float inv = (float)(1.0 / total_spp);
+    std::vector<float> row((size_t)width * 3);
+    bool ok = true;
+    for (int32_t y = height - 1; y >= 0 && ok; y--) {
+        const float *src = rgb_sum + (size_t)y * width * 3;
+        for (size_t i = 0; i < row.size(); i++) row[i] = inv * src[i];
+        ok = fwrite(row.data(), sizeof(float), row.size(), f) == row.size();
+    }
+    fclose(f);
+    return ok ? B200RT_OK : B200RT_HOST_ERR_IO;
 }
 
 int b200rt_host_timings(const b200rt_host_scene *s, double *parse_ms, double *bvh_ms) {

@@ -39,11 +39,13 @@ struct b200rt_host_scene {
 
 namespace b200rt_host {
 int load_text_scene(const char *path, int32_t mode, b200rt_host_scene &s);
-int load_gltf_scene(const char *path, int32_t mode, b200rt_host_scene &s);
+int load_gltf_scene(const char *path, int32_t mode, int32_t flags, b200rt_host_scene &s);
 // Decodes to tightly packed RGB8 (3 channels forced, like stbi_load(..., 3)).
 int load_image_rgb8(const std::string &path, int32_t &w, int32_t &h, std::vector<uint8_t> &rgb);
 // Builds Scene::bvh over s.tris (reorders them) and the FiguresMix light set + light BVH.
 void build_triangle_accel(b200rt_host_scene &s);
+// The product default: no trees; light set = the emissive triangles in file order (b200rt_upload_scene builds the trees).
+void collect_lights(b200rt_host_scene &s);
 // hw5: Scene::initBVH over the non-plane figures of s.prims (reorders them, planes last) and the FiguresMix
 // light set + light BVH (hw5/src/scene.cpp:18-23, hw5/src/include/distributions.h:172-199).
 void build_figure_accel(b200rt_host_scene &s);

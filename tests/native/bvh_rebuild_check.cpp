@@ -2,6 +2,7 @@
 // triangles, parallel path above) and verifies the tree invariants the flattener and the kernels rely on.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <random>
 #include <vector>
 #include "bvh_rebuild.h"
@@ -58,7 +59,36 @@ static int check(int n, unsigned seed) {
     return 0;
 }
 
+// A soup that drives SAH into maximally lopsided splits (sizes and positions in a geometric series: peeling off the
+// largest triangle is always the cheapest cut): without the depth cap of split_node the tree is a 4000-level comb.
+static int check_depth(int n) {
+    std::vector<b200rt_triangle> tris((size_t)n);
+    double x = 0, s = 1;
+    for (int i = 0; i < n; i++) {
+        b200rt_triangle &t = tris[(size_t)i];
+        memset(&t, 0, sizeof(t));
+        t.p[0][0] = (float)x; t.p[1][0] = (float)(x + s); t.p[2][0] = (float)x;
+        t.p[1][1] = (float)s; t.p[2][2] = (float)s;
+        x += 1.5 * s; s *= 0.98;
+    }
+    RebuiltBvh b;
+    rebuild_bvh_binned_sah(tris.data(), n, b);
+    struct It { uint32_t id; int d; };
+    std::vector<It> st(1, It{0u, 1});
+    int max_depth = 0;
+    while (!st.empty()) {
+        const It it = st.back();
+        st.pop_back();
+        max_depth = std::max(max_depth, it.d);
+        const b200rt_bvh_node &nd = b.nodes[it.id];
+        if (nd.left) { st.push_back({nd.left, it.d + 1}); st.push_back({nd.right, it.d + 1}); }
+    }
+    printf("comb n=%d depth=%d %s\n", n, max_depth, max_depth <= 60 ? "ok" : "TOO DEEP");
+    return max_depth <= 60 ? 0 : 12;
+}
+
 int main() {
+    if (int rc = check_depth(4000)) return rc;
     const int sizes[] = {1, 2, 17, 5000, 70000, 300000};
     for (int n : sizes) {
         const int rc = check(n, 1234u + (unsigned)n);

@@ -17,7 +17,7 @@ def test_bvh_rebuild_invariants(tmp_path):
                     os.path.join(ROOT, "tests", "native", "bvh_rebuild_check.cpp"), "-o", exe], check=True)
     r = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
     assert r.returncode == 0, r.stdout
-    assert r.stdout.count(" ok") == 6
+    assert r.stdout.count(" ok") == 7      # six soups + the depth-capped comb
 
 
 def test_host_pool_stress(tmp_path):

@@ -23,7 +23,7 @@ def _worker(rank, world, port, out_path):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    sc = rt.load_scene(os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), width=48, height=32, samples=6)
+    sc = ou.load_scene(os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), width=48, height=32, samples=6)
     b, e = sample_range(rank, world, sc.samples)
     part = ou.port_render(sc, 1, spp_begin=b, spp_end=e)["accum"]
     buf = torch.from_numpy(part.copy())
@@ -53,6 +53,6 @@ def test_two_rank_gloo_reduce_equals_single_range(tmp_path):
     port = 29500 + os.getpid() % 2000
     mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
     got = np.load(out)
-    sc = rt.load_scene(os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), width=48, height=32, samples=6)
+    sc = ou.load_scene(os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), width=48, height=32, samples=6)
     full = ou.port_render(sc, 1)["accum"]
     assert np.allclose(got, full, rtol=1e-5, atol=1e-6)

@@ -44,7 +44,7 @@ def _render(r, sc, b=0, e=None):
 # ---------------------------------------------------------------- deterministic configs
 @pytest.mark.parametrize("name,path", [("hw1_sample", "hw1/sample.txt"), ("hw2_sample", "hw2/sample.txt")])
 def test_deterministic_ids_and_pixels(renderer, name, path):
-    sc = rt.load_scene(os.path.join(S, path))
+    sc = ou.load_scene(os.path.join(S, path))
     acc = _render(renderer, sc)
     img = renderer.resolve(1)
     ids = renderer.primary_ids()
@@ -60,7 +60,7 @@ def test_deterministic_ids_and_pixels(renderer, name, path):
 
 def test_deterministic_upres_ids(renderer):
     """Synthetic up-res copy: 1920x1080 ids still bit-exact against the port."""
-    sc = rt.load_scene(os.path.join(S, "hw2/sample.txt"), width=960, height=540)
+    sc = ou.load_scene(os.path.join(S, "hw2/sample.txt"), width=960, height=540)
     _render(renderer, sc)
     assert np.array_equal(renderer.primary_ids(), ou.port_render(sc, 0)["ids"])
 
@@ -75,7 +75,7 @@ def _mean_close(gpu_sum, port_sum, spp, frac_needed, rel=2e-2):
 
 @pytest.mark.parametrize("k", [1, 3, 4])
 def test_hw4_matches_port_on_same_stream(renderer, k):
-    sc = rt.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16)
+    sc = ou.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16)
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1)
     ok, frac = _mean_close(acc, port["accum"], 16, 0.99)
@@ -87,7 +87,7 @@ def test_hw4_matches_port_on_same_stream(renderer, k):
 def test_hw3_matches_port_on_same_stream(renderer, k):
     """hw3 = the uniform-hemisphere integrator (hw3/src/scene.cpp:31-106); hw3 ships hw4's scenes, the mode is
     explicit (text scenes with SAMPLES are inferred as hw4)."""
-    sc = rt.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16, mode=rt.MODE_HW3)
+    sc = ou.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16, mode=rt.MODE_HW3)
     assert sc.mode == rt.MODE_HW3
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1)
@@ -95,14 +95,14 @@ def test_hw3_matches_port_on_same_stream(renderer, k):
     assert ok, frac
     assert abs(acc.mean() - port["accum"].mean()) <= 2e-3 * port["accum"].mean()
     # not the hw4 estimator: same scene, same stream, different image
-    sc4 = rt.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16)
+    sc4 = ou.load_scene(os.path.join(S, f"hw4/practice3_{k}.txt"), width=160, height=120, samples=16)
     assert not np.allclose(_render(renderer, sc4), acc)
 
 
 def test_hw5_matches_port_on_same_stream(renderer):
     """hw5: analytic figures scanned in constant memory + triangles through the library's own BVH (K7) against the
     port, which walks the reference's mixed-figure BVH: same Philox stream, same image up to float rounding."""
-    sc = rt.load_scene(os.path.join(S, "hw5/mixed.txt"), samples=16)
+    sc = ou.load_scene(os.path.join(S, "hw5/mixed.txt"), samples=16)
     assert sc.mode == rt.MODE_HW5
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
@@ -117,7 +117,7 @@ def test_hw5_matches_port_on_same_stream(renderer):
 def test_hw5_without_triangles_matches_port_on_same_stream(renderer):
     """hw5 rules on a scene with analytic figures only (planes, rotated box light, ellipsoids, box): the triangle side
     of K7 is empty, the mixed-figure BVH of the description holds boxes and ellipsoids."""
-    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16, mode=rt.MODE_HW5)
+    sc = ou.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16, mode=rt.MODE_HW5)
     assert sc.mode == rt.MODE_HW5 and sc.desc.n_light_prims == 1
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1)
@@ -127,7 +127,7 @@ def test_hw5_without_triangles_matches_port_on_same_stream(renderer):
 
 
 def test_hw4_box_light_matches_port_on_same_stream(renderer):
-    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16)
+    sc = ou.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), samples=16)
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1)
     ok, frac = _mean_close(acc, port["accum"], 16, 0.99)
@@ -137,7 +137,7 @@ def test_hw4_box_light_matches_port_on_same_stream(renderer):
 @pytest.mark.parametrize("path,frac", [("hw8/sphere_emissive.gltf", 0.99), ("hw7/practice7_1.gltf", 0.85),
                                        ("hw7/practice7_4.gltf", 0.90)])
 def test_gltf_matches_port_on_same_stream(renderer, path, frac):
-    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
     ok, got = _mean_close(acc, port["accum"], 16, frac, rel=5e-2)
@@ -159,7 +159,7 @@ def test_gltf_matches_port_on_same_stream(renderer, path, frac):
 def test_hw8_environment_map_matches_port_on_same_stream(renderer):
     """Misses sample the environment map (equirect lookup + sRGB decode on the device); with a non-black background
     the dark-ray rule must stay off: the ray count equals the port's in every scheduling."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=16,
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=16,
                        env_map=os.path.join(S, "hw8/sphere_emission.png"))
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
@@ -182,7 +182,7 @@ def test_hw8_environment_map_matches_port_on_same_stream(renderer):
 def test_ragged_frames_match_port(renderer, path, w, h):
     """Frames that are not multiples of the 8x4 pixel tile (partial tiles leave dead slots in a wave; the first queue
     is then compacted with atomics instead of being the identity), down to a single pixel."""
-    sc = rt.load_scene(os.path.join(S, path), width=w, height=h, samples=16)
+    sc = ou.load_scene(os.path.join(S, path), width=w, height=h, samples=16)
     acc = _render(renderer, sc)
     assert acc.shape == (h, w, 3)
     port = ou.port_render(sc, 1)
@@ -202,7 +202,7 @@ def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
     bounce early when its last ray pierces no emissive triangle (light stage: pdf sum == 0; shade: misses the emitters'
     boxes).  Those paths would have added exactly zero: the image is bit-identical with the rule off, the ray count
     with the rule off equals the port's, and fewer rays are traced with it on."""
-    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
     port = ou.port_render(sc, 1, want_counters=True)
     out = {}
     for drop in ("1", "0"):
@@ -219,7 +219,7 @@ def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
 def test_implicit_camera_state_is_the_stored_one(w, h, monkeypatch):
     """The first extend / shade of a wave derive a camera path's state from its slot (origin = camera, throughput 1,
     radiance 0, Philox key / counter) instead of reading what wf_generate would have stored: bit-identical image."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=w, height=h, samples=8)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=w, height=h, samples=8)
     out = {}
     for v in ("1", "0"):
         monkeypatch.setenv("B200RT_WF_FIRST_IMPLICIT", v)
@@ -236,7 +236,7 @@ def test_exported_scene_renders_the_same_image_in_another_context():
     torch = pytest.importorskip("torch")
     from raytracing_course_hw_b200 import dist as rtdist
     dev = torch.device("cuda", 0)
-    sc = rt.load_scene(_room(), width=160, height=96, samples=4)
+    sc = ou.load_scene(_room(), width=160, height=96, samples=4)
     a, b = rt.Renderer(), rt.Renderer()
     a.upload(sc)
     hdr, src, n = a.export_scene()
@@ -256,7 +256,7 @@ def test_exported_scene_renders_the_same_image_in_another_context():
     assert np.array_equal(c.download_accum(), imgs[0])
     c.close()
     # text scenes are not exported (they are a few hundred bytes of constant memory)
-    a.upload(rt.load_scene(os.path.join(S, "hw4/practice3_1.txt")))
+    a.upload(ou.load_scene(os.path.join(S, "hw4/practice3_1.txt")))
     with pytest.raises(rt.B200rtError):
         a.export_scene()
     with pytest.raises(rt.B200rtError):
@@ -267,7 +267,7 @@ def test_exported_scene_renders_the_same_image_in_another_context():
 def test_reference_tree_and_rebuilt_tree_agree():
     """FLAG_REFERENCE_BVH traverses the description's SAH tree, the default the library's own binned-SAH
     tree over the same triangles: same closest hits (ties aside) => same image on the same stream."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=8)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=8)
     imgs, rays = [], []
     for flags in (0, rt.FLAG_REFERENCE_BVH):
         r = rt.Renderer(flags=flags)
@@ -285,7 +285,7 @@ def test_reference_tree_and_rebuilt_tree_agree():
 def test_hw6_matches_port_on_same_stream(renderer, path, frac):
     """hw6 mode (hw5 integrator on triangles; the device traverses its own binned-SAH tree, the port the
     reference's): same Philox stream => same paths up to float rounding of the hit points."""
-    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16, mode=6)
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=16, mode=6)
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
     ok, got = _mean_close(acc, port["accum"], 16, frac, rel=5e-2)
@@ -319,13 +319,13 @@ def _linear(img8):
 def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind):
     spp = 64
     if kind == "gltf":
-        sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp)
+        sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=spp)
     elif kind == "gltf6":
-        sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
+        sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
     elif kind == "text3":
-        sc = rt.load_scene(os.path.join(G, path), samples=spp, mode=rt.MODE_HW3)
+        sc = ou.load_scene(os.path.join(G, path), samples=spp, mode=rt.MODE_HW3)
     else:
-        sc = rt.load_scene(os.path.join(G, path), samples=spp)
+        sc = ou.load_scene(os.path.join(G, path), samples=spp)
     # hw5: 2048 spp is as far as the reference binary gets on the fixture (tools/make_golden.py)
     truth = _linear(ou.golden(name + ("_spp2048" if name.startswith("hw5") else "_spp4096")))
     renderer.upload(sc)
@@ -352,7 +352,7 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
 # ---------------------------------------------------------------- K5 resolve
 @pytest.mark.parametrize("path", ["hw8/sphere_emissive.gltf", "hw7/practice7_4.gltf"])
 def test_resolve_bytes_match_port(renderer, path):
-    sc = rt.load_scene(os.path.join(S, path), width=256, height=192, samples=8)
+    sc = ou.load_scene(os.path.join(S, path), width=256, height=192, samples=8)
     acc = _render(renderer, sc)
     img = renderer.resolve(8)
     cmp = ou.compare_u8(img, ou.port_resolve(acc, 8))
@@ -361,7 +361,7 @@ def test_resolve_bytes_match_port(renderer, path):
 
 def test_resolve_edge_values(renderer):
     """Zeros, huge values, NaN-free ramps through upload_accum -> K5."""
-    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=64, height=64, samples=1)
+    sc = ou.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=64, height=64, samples=1)
     _render(renderer, sc)
     ramp = np.zeros((64, 64, 3), np.float32)
     ramp[..., 0] = np.linspace(0, 4, 64 * 64, dtype=np.float32).reshape(64, 64)
@@ -387,7 +387,7 @@ def test_every_build_renders_the_same_image():
     arithmetic on the same Philox stream: bit-identical radiance, and a second process-independent context
     reproduces it (regression: a register-starved counting build of wf_shade once shaded ~0.1 % of the hits
     of a bounce differently).  The port on the same stream bounds the absolute error."""
-    sc = rt.load_scene(_room(), width=320, height=180, samples=2)
+    sc = ou.load_scene(_room(), width=320, height=180, samples=2)
     imgs = {}
     for name, flags in (("plain", 0), ("plain-again", 0), ("counting", rt.FLAG_COUNTERS), ("serial", rt.FLAG_SERIAL_WAVES),
                         ("megakernel", rt.FLAG_MEGAKERNEL), ("megakernel-counting", rt.FLAG_MEGAKERNEL | rt.FLAG_COUNTERS)):
@@ -406,7 +406,7 @@ def test_every_build_renders_the_same_image():
 
 # ---------------------------------------------------------------- size-independent properties
 def test_sample_ranges_add_up_and_are_deterministic(renderer):
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=640, height=360, samples=32)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=640, height=360, samples=32)
     full = _render(renderer, sc, 0, 32)
     again = _render(renderer, sc, 0, 32)
     assert np.array_equal(full, again), "no float atomics: the same launch is bit-reproducible"
@@ -427,7 +427,7 @@ def test_sample_ranges_add_up_and_are_deterministic(renderer):
 
 def test_full_size_frame_properties(renderer):
     """BASELINE config size (4K): every pixel written, finite, non-negative, stats consistent."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=3840, height=2160, samples=2)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=3840, height=2160, samples=2)
     acc = _render(renderer, sc)
     st = renderer.stats()
     assert st["paths"] == 3840 * 2160 * 2
@@ -441,8 +441,8 @@ def test_full_size_frame_properties(renderer):
 def test_wave_of_two_to_the_26_slots():
     """8192 x 8192 = 2^26 pixels: the largest wave whose slot index leaves no room for the light-cut mask in a queue
     entry (the light stage then tests the cut boxes itself).  Same camera => same mean radiance as a small frame."""
-    small = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=256, height=256, samples=64)
-    big = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=8192, height=8192, samples=1)
+    small = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=256, height=256, samples=64)
+    big = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=8192, height=8192, samples=1)
     r = rt.Renderer()
     ref = _render(r, small).mean() / 64
     acc = _render(r, big)
@@ -460,7 +460,7 @@ def test_empty_text_scene_is_background(renderer, tmp_path, mode_lines, mode):
     p = tmp_path / "empty.txt"
     p.write_text("DIMENSIONS 33 17\nBG_COLOR 0.25 0.5 0.75\nCAMERA_POSITION 0 0 0\nCAMERA_RIGHT 1 0 0\nCAMERA_UP 0 1 0\n"
                  "CAMERA_FORWARD 0 0 -1\nCAMERA_FOV_X 1.0\n" + mode_lines)
-    sc = rt.load_scene(str(p), mode=mode if mode == rt.MODE_HW3 else 0)
+    sc = ou.load_scene(str(p), mode=mode if mode == rt.MODE_HW3 else 0)
     assert sc.mode == mode and sc.desc.n_prims == 0
     acc = _render(renderer, sc)
     n = 1 if mode <= rt.MODE_HW2 else 4
@@ -480,7 +480,7 @@ def test_gltf_scene_without_emitters_under_an_environment_map(renderer, tmp_path
     dark, n = re.subn(r'"emissiveFactor"\s*:\s*\[[^\]]*\]', '"emissiveFactor": [0, 0, 0]', src)
     assert n >= 1
     (tmp_path / "dark.gltf").write_text(dark)
-    sc = rt.load_scene(str(tmp_path / "dark.gltf"), width=96, height=64, samples=16, env_map=os.path.join(S, "hw8/sphere_emission.png"))
+    sc = ou.load_scene(str(tmp_path / "dark.gltf"), width=96, height=64, samples=16, env_map=os.path.join(S, "hw8/sphere_emission.png"))
     assert sc.desc.n_light_tris == 0 and sc.desc.n_tris == 970
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
@@ -499,7 +499,7 @@ def test_errors_are_reported_not_thrown(renderer):
         assert e.value.code == -4
     finally:
         r.close()
-    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=16, height=16, samples=1)
+    sc = ou.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=16, height=16, samples=1)
     renderer.upload(sc)
     with pytest.raises(rt.B200rtError):
         renderer.render(4, 4)          # empty sample range

@@ -14,7 +14,7 @@ S, G = ou.SCENES, ou.GOLDEN
 
 
 def test_port_hw1_bytes_equal_reference():
-    sc = rt.load_scene(os.path.join(S, "hw1/sample.txt"))
+    sc = ou.load_scene(os.path.join(S, "hw1/sample.txt"))
     assert (sc.mode, sc.width, sc.height) == (rt.MODE_HW1, 640, 480)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden("hw1_sample"))
@@ -27,7 +27,7 @@ def test_port_hw1_bytes_equal_reference():
 
 
 def test_port_hw2_bytes_equal_reference():
-    sc = rt.load_scene(os.path.join(S, "hw2/sample.txt"))
+    sc = ou.load_scene(os.path.join(S, "hw2/sample.txt"))
     assert (sc.mode, sc.width, sc.height, sc.ray_depth) == (rt.MODE_HW2, 664, 510, 5)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden("hw2_sample"))
@@ -35,7 +35,7 @@ def test_port_hw2_bytes_equal_reference():
 
 @pytest.mark.parametrize("k", [1, 3, 4])
 def test_port_hw4_bytes_equal_reference(k):
-    sc = rt.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"))
+    sc = ou.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"))
     assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW4, 160, 120, 4, 6)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden(f"hw4_p3_{k}_spp4"))
@@ -44,7 +44,7 @@ def test_port_hw4_bytes_equal_reference(k):
 @pytest.mark.parametrize("k", [1, 3, 4])
 def test_port_hw3_bytes_equal_reference(k):
     """hw3 ships hw4's scenes (only SAMPLES differs); the golden is the hw3 binary on the shrunk hw4 input."""
-    sc = rt.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"), mode=rt.MODE_HW3)
+    sc = ou.load_scene(os.path.join(G, f"hw4_p3_{k}_spp4.txt"), mode=rt.MODE_HW3)
     assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW3, 160, 120, 4, 6)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden(f"hw3_p3_{k}_spp4"))
@@ -57,7 +57,7 @@ def test_port_hw5_bytes_equal_reference():
     tests/scenes/hw5/mixed.txt (tools/make_hw5_fixture.py) holds every figure kind, material and light kind, a
     rotated box light and a triangle with its own POSITION / ROTATION.  Byte equality with the hw5 binary pins the
     host's figure BVH (order of the lights) and the port's BoxLight draw order."""
-    sc = rt.load_scene(os.path.join(S, "hw5/mixed.txt"))
+    sc = ou.load_scene(os.path.join(S, "hw5/mixed.txt"))
     d = sc.desc
     assert (sc.mode, sc.width, sc.height, sc.samples, sc.ray_depth) == (rt.MODE_HW5, 160, 120, 4, 6)
     assert (d.n_prims, d.n_bvh_prims, d.n_light_prims) == (36, 31, 4)
@@ -69,7 +69,7 @@ def test_port_hw5_bytes_equal_reference():
 def test_port_box_light_bytes_equal_reference(hw, mode):
     """None of the reference's hw3 / hw4 scenes has a BOX light; this subset of the hw5 fixture has a rotated one
     (non-unit quaternion).  Pins BoxLight::sample's argument evaluation order (right to left under g++)."""
-    sc = rt.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), mode=mode)
+    sc = ou.load_scene(os.path.join(G, "hw4_boxlight_spp4.txt"), mode=mode)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden(f"{hw}_boxlight_spp4"))
 
@@ -78,7 +78,7 @@ def test_port_box_light_bytes_equal_reference(hw, mode):
                                        ("hw7_practice7_4", "hw7/practice7_4.gltf"),
                                        ("hw8_sphere_emissive", "hw8/sphere_emissive.gltf")])
 def test_port_gltf_bytes_equal_reference(name, path):
-    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=4)
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=4)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
 
@@ -86,7 +86,7 @@ def test_port_gltf_bytes_equal_reference(name, path):
 def test_port_hw8_environment_map_bytes_equal_reference():
     """hw8's optional argv[6]: misses look the equirectangular image up instead of returning black
     (hw8/src/scene.cpp:90-97, hw8/src/main.cpp:12-14)."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=4,
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=4,
                        env_map=os.path.join(S, "hw8/sphere_emission.png"))
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden("hw8_sphere_emissive_env_128x96_spp4"))
@@ -99,7 +99,7 @@ def test_port_hw6_bytes_equal_reference(name, path):
     """hw6 = hw5 integrator (diffuse / mirror / dielectric) on glTF triangles: the port with the reference's
     generator reproduces the hw6 binary's PPM byte for byte (this also pins the hw6 loader's material
     mapping and its BVH build over all-equal sort keys, which fixes the light order)."""
-    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=4, mode=6)
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=4, mode=6)
     o = ou.port_render(sc, 0)
     assert np.array_equal(o["rgb"], ou.golden(f"{name}_128x96_spp4"))
 
@@ -107,7 +107,7 @@ def test_port_hw6_bytes_equal_reference(name, path):
 def test_port_philox_is_statistically_the_same_estimator():
     """The Philox policy changes only the random numbers: at equal spp its error against the
     4096-spp reference render must be comparable to the minstd policy's, and the mean must agree."""
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=32)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=128, height=96, samples=32)
     truth = ou.inv_display(ou.golden("hw8_sphere_emissive_128x96_spp4096"))
     a = ou.inv_display(ou.port_render(sc, 0)["rgb"])
     b = ou.inv_display(ou.port_render(sc, 1)["rgb"])
@@ -119,13 +119,13 @@ def test_port_philox_is_statistically_the_same_estimator():
 
 def test_port_sample_ranges_add_up():
     """Counter-based stream: rendering [0,4) and [4,8) separately equals [0,8) up to float order."""
-    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=64, height=48, samples=8)
+    sc = ou.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=64, height=48, samples=8)
     full = ou.port_render(sc, 1, spp_begin=0, spp_end=8)["accum"]
     parts = ou.port_render(sc, 1, spp_begin=0, spp_end=4)["accum"] + ou.port_render(sc, 1, spp_begin=4, spp_end=8)["accum"]
     assert np.allclose(full, parts, rtol=1e-5, atol=1e-6)
 
 
 def test_port_resolve_matches_port_render():
-    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=64, height=48, samples=4)
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=64, height=48, samples=4)
     o = ou.port_render(sc, 1)
     assert np.array_equal(ou.port_resolve(o["accum"], 4), o["rgb"])
