@@ -177,6 +177,11 @@ typedef struct b200rt_options {
 #define B200RT_FLAG_SERIAL_WAVES 4 /* wavefront: one wave in flight on one stream (default: two waves overlap on two
                                       streams); the per-stage times in b200rt_stats are then exclusive kernel times */
 
+#define B200RT_FLAG_KEEP_DARK_RAYS 16 /* wavefront: do not end a path one bounce early when its last ray cannot reach an
+                                       emitter (black background only; the image is bit-identical either way -- test aid) */
+#define B200RT_FLAG_EXPLICIT_CAMERA_STATE 32 /* wavefront: wf_generate stores the whole state record of a camera path
+                                       instead of the direction only (bit-identical image -- test aid) */
+
 typedef struct b200rt_stats {
     double   kernel_ms;        /* device time of the last b200rt_render (CUDA events) */
     uint64_t paths;            /* camera samples started                                */
@@ -238,6 +243,49 @@ int b200rt_import_scene_begin(b200rt_ctx *ctx, const b200rt_scene_image *hdr, vo
 int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr);
 /* The three steps in one call for two contexts of the same process (cudaMemcpyPeerAsync between their devices). */
 int b200rt_replicate_scene(b200rt_ctx *src, b200rt_ctx *dst);
+
+/* ---- several GPUs (the sample split of ONE frame, reduce inside the library) -------------------
+ * Replaces: the OpenMP pixel loop as the unit of parallelism (hw8/src/sceneio.cpp:386-396).  The scene is replicated,
+ * GPU g renders the global sample indices [b + g*S/G, b + (g+1)*S/G) of every pixel into its own float buffer, and the
+ * buffers are combined by ONE kernel on the first GPU that READS the other GPUs' buffers through peer memory (NVLink /
+ * NVSwitch loads), sums them in rank order and tonemaps in the same pass -- no host copy, no separate collective.
+ *
+ * Peer level (any mix of contexts, also of other processes through CUDA IPC): */
+#define B200RT_MAX_PEERS 15
+/* rgb_out = resolve(own accumulation buffer + peer_accum[0] + ... + peer_accum[n_peers-1]) (summed in that order);
+ * every peer pointer must be readable from ctx's device (same device, peer access, or b200rt_ipc_open) and hold the
+ * same frame size; the peers' renders must have finished (b200rt_synchronize on their contexts).  Blocks. */
+int b200rt_resolve_peers(b200rt_ctx *ctx, int32_t total_spp, const void *const *peer_accum, int32_t n_peers, uint8_t *rgb_out);
+/* own accumulation buffer += the peers' (same order; for b200rt_download_accum of the whole frame).  Asynchronous. */
+int b200rt_reduce_peers(b200rt_ctx *ctx, const void *const *peer_accum, int32_t n_peers);
+/* Lets ctx's device read memory of `peer_device` directly (cudaDeviceEnablePeerAccess; a no-op on the same device). */
+int b200rt_enable_peer(b200rt_ctx *ctx, int32_t peer_device);
+/* One process per GPU: a 64-byte handle of the accumulation buffer to hand to the reducing process ... */
+typedef struct b200rt_ipc_handle { uint8_t opaque[64]; } b200rt_ipc_handle;
+int b200rt_accum_ipc_export(b200rt_ctx *ctx, b200rt_ipc_handle *out);
+/* ... which maps it into its own address space (and unmaps it when done). */
+int b200rt_ipc_open(b200rt_ctx *ctx, const b200rt_ipc_handle *h, void **peer_ptr);
+int b200rt_ipc_close(b200rt_ctx *ctx, void *peer_ptr);
+
+/* Group level (one process drives all GPUs; what the CLI uses).  devices[] may repeat a device (two contexts on one
+ * GPU take the same path: that is how a single-GPU box tests it). */
+typedef struct b200rt_group b200rt_group;
+int b200rt_group_create(b200rt_group **out, const int32_t *devices, int32_t n_devices, const b200rt_options *opt);
+void b200rt_group_destroy(b200rt_group *g);
+int32_t b200rt_group_size(const b200rt_group *g);
+b200rt_ctx *b200rt_group_member(b200rt_group *g, int32_t i);
+/* One host-side upload on member 0, device-to-device replication to the others (glTF modes; text scenes upload per member). */
+int b200rt_group_upload_scene(b200rt_group *g, const b200rt_scene_desc *scene);
+/* Splits [spp_begin, spp_end) contiguously over the members (hw1 / hw2: member 0 alone) and launches all of them. */
+int b200rt_group_render(b200rt_group *g, int32_t width, int32_t height, int32_t spp_begin, int32_t spp_end, int32_t ray_depth);
+int b200rt_group_clear(b200rt_group *g);
+/* Waits for every member, then the fused peer reduce + resolve on member 0. */
+int b200rt_group_resolve(b200rt_group *g, int32_t total_spp, uint8_t *rgb_out);
+/* Radiance SUM of the whole frame (peer reduce into a scratch copy on member 0; the members' buffers are untouched). */
+int b200rt_group_download_accum(b200rt_group *g, float *rgb_out);
+/* Counters summed over the members, times = the slowest member's. */
+int b200rt_group_get_stats(b200rt_group *g, b200rt_stats *out);
+const char *b200rt_group_last_error(b200rt_group *g);
 
 /* hw1/hw2 parity aid: primitive index of the primary hit per pixel (-1 = miss), int32 W*H. */
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out);

@@ -19,6 +19,8 @@ MODE_HW1, MODE_HW2, MODE_HW3, MODE_HW4, MODE_HW5, MODE_HW6, MODE_HW7, MODE_HW8 =
 FLAG_COUNTERS = 1
 FLAG_MEGAKERNEL = 2   # glTF modes: per-path megakernel instead of the wavefront pipeline
 FLAG_REFERENCE_BVH = 8  # glTF modes: traverse the description's BVH instead of the library's rebuilt one
+FLAG_KEEP_DARK_RAYS = 16
+FLAG_EXPLICIT_CAMERA_STATE = 32
 FLAG_SERIAL_WAVES = 4  # wavefront: one wave in flight (stage times in stats() are then exclusive kernel times)
 
 
@@ -128,6 +130,26 @@ def device_lib():
         L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
         L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
         L.b200rt_stream.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        L.b200rt_resolve_peers.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_reduce_peers.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32]
+        L.b200rt_enable_peer.argtypes = [ctypes.c_void_p, ctypes.c_int32]
+        L.b200rt_accum_ipc_export.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_ipc_open.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        L.b200rt_ipc_close.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_group_create.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int32), ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_group_destroy.argtypes = [ctypes.c_void_p]
+        L.b200rt_group_destroy.restype = None
+        L.b200rt_group_size.argtypes = [ctypes.c_void_p]
+        L.b200rt_group_member.argtypes = [ctypes.c_void_p, ctypes.c_int32]
+        L.b200rt_group_member.restype = ctypes.c_void_p
+        L.b200rt_group_upload_scene.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_group_render.argtypes = [ctypes.c_void_p] + [ctypes.c_int32] * 5
+        L.b200rt_group_clear.argtypes = [ctypes.c_void_p]
+        L.b200rt_group_resolve.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
+        L.b200rt_group_download_accum.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.b200rt_group_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
+        L.b200rt_group_last_error.argtypes = [ctypes.c_void_p]
+        L.b200rt_group_last_error.restype = ctypes.c_char_p
         _dev = L
     return _dev
 
@@ -136,7 +158,11 @@ DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b20
                   "b200rt_resolve", "b200rt_download_accum", "b200rt_upload_accum", "b200rt_accum_device_ptr",
                   "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end", "b200rt_replicate_scene",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
-                  "b200rt_strerror", "b200rt_last_error", "b200rt_device_count"]
+                  "b200rt_strerror", "b200rt_last_error", "b200rt_device_count",
+                  "b200rt_resolve_peers", "b200rt_reduce_peers", "b200rt_enable_peer", "b200rt_accum_ipc_export",
+                  "b200rt_ipc_open", "b200rt_ipc_close", "b200rt_group_create", "b200rt_group_destroy", "b200rt_group_size",
+                  "b200rt_group_member", "b200rt_group_upload_scene", "b200rt_group_render", "b200rt_group_clear",
+                  "b200rt_group_resolve", "b200rt_group_download_accum", "b200rt_group_get_stats", "b200rt_group_last_error"]
 HOST_SYMBOLS = ["b200rt_host_load_text", "b200rt_host_load_gltf", "b200rt_host_load_gltf_ex", "b200rt_host_set_env_map",
                 "b200rt_host_desc", "b200rt_host_set_frame", "b200rt_host_free", "b200rt_host_write_ppm",
                 "b200rt_host_write_png", "b200rt_host_write_pfm", "b200rt_host_timings", "b200rt_host_strerror"]
@@ -301,6 +327,37 @@ class Renderer:
         self._ck(self._L.b200rt_replicate_scene(other._ctx, self._ctx))
         self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
 
+    # several GPUs, peer level (include/b200rt.h): fused reduce + resolve over peer-readable buffers
+    @staticmethod
+    def _ptr_array(ptrs):
+        return (ctypes.c_void_p * max(len(ptrs), 1))(*ptrs)
+
+    def resolve_peers(self, total_spp, peer_ptrs, out=None):
+        """RGB8 of (own accumulation buffer + the peers'), summed in the order given, in ONE kernel."""
+        if out is None:
+            out = np.empty((self.height, self.width, 3), np.uint8)
+        self._ck(self._L.b200rt_resolve_peers(self._ctx, total_spp, self._ptr_array(peer_ptrs), len(peer_ptrs), out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def reduce_peers(self, peer_ptrs):
+        self._ck(self._L.b200rt_reduce_peers(self._ctx, self._ptr_array(peer_ptrs), len(peer_ptrs)))
+
+    def enable_peer(self, device):
+        self._ck(self._L.b200rt_enable_peer(self._ctx, device))
+
+    def accum_ipc_export(self):
+        h = ctypes.create_string_buffer(64)
+        self._ck(self._L.b200rt_accum_ipc_export(self._ctx, h))
+        return h.raw
+
+    def ipc_open(self, handle):
+        p = ctypes.c_void_p()
+        self._ck(self._L.b200rt_ipc_open(self._ctx, ctypes.create_string_buffer(bytes(handle), 64), ctypes.byref(p)))
+        return p.value
+
+    def ipc_close(self, ptr):
+        self._ck(self._L.b200rt_ipc_close(self._ctx, ctypes.c_void_p(ptr)))
+
     def primary_ids(self):
         out = np.empty((self.height, self.width), np.int32)
         self._ck(self._L.b200rt_primary_ids(self._ctx, self.width, self.height, out.ctypes.data_as(ctypes.c_void_p)))
@@ -320,6 +377,78 @@ class Renderer:
         if self._ctx:
             self._L.b200rt_destroy(self._ctx)
             self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Group:
+    """Several contexts driven by one process (b200rt_group_*): one upload + device-to-device replication, samples
+    split contiguously over the members, ONE fused peer reduce + resolve kernel on member 0.  `devices` may repeat."""
+
+    def __init__(self, devices, seed=0, flags=0):
+        self._L = device_lib()
+        self._g = ctypes.c_void_p()
+        opt = Options(0, seed, flags)
+        dv = (ctypes.c_int32 * len(devices))(*devices)
+        rc = self._L.b200rt_group_create(ctypes.byref(self._g), dv, len(devices), ctypes.byref(opt))
+        if rc:
+            raise B200rtError(rc, self._L.b200rt_strerror(rc).decode())
+        self.width = self.height = 0
+
+    def _ck(self, rc):
+        if rc:
+            raise B200rtError(rc, self._L.b200rt_strerror(rc).decode() + " / " + self._L.b200rt_group_last_error(self._g).decode())
+
+    def upload(self, scene):
+        self._ck(self._L.b200rt_group_upload_scene(self._g, scene.desc_ptr))
+        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
+
+    def render(self, spp_begin=0, spp_end=None, width=0, height=0, ray_depth=0):
+        if spp_end is None:
+            spp_end = self.samples
+        if width > 0:
+            self.width = width
+        if height > 0:
+            self.height = height
+        self._ck(self._L.b200rt_group_render(self._g, width, height, spp_begin, spp_end, ray_depth))
+
+    def clear(self):
+        self._ck(self._L.b200rt_group_clear(self._g))
+
+    def resolve(self, total_spp=None, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 3), np.uint8)
+        self._ck(self._L.b200rt_group_resolve(self._g, total_spp or self.samples, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def download_accum(self):
+        out = np.empty((self.height, self.width, 3), np.float32)
+        self._ck(self._L.b200rt_group_download_accum(self._g, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def member_accum(self, i):
+        """Radiance sum buffer of member i alone (tests)."""
+        out = np.empty((self.height, self.width, 3), np.float32)
+        rc = self._L.b200rt_download_accum(self._L.b200rt_group_member(self._g, i), out.ctypes.data_as(ctypes.c_void_p))
+        self._ck(rc)
+        return out
+
+    def stats(self):
+        s = Stats()
+        self._ck(self._L.b200rt_group_get_stats(self._g, ctypes.byref(s)))
+        return s.as_dict()
+
+    def __len__(self):
+        return self._L.b200rt_group_size(self._g)
+
+    def close(self):
+        if self._g:
+            self._L.b200rt_group_destroy(self._g)
+            self._g = ctypes.c_void_p()
 
     def __del__(self):
         try:

@@ -51,7 +51,7 @@ def build_cuda(force=False, verbose=False):
     os.makedirs(LIB, exist_ok=True)
     cu = os.path.join(CSRC, "cuda")
     out = os.path.join(LIB, "libb200rt.so")
-    deps = _all_under(cu, (".cu", ".cuh", ".h")) + _all_under(INC, (".h",))
+    deps = _all_under(cu, (".cu", ".cuh", ".h")) + _all_under(os.path.join(CSRC, "common"), (".h",)) + _all_under(INC, (".h",))
     if not force and not _newer(deps, out):
         return out
     common = [NVCC] + ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INC, "-I", cu,
@@ -61,12 +61,21 @@ def build_cuda(force=False, verbose=False):
         common += ["-Xptxas", "-v"]
     objs = []
     # analytic kernels: no FMA contraction (bit-exact hw1/hw2); path tracer: default FMA
-    for src, extra in (("b200rt.cu", []), ("analytic_kernels.cu", ["-fmad=false"])):
+    units = (("b200rt.cu", []), ("upload.cu", []), ("scheduler.cu", []), ("multi_gpu.cu", []),
+             ("analytic_kernels.cu", ["-fmad=false"]))
+    procs = []
+    for src, extra in units:        # the units compile concurrently (scheduler.cu holds the big kernels)
         obj = os.path.join(LIB, src.replace(".cu", ".o"))
-        log = _run(common + extra + ["-c", os.path.join(cu, src), "-o", obj])
+        cmd = common + extra + ["-c", os.path.join(cu, src), "-o", obj]
+        procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+        objs.append(obj)
+    for cmd, pr in procs:
+        log = pr.communicate()[0]
+        if pr.returncode != 0:
+            sys.stderr.write(" ".join(cmd) + "\n" + log + "\n")
+            raise RuntimeError("build step failed: " + cmd[0])
         if verbose:
             print(log)
-        objs.append(obj)
     _run([NVCC] + ARCH + ["-shared", "-ccbin", GXX, "-o", out] + objs)
     return out
 
@@ -77,7 +86,7 @@ def build_host(force=False):
     hd = os.path.join(CSRC, "host")
     out = os.path.join(LIB, "libb200rt_host.so")
     srcs = [os.path.join(hd, f) for f in ("text_scene.cpp", "gltf_scene.cpp", "host_api.cpp", "png_decode.cpp")]
-    if not force and not _newer(_all_under(hd, (".cpp", ".h")) + _all_under(INC, (".h",)), out):
+    if not force and not _newer(_all_under(hd, (".cpp", ".h")) + _all_under(os.path.join(CSRC, "common"), (".h",)) + _all_under(INC, (".h",)), out):
         return out
     flags = ["-O2", "-std=c++17", "-Wall", "-Wextra", "-fPIC", "-shared", "-I", INC]
     if os.path.exists(os.path.join(STB_DIR, "stb_image.h")):

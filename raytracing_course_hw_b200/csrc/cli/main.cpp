@@ -5,7 +5,8 @@
 // Same stderr chatter ("UNKNOWN COMMAND: ..", "FINISH"), same binary P6 output.  Unlike the
 // reference (which never checks argc) a wrong invocation prints a usage line and exits 2.
 // Environment: B200RT_MODE=hw1..hw8 forces the semantics (default: inferred from the scene),
-// B200RT_GPUS=N renders with N GPUs (samples split, partial sums added on the host in rank order),
+// B200RT_GPUS=N renders with N GPUs (samples split; the buffers are combined by one peer-memory kernel on GPU 0),
+// output container by file name (.ppm / anything: binary P6 like the reference; .png; .pfm = float radiance),
 // B200RT_SEED, B200RT_STATS=1 (JSON with timings and ray counts on stderr).
 #include <chrono>
 #include <cstdio>
@@ -60,57 +61,58 @@ int main(int argc, const char *argv[]) {
     int avail = b200rt_device_count();
     if (avail <= 0) { fprintf(stderr, "b200rt: no CUDA device (this renderer has no CPU fallback)\n"); return 1; }
     if (n_gpus < 1) n_gpus = 1;
-    if (n_gpus > avail) n_gpus = avail;
+    if (n_gpus > B200RT_MAX_PEERS + 1) n_gpus = B200RT_MAX_PEERS + 1;
+    // more members than devices: they share devices round robin (same code path; how a one-GPU box exercises it)
     if (d->mode <= B200RT_MODE_HW2 || d->samples < n_gpus) n_gpus = 1;   // one sample per pixel: nothing to split
 
     t0 = now_ms();
-    std::vector<b200rt_ctx *> ctx((size_t)n_gpus, nullptr);
+    // All GPUs behind one group: one host-side upload, device-to-device replication, sample split
+    // [g*S/G, (g+1)*S/G), and ONE fused peer reduce + resolve kernel on the first GPU (include/b200rt.h).
     b200rt_options opt{};
     opt.seed = getenv("B200RT_SEED") ? (uint32_t)strtoul(getenv("B200RT_SEED"), nullptr, 10) : 0u;
-    for (int g = 0; g < n_gpus && !rc; g++) {
-        opt.device = g;
-        rc = b200rt_create(&ctx[g], &opt);
-        // one host-side upload; the other GPUs get a device-to-device copy of the resident scene (glTF modes)
-        if (!rc) rc = (g > 0 && d->mode >= B200RT_MODE_HW6) ? b200rt_replicate_scene(ctx[0], ctx[g]) : b200rt_upload_scene(ctx[g], d);
-        if (rc) fprintf(stderr, "b200rt: GPU %d: %s (%s)\n", g, b200rt_strerror(rc), ctx[g] ? b200rt_last_error(ctx[g]) : "");
-    }
+    std::vector<int32_t> devices((size_t)n_gpus);
+    for (int g = 0; g < n_gpus; g++) devices[(size_t)g] = g % avail;
+    b200rt_group *grp = nullptr;
+    rc = b200rt_group_create(&grp, devices.data(), n_gpus, &opt);
+    if (rc) { fprintf(stderr, "b200rt: cannot create the render contexts: %s\n", b200rt_strerror(rc)); b200rt_host_free(scene); return 1; }
+    auto report = [&](const char *what) { fprintf(stderr, "b200rt: %s: %s (%s)\n", what, b200rt_strerror(rc), b200rt_group_last_error(grp)); };
+    rc = b200rt_group_upload_scene(grp, d);
+    if (rc) report("upload");
     double t_upload = now_ms() - t0;
     t0 = now_ms();
-    // sample-split: GPU g renders global sample indices [g*S/G, (g+1)*S/G)  (async on each context)
-    for (int g = 0; g < n_gpus && !rc; g++) {
-        int b = (int)((long long)d->samples * g / n_gpus), e = (int)((long long)d->samples * (g + 1) / n_gpus);
-        rc = b200rt_render(ctx[g], 0, 0, b, e, 0);
-        if (rc) fprintf(stderr, "b200rt: render on GPU %d: %s (%s)\n", g, b200rt_strerror(rc), b200rt_last_error(ctx[g]));
-    }
-    std::vector<uint8_t> rgb((size_t)d->width * d->height * 3);
-    if (!rc && n_gpus > 1) {
-        size_t n = rgb.size();
-        std::vector<float> sum(n, 0.f), part(n);
-        for (int g = 0; g < n_gpus && !rc; g++) {
-            rc = b200rt_download_accum(ctx[g], part.data());
-            for (size_t i = 0; i < n; i++) sum[i] += part[i];
-        }
-        if (!rc) rc = b200rt_upload_accum(ctx[0], sum.data());
-    }
-    if (!rc) rc = b200rt_resolve(ctx[0], d->samples, rgb.data());
-    double t_render = now_ms() - t0;
-    if (rc) fprintf(stderr, "b200rt: %s (%s)\n", b200rt_strerror(rc), ctx[0] ? b200rt_last_error(ctx[0]) : "");
+    if (!rc && (rc = b200rt_group_render(grp, 0, 0, 0, d->samples, 0))) report("render");
+    const size_t n_bytes = (size_t)d->width * d->height * 3;
+    const size_t len = strlen(out_path);
+    const bool want_pfm = len > 4 && !strcmp(out_path + len - 4, ".pfm");
+    const bool want_png = len > 4 && !strcmp(out_path + len - 4, ".png");
+    std::vector<uint8_t> rgb;
+    std::vector<float> sum;
     if (!rc) {
-        rc = b200rt_host_write_ppm(out_path, d->width, d->height, rgb.data());
+        try { if (want_pfm) sum.resize(n_bytes); else rgb.resize(n_bytes); }
+        catch (...) { fprintf(stderr, "b200rt: out of memory for the frame\n"); rc = B200RT_ERR_INVALID; }
+    }
+    if (!rc) {
+        // the output container follows the file name: .pfm = float radiance before tonemapping, .png, else the
+        // reference's binary P6 (hw8/src/sceneio.cpp:382-401)
+        rc = want_pfm ? b200rt_group_download_accum(grp, sum.data()) : b200rt_group_resolve(grp, d->samples, rgb.data());
+        if (rc) report("resolve");
+    }
+    double t_render = now_ms() - t0;
+    if (!rc) {
+        rc = want_pfm ? b200rt_host_write_pfm(out_path, d->width, d->height, sum.data(), d->mode <= B200RT_MODE_HW2 ? 1 : d->samples)
+           : want_png ? b200rt_host_write_png(out_path, d->width, d->height, rgb.data())
+                      : b200rt_host_write_ppm(out_path, d->width, d->height, rgb.data());
         if (rc) fprintf(stderr, "b200rt: cannot write %s\n", out_path);
     }
     if (!rc && want_stats) {
         b200rt_stats st{};
-        unsigned long long paths = 0, rays = 0;
-        double kernel_ms = 0;
-        for (int g = 0; g < n_gpus; g++)
-            if (b200rt_get_stats(ctx[g], &st) == 0) { paths += st.paths; rays += st.rays; if (st.kernel_ms > kernel_ms) kernel_ms = st.kernel_ms; }
-        fprintf(stderr, "{\"mode\": %d, \"width\": %d, \"height\": %d, \"samples\": %d, \"gpus\": %d, \"load_ms\": %.3f, \"upload_ms\": %.3f, "
-                        "\"render_ms\": %.3f, \"kernel_ms\": %.3f, \"paths\": %llu, \"rays\": %llu, \"mpaths_per_s\": %.3f}\n",
-                d->mode, d->width, d->height, d->samples, n_gpus, t_load, t_upload, t_render, kernel_ms, paths, rays,
-                kernel_ms > 0 ? paths / kernel_ms / 1e3 : 0.0);
+        if (b200rt_group_get_stats(grp, &st) == 0)
+            fprintf(stderr, "{\"mode\": %d, \"width\": %d, \"height\": %d, \"samples\": %d, \"gpus\": %d, \"load_ms\": %.3f, \"upload_ms\": %.3f, "
+                            "\"render_ms\": %.3f, \"kernel_ms\": %.3f, \"paths\": %llu, \"rays\": %llu, \"mpaths_per_s\": %.3f}\n",
+                    d->mode, d->width, d->height, d->samples, n_gpus, t_load, t_upload, t_render, st.kernel_ms,
+                    (unsigned long long)st.paths, (unsigned long long)st.rays, st.kernel_ms > 0 ? st.paths / st.kernel_ms / 1e3 : 0.0);
     }
-    for (auto c : ctx) b200rt_destroy(c);
+    b200rt_group_destroy(grp);
     b200rt_host_free(scene);
     if (!rc && gltf) fprintf(stderr, "FINISH\n");   // hw6-hw8 main.cpp print this on success
     return rc ? 1 : 0;

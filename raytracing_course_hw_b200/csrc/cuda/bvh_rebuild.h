@@ -298,9 +298,11 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
     c.leaf_max = 4; c.trav = 1.f;        // sweep: profiles/r01_sweep_bvh_rebuild.log
     c.sweep_max = 12;
     c.sah_depth = 32;      // + ceil(log2(2^27 / leaf)) median levels < B200RT_STACK (64)
+#ifdef B200RT_DEV      // tools/sweep_*.sh
     if (const char *e = getenv("B200RT_REBUILD_SWEEP")) c.sweep_max = std::max(0, std::min(SWEEP_MAX, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_LEAF_LIGHT" : "B200RT_REBUILD_LEAF")) c.leaf_max = std::max(1, std::min(15, atoi(e)));
     if (const char *e = getenv(light_set ? "B200RT_REBUILD_TRAV_LIGHT" : "B200RT_REBUILD_TRAV")) c.trav = (float)atof(e);
+#endif
     c.threads = host_threads();
     if (n < 65536) c.threads = 1;
     static_assert(sizeof(B3) == 6 * sizeof(float), "B3 is six floats");
@@ -326,6 +328,7 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
         } else prep(0, (size_t)n);
     }
     c.box = box; c.cen = cen; c.order = out.order.data();
+#ifdef B200RT_DEV
     const bool timing = !light_set && getenv("B200RT_UPLOAD_TIMING") != nullptr;
     auto t_last = std::chrono::steady_clock::now();
     auto lap = [&](const char *what) {
@@ -334,6 +337,9 @@ inline void rebuild_bvh_binned_sah(const b200rt_triangle *tris, int n, RebuiltBv
         fprintf(stderr, "[rebuild] %-20s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
         t_last = now;
     };
+#else
+    auto lap = [](const char *) {};
+#endif
     lap("boxes, centroids");
 
     // Node slots: 0 = root; a node with `count` triangles owns at most 2 * count - 2 descendants.  The top of

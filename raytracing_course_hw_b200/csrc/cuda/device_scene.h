@@ -20,6 +20,8 @@ namespace b200rt {
 #define B200RT_QBITS 15      /* 15: the PRMT result is used as a float directly (no FADD); 16: finer grid, one more op per plane */
 #endif
 #define B200RT_QMAX ((1 << B200RT_QBITS) - 1)
+#define B200RT_LEAF 0x80000000u   /* child word: leaf flag */
+#define B200RT_STACK 64           /* traversal stack entries per thread; the upload bounds the tree depth by it */
 struct DPair {
     uint4 a, b;
 };

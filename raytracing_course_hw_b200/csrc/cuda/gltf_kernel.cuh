@@ -13,10 +13,8 @@
 
 namespace b200rt {
 
-#define B200RT_STACK 64
 #define B200RT_TMAX 1e4f
 #define B200RT_EPS 1e-4f
-#define B200RT_LEAF 0x80000000u
 
 struct TraceHit {
     float t, u, v;

@@ -17,13 +17,10 @@
 // distributions.h:122-165).
 #pragma once
 #include "gltf_kernel.cuh"
+#include "wave_state.h"
 
 namespace b200rt {
 
-#define B200RT_WF_BATCH 16       /* traversal steps between refills (sweep: profiles/r01_sweep_wf.log) */
-#define B200RT_WF_BATCH_LIGHT 16 /* same for the light-pdf traversal */
-#define B200RT_WF_LEAF_T_LIGHT 24 /* light-pdf traversal: leaves are rare and dear, wait for a fuller warp (profiles/r01_sweep_light.log) */
-#define B200RT_WF_LEAF_T 8       /* lanes waiting at a leaf that trigger a leaf phase */
 #ifndef B200RT_EXT_MINB
 #define B200RT_EXT_MINB 9        /* min resident blocks per SM asked of ptxas for extend / light (sweep: profiles/r01_sweep_quantised_nodes.log) */
 #endif
@@ -33,50 +30,8 @@ namespace b200rt {
 #ifndef B200RT_EXT_UNROLL
 #define B200RT_EXT_UNROLL 2      /* box steps per phase decision in wf_extend's inner phase */
 #endif
-#define B200RT_WF_MASK_SHIFT 26  /* light-queue entry = path slot | light-cut mask << 26 (slots < 2^26, <= 6 cut boxes) */
 #define B200RT_WF_MISS 0x7FFFFFFFu
-#define B200RT_WF_DEAD 0x7FFFFFFEu   /* written by wf_trace: the firefly clamp ended this path */
 #define B200RT_FULL 0xffffffffu
-
-// Path state is one 128-byte record per path slot (AoS): after the first bounce the stages visit slots in an
-// order scrambled by the persistent kernels, and ncu showed every scattered 16-byte field access of the former
-// six-array (SoA) layout costing a 64-byte DRAM burst (shade: 1.8 GB read per launch for 0.56 GB of state).  In
-// the record, the fields a stage touches together share a 32-byte sector: {ray_o, ray_d} {hit, thr} {rad, bsdf}.
-// B200RT_STATE_AOS=0 restores the separate arrays.
-#ifndef B200RT_STATE_AOS
-#define B200RT_STATE_AOS 1
-#endif
-#if B200RT_STATE_AOS
-#define B200RT_STATE_STRIDE 8      /* float4 units: 128 bytes per path slot */
-#else
-#define B200RT_STATE_STRIDE 1
-#endif
-struct StateField {
-    float4 *base;
-    __host__ __device__ __forceinline__ float4 &operator[](size_t slot) const { return base[slot * B200RT_STATE_STRIDE]; }
-};
-struct WaveBuffers {
-    float4 *state;      // the one allocation behind the fields below
-    StateField ray_o;   // o.xyz, pixel index (int bits): the Philox key of the path
-    StateField ray_d;   // d.xyz, |nd . n_s| of the bounce that produced this ray
-    StateField hit;     // t, u, v, bits: triangle index | inside << 31 (B200RT_WF_MISS = no hit)
-    StateField thr;     // throughput T.xyz, partial pdf (cosine + vndf)
-    StateField rad;     // radiance L.xyz, global sample index (int bits): the Philox counter of the path
-    StateField bsdf;    // BRDF value of the pending bounce
-    int *queue[3];
-    // per bounce b, c = ctr + 4b: c[-1] = rays entering bounce b, c[0] = extend cursor, c[1] = light cursor,
-    //               c[2] = light queries of bounce b, c[3] = rays entering bounce b+1.  (c[2], c[3]) is an aligned
-    //               64-bit word: the shade stage appends to both queues with ONE atomic (queue_push2).
-    //               ctr points 4 ints into its allocation, so ctr[-1] exists.
-    int *ctr;
-};
-
-struct WaveParams {
-    DCamera cam;
-    int32_t tiles_x, n_tiles;     // 8x4 pixel tiles
-    int32_t s_begin, s_count;     // global sample indices [s_begin, s_begin + s_count) in this wave
-    uint32_t seed;
-};
 
 // Wave state accessors: plain caching.  Evict-first (.cs) accesses were measured: extend and light gain 1 %, shade
 // loses 15 % (it re-reads what the previous stage just wrote).
@@ -367,9 +322,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
             const V3 o = mk(ro.x, ro.y, ro.z), d = mk(rd.x, rd.y, rd.z);
             V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
             const uint32_t bits = __float_as_uint(h.w);
-            if (bits == B200RT_WF_DEAD) {
-                // clamped at the end of the previous bounce (wf_trace): nothing more is added
-            } else if (bits == B200RT_WF_MISS) {
+            if (bits == B200RT_WF_MISS) {
                 V3 bg = ld3(sc.bg);
                 if (HW8 && sc.env) {
                     const float tx = 0.5f + 0.5f * atan2f(d.z, d.x) * 0.318309886183791f;
@@ -456,10 +409,14 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
             if (!active) {
                 const int idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) {
+                    // `filtered`: the entry carries the pierced-cut mask above bit 26 (the host packs it only for waves
+                    // below 2^26 slots); otherwise the entry IS the slot and must not be masked (a frame above 67 M
+                    // pixels has slots >= 2^26: masking aliased them onto low slots)
+                    const uint32_t slot_mask = filtered ? (1u << B200RT_WF_MASK_SHIFT) - 1u : 0xFFFFFFFFu;
                     const uint32_t entry = (uint32_t)__ldcs(q_in + idx);
-                    p = (int)(entry & ((1u << B200RT_WF_MASK_SHIFT) - 1u));
+                    p = (int)(entry & slot_mask);
 #if B200RT_REFILL_PF
-                    const int ahead = idx + B200RT_REFILL_PF < n ? (int)((uint32_t)__ldcs(q_in + idx + B200RT_REFILL_PF) & ((1u << B200RT_WF_MASK_SHIFT) - 1u)) : -1;
+                    const int ahead = idx + B200RT_REFILL_PF < n ? (int)((uint32_t)__ldcs(q_in + idx + B200RT_REFILL_PF) & slot_mask) : -1;
 #endif
                     const float4 ro = ld_state(&wb.ray_o[p]), rd = ld_state(&wb.ray_d[p]);
 #if B200RT_REFILL_PF

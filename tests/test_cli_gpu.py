@@ -59,8 +59,8 @@ def test_cli_hw5_and_hw3_text_scenes(tmp_path):
 
 
 def test_cli_multi_gpu_sample_split(tmp_path):
-    if rt.device_lib().b200rt_device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    """B200RT_GPUS=2: two contexts behind b200rt_group (on two GPUs when the box has them, else sharing device 0 --
+    the same code path: replication, sample split, fused peer reduce + resolve)."""
     a, b = tmp_path / "a.ppm", tmp_path / "b.ppm"
     args = [os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), "128", "96", "64"]
     subprocess.run([RUN] + args + [str(a)], check=True, capture_output=True)
@@ -72,3 +72,24 @@ def test_cli_multi_gpu_sample_split(tmp_path):
 def test_cli_usage_and_missing_file(tmp_path):
     assert subprocess.run([RUN]).returncode == 2
     assert subprocess.run([RUN, str(tmp_path / "nope.txt"), str(tmp_path / "o.ppm")], capture_output=True).returncode == 1
+
+
+def test_cli_png_and_pfm_outputs(tmp_path):
+    """Output container by file name: .png decodes (own decoder) to the PPM's bytes, .pfm holds sum / spp as floats."""
+    import ctypes
+    args = [os.path.join(ou.SCENES, "hw8/sphere_emissive.gltf"), "64", "48", "8"]
+    ppm, png, pfm = tmp_path / "o.ppm", tmp_path / "o.png", tmp_path / "o.pfm"
+    for o in (ppm, png, pfm):
+        subprocess.run([RUN] + args + [str(o)], check=True, capture_output=True)
+    ref = ou.parse_ppm(ppm.read_bytes())
+    sc = rt.load_scene(args[0], width=64, height=48, samples=8)     # only to reach the host library's PNG decoder
+    sc.set_env_map(str(png))
+    env = sc.desc.env_map.contents
+    assert (env.width, env.height) == (64, 48)
+    got = np.ctypeslib.as_array(env.rgb, shape=(48, 64, 3))
+    assert np.array_equal(got, ref)
+    raw = pfm.read_bytes()
+    head, body = raw.split(b"\n", 3)[:3], raw.split(b"\n", 3)[3]
+    assert head == [b"PF", b"64 48", b"-1.0"]
+    mean = np.frombuffer(body, "<f4").reshape(48, 64, 3)[::-1]
+    assert np.array_equal(ou.port_resolve(mean * 8, 8), ref) or ou.compare_u8(ou.port_resolve(mean * 8, 8), ref)["within1"] >= 0.999

@@ -206,8 +206,7 @@ def test_dark_rays_are_dropped_without_changing_the_image(path, monkeypatch):
     port = ou.port_render(sc, 1, want_counters=True)
     out = {}
     for drop in ("1", "0"):
-        monkeypatch.setenv("B200RT_WF_DROP_DARK", drop)
-        r = rt.Renderer()
+        r = rt.Renderer(flags=0 if drop == "1" else rt.FLAG_KEEP_DARK_RAYS)
         out[drop] = (_render(r, sc), int(r.stats()["rays"]))
         r.close()
     assert np.array_equal(out["1"][0], out["0"][0])
@@ -222,8 +221,7 @@ def test_implicit_camera_state_is_the_stored_one(w, h, monkeypatch):
     sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=w, height=h, samples=8)
     out = {}
     for v in ("1", "0"):
-        monkeypatch.setenv("B200RT_WF_FIRST_IMPLICIT", v)
-        r = rt.Renderer()
+        r = rt.Renderer(flags=0 if v == "1" else rt.FLAG_EXPLICIT_CAMERA_STATE)
         out[v] = (_render(r, sc), r.stats()["rays"])
         r.close()
     assert np.array_equal(out["1"][0], out["0"][0]) and out["1"][1] == out["0"][1]
@@ -503,3 +501,92 @@ def test_errors_are_reported_not_thrown(renderer):
     renderer.upload(sc)
     with pytest.raises(rt.B200rtError):
         renderer.render(4, 4)          # empty sample range
+
+
+# ---- several GPUs behind the library (b200rt_group_*, fused peer reduce + resolve) -----------------------------
+@pytest.mark.parametrize("w,h,members", [(128, 96, 2), (101, 67, 3)])
+def test_group_on_one_device_equals_one_context(w, h, members):
+    """Members sharing device 0 take the multi-GPU path (replication, sample split by global index, ONE kernel that
+    sums the members' buffers in member order and resolves): the frame sum is EXACTLY own + peer1 + ... in float32,
+    its bytes are exactly the single-context resolve of that sum, and they agree with a one-context render of the same
+    samples up to float summation order.  101 x 67 x 3 floats is not a multiple of four: the scalar tail runs."""
+    sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=w, height=h, samples=12)
+    g = rt.Group([0] * members)
+    assert len(g) == members
+    g.upload(sc)
+    g.render(0, 12)
+    total = g.download_accum()
+    parts = [g.member_accum(i) for i in range(members)]
+    expect = parts[0].copy()
+    for p_ in parts[1:]:
+        expect += p_
+    assert np.array_equal(total, expect) and all(p_.max() > 0 for p_ in parts)
+    img = g.resolve(12)
+    one = rt.Renderer()
+    one.upload(sc)
+    one.render(0, 12)
+    single = one.download_accum()
+    assert np.allclose(total, single, rtol=1e-5, atol=1e-6)
+    one.upload_accum(total)
+    assert np.array_equal(one.resolve(12), img)
+    st = g.stats()
+    assert st["paths"] == w * h * 12
+    one.close(); g.close()
+
+
+def test_group_text_scene_and_deterministic_modes():
+    """hw4 text scenes upload per member and split samples; hw2 (one sample per pixel) renders on member 0 alone and
+    the others contribute zero buffers: bytes equal the single-context frame exactly."""
+    sc = ou.load_scene(os.path.join(S, "hw4/practice3_1.txt"), width=96, height=64, samples=8)
+    g = rt.Group([0, 0])
+    g.upload(sc); g.render(0, 8)
+    one = rt.Renderer(); one.upload(sc); one.render(0, 8)
+    assert np.allclose(g.download_accum(), one.download_accum(), rtol=1e-5, atol=1e-6)
+    sc2 = ou.load_scene(os.path.join(S, "hw2/sample.txt"))
+    g.upload(sc2); g.render()
+    one.upload(sc2); one.render()
+    assert np.array_equal(g.resolve(1), one.resolve(1))
+    one.close(); g.close()
+
+
+# ---- the product's default load: no trees in the description ----------------------------------------------------
+@pytest.mark.parametrize("path,mode", [("hw7/practice7_4.gltf", 0), ("hw8/sphere_emissive.gltf", 0), ("hw7/practice7_1.gltf", 6)])
+def test_default_load_without_trees_matches_port_on_same_stream(path, mode):
+    """b200rt_host_load_gltf delivers triangles in file order and no trees; the library builds its own, the port
+    traverses private ones (oracle/port_mc.cpp) and samples lights in the description's order: same Philox stream,
+    same image up to edge ties; ray counts equal within 0.2 %."""
+    sc = rt.load_scene(os.path.join(S, path), width=128, height=96, samples=16, mode=mode)
+    assert sc.desc.n_nodes == 0 and not sc.desc.nodes and not sc.desc.light_nodes
+    r = rt.Renderer()
+    acc = _render(r, sc)
+    rays = int(r.stats()["rays"])
+    r.close()
+    port = ou.port_render(sc, 1, want_counters=True)
+    p = port["accum"]
+    d = np.abs(acc - p).max(axis=2) / 16
+    ok = (d <= 5e-2 * (np.abs(p).max(axis=2) / 16 + 1e-2)).mean()
+    assert ok >= 0.9, ok
+    assert abs(acc.mean() - p.mean()) <= 2e-2 * p.mean()
+    assert abs(rays - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0])
+
+
+def test_reference_bvh_flag_needs_the_description_trees():
+    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=16, height=16, samples=1)
+    r = rt.Renderer(flags=rt.FLAG_REFERENCE_BVH)
+    with pytest.raises(rt.B200rtError):
+        r.upload(sc)
+    r.close()
+
+
+def test_hw7_file_loads_under_hw8_rules_with_generated_attributes():
+    """hw8/src/sceneio.cpp:88-93 reads TANGENT and TEXCOORD_0 unconditionally; practice7_1.gltf has neither.  The loader
+    generates them (uv = 0, tangent in the normal's frame): the file renders under hw8 rules like the port."""
+    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=96, height=64, samples=16, mode=rt.MODE_HW8)
+    assert sc.mode == rt.MODE_HW8
+    r = rt.Renderer()
+    acc = _render(r, sc)
+    r.close()
+    p = ou.port_render(sc, 1)["accum"]
+    d = np.abs(acc - p).max(axis=2) / 16
+    assert (d <= 5e-2 * (np.abs(p).max(axis=2) / 16 + 1e-2)).mean() >= 0.9
+    assert abs(acc.mean() - p.mean()) <= 2e-2 * p.mean()

@@ -95,3 +95,117 @@ def test_png_decoder_matches_pil():
     mine = np.ctypeslib.as_array(img.rgb, shape=(img.height, img.width, 3))
     assert (img.height, img.width) == ref.shape[:2]
     assert np.array_equal(mine, ref)
+
+
+def test_default_gltf_load_has_no_trees_and_the_same_triangles():
+    """b200rt_host_load_gltf: no reference SAH build -- triangles in file order, light set = the emissive ones in
+    file order, nodes / light_nodes NULL.  The reference-ordered load holds the same triangles in another order."""
+    p = os.path.join(S, "hw7/practice7_4.gltf")
+    a = rt.load_scene(p, width=8, height=8, samples=1)
+    b = rt.load_scene(p, width=8, height=8, samples=1, reference_bvh=True)
+    da, db = a.desc, b.desc
+    assert da.n_nodes == 0 and not da.nodes and da.n_light_nodes == 0 and not da.light_nodes
+    assert db.n_nodes > 0 and db.nodes and db.n_light_nodes > 0
+    assert da.n_tris == db.n_tris and da.n_light_tris == db.n_light_tris > 0
+    tri_bytes = 148
+
+    def rows(ptr, n):
+        raw = ctypes.string_at(ptr, n * tri_bytes)
+        return sorted(raw[i * tri_bytes:(i + 1) * tri_bytes] for i in range(n))
+    assert rows(da.tris, da.n_tris) == rows(db.tris, db.n_tris)
+    assert rows(da.light_tris, da.n_light_tris) == rows(db.light_tris, db.n_light_tris)
+
+
+def test_port_with_private_trees_agrees_with_reference_trees():
+    """The oracle port traverses private trees when the description has none: with the light set's ORDER made equal
+    (one emitter) the two loads render the same Philox image up to tie / summation-order rounding."""
+    import oracle_util as ou
+    p = os.path.join(S, "hw7/practice7_1.gltf")
+    a = rt.load_scene(p, width=48, height=32, samples=4)
+    b = rt.load_scene(p, width=48, height=32, samples=4, reference_bvh=True)
+    ia, ib = ou.port_render(a, 1)["accum"], ou.port_render(b, 1)["accum"]
+    assert abs(ia.mean() - ib.mean()) <= 0.05 * ib.mean()
+
+
+def test_generated_tangents_are_unit_and_orthogonal_to_the_normals():
+    sc = rt.load_scene(os.path.join(S, "hw7/practice7_1.gltf"), width=8, height=8, samples=1, mode=rt.MODE_HW8)
+    d = sc.desc
+    raw = np.frombuffer(ctypes.string_at(d.tris, d.n_tris * 148), np.uint8).reshape(d.n_tris, 148)
+    f = raw[:, :144].copy().view(np.float32).reshape(d.n_tris, 36)
+    n = f[:, 15:24].reshape(-1, 3, 3)
+    t = f[:, 24:36].reshape(-1, 3, 4)
+    assert np.allclose(np.linalg.norm(t[..., :3], axis=2), 1, atol=1e-4)
+    assert np.abs((t[..., :3] * n).sum(axis=2)).max() < 1e-3
+    assert np.all(t[..., 3] == 1)
+
+
+def test_png_writer_round_trips_through_the_decoder_and_rejects_truncation(tmp_path):
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    p = tmp_path / "a.png"
+    rt.write_png(str(p), img)
+    sc = rt.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=8, height=8, samples=1)
+    sc.set_env_map(str(p))
+    env = sc.desc.env_map.contents
+    assert (env.width, env.height) == (53, 37)
+    assert np.array_equal(np.ctypeslib.as_array(env.rgb, shape=(37, 53, 3)), img)
+    # the shipped PNG (deflate with dynamic Huffman blocks) still decodes to the committed texels
+    sc.set_env_map(os.path.join(S, "hw8/sphere_emission.png"))
+    env = sc.desc.env_map.contents
+    tex = np.ctypeslib.as_array(env.rgb, shape=(env.height, env.width, 3))
+    import zlib
+    assert zlib.crc32(tex.tobytes()) == zlib.crc32(_stb_free_decode(os.path.join(S, "hw8/sphere_emission.png")).tobytes())
+    data = p.read_bytes()
+    (tmp_path / "cut.png").write_bytes(data[:len(data) // 2])
+    with pytest.raises(rt.B200rtError):
+        sc.set_env_map(str(tmp_path / "cut.png"))
+    # a header announcing a huge image over a tiny stream is rejected before any allocation
+    bad = bytearray(data)
+    bad[16:24] = (30000).to_bytes(4, "big") + (30000).to_bytes(4, "big")
+    (tmp_path / "huge.png").write_bytes(bytes(bad))
+    with pytest.raises(rt.B200rtError):
+        sc.set_env_map(str(tmp_path / "huge.png"))
+
+
+def _stb_free_decode(path):
+    """Independent PNG decode with zlib + numpy (8-bit RGB / RGBA, non-interlaced) to check the built-in decoder."""
+    import struct, zlib
+    raw = open(path, "rb").read()
+    pos, idat, w = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        if typ == b"IHDR":
+            w, h, depth, ctype = struct.unpack(">IIBB", body[:10])
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    ch = {2: 3, 6: 4, 0: 1}[ctype]
+    assert depth == 8
+    data = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, w * ch + 1)
+    out = np.zeros((h, w * ch), np.uint8)
+    prev = np.zeros(w * ch, np.int32)
+    for y in range(h):
+        ft, line = int(data[y, 0]), data[y, 1:].astype(np.int32)
+        cur = np.zeros(w * ch, np.int32)
+        if ft == 0:
+            cur = line
+        elif ft == 2:
+            cur = (line + prev) & 255
+        else:
+            for i in range(w * ch):
+                a = cur[i - ch] if i >= ch else 0
+                b = prev[i]
+                c = prev[i - ch] if i >= ch else 0
+                if ft == 1:
+                    pr = a
+                elif ft == 3:
+                    pr = (a + b) >> 1
+                else:
+                    pa, pb, pc = abs(b - c), abs(a - c), abs(a + b - 2 * c)
+                    pr = a if pa <= pb and pa <= pc else (b if pb <= pc else c)
+                cur[i] = (line[i] + pr) & 255
+        out[y] = cur
+        prev = cur
+    out = out.reshape(h, w, ch)
+    return np.repeat(out, 3, axis=2) if ch == 1 else out[:, :, :3]
