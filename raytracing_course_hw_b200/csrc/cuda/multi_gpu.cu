@@ -263,15 +263,16 @@ int b200rt_group_render(b200rt_group *g, int32_t width, int32_t height, int32_t 
     const long long S = spp_end - spp_begin, G = (long long)g->m.size();
     for (long long k = 0; k < G; k++) {
         b200rt_ctx *ctx = g->m[(size_t)k];
-        const int32_t b = spp_begin + (int32_t)(S * k / G), e = spp_begin + (int32_t)(S * (k + 1) / G);
+        // hw1 / hw2 hold ONE sample per pixel: member 0 renders it, nothing is split
+        const int32_t b = deterministic ? 0 : spp_begin + (int32_t)(S * k / G);
+        const int32_t e = deterministic ? (k == 0 ? 1 : 0) : spp_begin + (int32_t)(S * (k + 1) / G);
         int rc;
-        if (e > b && !(deterministic && k > 0)) rc = b200rt_render(ctx, width, height, b, e, ray_depth);
+        if (e > b) rc = b200rt_render(ctx, width, height, b, e, ray_depth);
         else {
-            // no samples for this member: it still contributes a (zero) buffer of the frame's size
+            // no samples for this member: it still contributes a buffer of the frame's size (zeroed when the frame
+            // size changes, by b200rt_group_clear / upload otherwise)
             CK(cudaSetDevice(ctx->device));
-            const bool fresh = ctx->acc_w != width || ctx->acc_h != height;
             rc = ensure_buffers(ctx, width, height, 0);
-            (void)fresh;
         }
         if (rc) return gfail(g, rc, "member render", ctx);
     }
