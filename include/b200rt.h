@@ -35,6 +35,7 @@ extern "C" {
 #define B200RT_ERR_NO_SCENE     -4  /* render/resolve before upload_scene                   */
 #define B200RT_ERR_UNSUPPORTED  -5  /* mode / feature not implemented on the device path    */
 #define B200RT_ERR_STACK        -6  /* BVH deeper than the traversal stack                  */
+#define B200RT_ERR_TOO_LARGE    -7  /* frame above B200RT_NOALLOC_MAX_PIXELS (b200rt_resolve_noalloc) */
 
 /* ---- scene semantics: which homework's integrator is reproduced -- */
 #define B200RT_MODE_HW1 1  /* flat-colour primary cast          hw1/src/scene.cpp:7-20      */
@@ -286,6 +287,25 @@ int b200rt_group_download_accum(b200rt_group *g, float *rgb_out);
 /* Counters summed over the members, times = the slowest member's. */
 int b200rt_group_get_stats(b200rt_group *g, b200rt_stats *out);
 const char *b200rt_group_last_error(b200rt_group *g);
+
+/* ---- no-allocation resolve ------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arithmetic and bytes as b200rt_resolve (mean, ACES, gamma, quantise) but context-free and allocation-free: the
+ * RGB8 staging buffer between the kernel and the device-to-host copy is a static __device__ array inside the library
+ * (B200RT_NOALLOC_MAX_PIXELS * 3 bytes = 6 MiB on every GPU that loads libb200rt.so, until exit) instead of a
+ * cudaMalloc'ed buffer of a context.  The call performs no cudaMalloc / cudaFree / stream or event creation.
+ *   device            CUDA device ordinal that owns accum_sum_device
+ *   stream            cudaStream_t as void* (NULL = the default stream); the call blocks until the bytes are on the host
+ *   accum_sum_device  DEVICE pointer: width * height * 3 floats, the radiance SUM (e.g. b200rt_accum_device_ptr)
+ *   total_spp, mode   as in b200rt_resolve: hw1 / hw2 hold one sample, hw1 is not tonemapped (B200RT_MODE_HWn)
+ *   rgb_out           HOST pointer, width * height * 3 bytes, top row first
+ * Frames above B200RT_NOALLOC_MAX_PIXELS pixels are rejected with B200RT_ERR_TOO_LARGE (use b200rt_resolve).
+ * The static array is shared by all calls on a device and keeps the last call's contents; no part of it has to be
+ * cleared (a call overwrites every byte it later reads), but calls that overlap on one GPU race on it: serialise them. */
+#define B200RT_NOALLOC_MAX_PIXELS (2048 * 1024)
+int b200rt_resolve_noalloc(int32_t device, void *stream, const float *accum_sum_device, int32_t width, int32_t height,
+                           int32_t total_spp, int32_t mode, uint8_t *rgb_out);
 
 /* hw1/hw2 parity aid: primitive index of the primary hit per pixel (-1 = miss), int32 W*H. */
 int b200rt_primary_ids(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t *ids_out);

@@ -130,6 +130,8 @@ def device_lib():
         L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
         L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
         L.b200rt_stream.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        L.b200rt_resolve_noalloc.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
         L.b200rt_resolve_peers.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_void_p]
         L.b200rt_reduce_peers.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32]
         L.b200rt_enable_peer.argtypes = [ctypes.c_void_p, ctypes.c_int32]
@@ -159,7 +161,7 @@ DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b20
                   "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end", "b200rt_replicate_scene",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
                   "b200rt_strerror", "b200rt_last_error", "b200rt_device_count",
-                  "b200rt_resolve_peers", "b200rt_reduce_peers", "b200rt_enable_peer", "b200rt_accum_ipc_export",
+                  "b200rt_resolve_noalloc", "b200rt_resolve_peers", "b200rt_reduce_peers", "b200rt_enable_peer", "b200rt_accum_ipc_export",
                   "b200rt_ipc_open", "b200rt_ipc_close", "b200rt_group_create", "b200rt_group_destroy", "b200rt_group_size",
                   "b200rt_group_member", "b200rt_group_upload_scene", "b200rt_group_render", "b200rt_group_clear",
                   "b200rt_group_resolve", "b200rt_group_download_accum", "b200rt_group_get_stats", "b200rt_group_last_error"]
@@ -383,6 +385,23 @@ class Renderer:
             self.close()
         except Exception:
             pass
+
+
+ERR_TOO_LARGE = -7
+NOALLOC_MAX_PIXELS = 2048 * 1024
+
+
+def resolve_noalloc(device, accum_device_ptr, width, height, total_spp, mode, stream=0, out=None):
+    """b200rt_resolve_noalloc: RGB8 of a device-resident radiance SUM buffer through the library's static scratch
+    (no context, no allocation); frames above NOALLOC_MAX_PIXELS raise B200rtError(code ERR_TOO_LARGE)."""
+    L = device_lib()
+    if out is None:
+        out = np.empty((height, width, 3), np.uint8)
+    rc = L.b200rt_resolve_noalloc(device, ctypes.c_void_p(stream), ctypes.c_void_p(accum_device_ptr), width, height,
+                                  total_spp, mode, out.ctypes.data_as(ctypes.c_void_p))
+    if rc:
+        raise B200rtError(rc, L.b200rt_strerror(rc).decode())
+    return out
 
 
 class Group:

@@ -61,7 +61,7 @@ def build_cuda(force=False, verbose=False):
         common += ["-Xptxas", "-v"]
     objs = []
     # analytic kernels: no FMA contraction (bit-exact hw1/hw2); path tracer: default FMA
-    units = (("b200rt.cu", []), ("upload.cu", []), ("scheduler.cu", []), ("multi_gpu.cu", []),
+    units = (("b200rt.cu", []), ("upload.cu", []), ("scheduler.cu", []), ("multi_gpu.cu", []), ("noalloc.cu", []),
              ("analytic_kernels.cu", ["-fmad=false"]))
     procs = []
     for src, extra in units:        # the units compile concurrently (scheduler.cu holds the big kernels)

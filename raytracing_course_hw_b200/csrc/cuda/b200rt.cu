@@ -223,6 +223,7 @@ const char *b200rt_strerror(int code) {
         case B200RT_ERR_NO_SCENE: return "no scene uploaded / nothing rendered";
         case B200RT_ERR_UNSUPPORTED: return "not implemented on the device path";
         case B200RT_ERR_STACK: return "BVH deeper than the traversal stack";
+        case B200RT_ERR_TOO_LARGE: return "frame above B200RT_NOALLOC_MAX_PIXELS: too large for the static scratch of b200rt_resolve_noalloc";
         default: return "unknown error";
     }
 }
