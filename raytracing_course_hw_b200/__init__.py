@@ -318,16 +318,22 @@ class Renderer:
         self._ck(self._L.b200rt_import_scene_begin(self._ctx, hdr, ctypes.byref(p)))
         return p.value
 
-    def import_scene_end(self, header, scene):
-        """`scene` supplies the frame metadata (the same description every rank loaded; only its upload is skipped)."""
+    def import_scene_end(self, header, scene=None, frame=None):
+        """Frame metadata comes from `scene` (a description this rank loaded too) or from `frame` =
+        (width, height, samples, mode) when only the uploading rank read the file."""
         hdr = ctypes.create_string_buffer(bytes(header), self.SCENE_IMAGE_BYTES)
         self._ck(self._L.b200rt_import_scene_end(self._ctx, hdr))
-        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
+        if scene is not None:
+            frame = (scene.width, scene.height, scene.samples, scene.mode)
+        self.width, self.height, self.samples, self.mode = frame
 
-    def replicate_from(self, other, scene):
-        """Device-to-device copy of `other`'s uploaded scene into this context (same process, any two devices)."""
+    def replicate_from(self, other, scene=None, frame=None):
+        """Device-to-device copy of `other`'s uploaded scene into this context (same process, any two devices);
+        frame metadata from `scene` or `frame` = (width, height, samples, mode)."""
         self._ck(self._L.b200rt_replicate_scene(other._ctx, self._ctx))
-        self.width, self.height, self.samples, self.mode = scene.width, scene.height, scene.samples, scene.mode
+        if scene is not None:
+            frame = (scene.width, scene.height, scene.samples, scene.mode)
+        self.width, self.height, self.samples, self.mode = frame
 
     # several GPUs, peer level (include/b200rt.h): fused reduce + resolve over peer-readable buffers
     @staticmethod

@@ -34,15 +34,17 @@ def device_bytes(ptr, n, device):
     return torch.as_tensor(_CudaBytes(ptr, n), device=device)
 
 
-def upload_replicated(renderer, scene, rank, world, device=None, src=0):
+def upload_replicated(renderer, scene, rank, world, device=None, src=0, frame=None):
     """Replicates the scene on every rank's GPU with ONE host-side upload: rank `src` runs b200rt_upload_scene (BVH
-    rebuild, record building, H2D) and broadcasts its device-resident scene blob over NCCL / NVLink; the other ranks
-    import the copy (b200rt_import_scene_*) instead of repeating the host work on cores they would have to share."""
+    build, record building, H2D) and broadcasts its device-resident scene blob over NCCL / NVLink; the other ranks
+    import the copy (b200rt_import_scene_*) instead of repeating the host work on cores they would have to share.
+    Only rank `src` needs `scene`; the others may pass None and `frame` = (width, height, samples, mode).
+    Returns the number of bytes of the device blob (what crossed PCIe on `src`)."""
     import torch
     import torch.distributed as dist
     if world == 1:
         renderer.upload(scene)
-        return
+        return renderer.export_scene()[2] if scene.mode >= 6 else 0
     nb = renderer.SCENE_IMAGE_BYTES
     hdr = torch.zeros(nb, dtype=torch.uint8, device=device)
     ptr = n = None
@@ -59,7 +61,42 @@ def upload_replicated(renderer, scene, rank, world, device=None, src=0):
             n = int.from_bytes(h[16:24], "little")        # SceneImage::bytes
         dist.broadcast(device_bytes(ptr, n, device), src=src)
     if rank != src:
-        renderer.import_scene_end(h, scene)
+        renderer.import_scene_end(h, scene, frame)
+    return n
+
+
+class PeerFrame:
+    """One process per GPU: rank 0 maps every other rank's accumulation buffer (CUDA IPC handles exchanged once, like
+    a communicator) and combines + resolves them with the library's fused peer-memory kernel (b200rt_resolve_peers):
+    the radiance buffers cross NVLink once, as loads issued by the resolving kernel -- no separate collective."""
+
+    def __init__(self, renderer, rank, world):
+        import torch.distributed as dist
+        self.r, self.rank, self.world, self.ptrs = renderer, rank, world, []
+        if world == 1:
+            return
+        handles = [None] * world
+        dist.all_gather_object(handles, renderer.accum_ipc_export() if rank != 0 else None)
+        if rank == 0:
+            self.ptrs = [renderer.ipc_open(h) for h in handles[1:]]
+
+    def resolve(self, total_spp, out=None):
+        """Call on every rank after its render: waits for all ranks' GPUs, then rank 0 reads the peers' buffers."""
+        import torch.distributed as dist
+        self.r.synchronize()
+        if self.world > 1:
+            dist.barrier()
+        img = None
+        if self.rank == 0:
+            img = self.r.resolve_peers(total_spp, self.ptrs, out) if self.world > 1 else self.r.resolve(total_spp, out)
+        if self.world > 1:
+            dist.barrier()          # the peers' buffers stay untouched until rank 0 has read them
+        return img
+
+    def close(self):
+        for p in self.ptrs:
+            self.r.ipc_close(p)
+        self.ptrs = []
 
 
 def reduce_to_rank0(buf, dst=0):

@@ -1,9 +1,13 @@
 #!/usr/bin/env python3
 """Summarise an `ncu --set full` capture (raw CSV page) of the dominant kernel into profiles/traffic.json.
 
-usage: ncu -i capture.ncu-rep --page raw --csv > raw.csv ; tools/ncu_traffic.py raw.csv wf_extend "<command that was profiled>"
-bench.py reads `dram_bytes_per_launch` from the result for roofline.traffic."""
+usage: ncu -i capture.ncu-rep --page raw --csv > raw.csv
+       tools/ncu_traffic.py raw.csv wf_extend "<command that was profiled>" [bench line .json of the same command, run without ncu]
+bench.py reads the result for roofline.traffic / roofline.limiter; `kernel_source_hash` lets it flag a capture of older
+kernels, `algorithmic_bytes_per_launch` (from the plain run's JSON line) lets it scale the DRAM bytes to other slices."""
 import csv, json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench
 
 UNIT = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
 raw, kernel, cmd = sys.argv[1], sys.argv[2], (sys.argv[3] if len(sys.argv) > 3 else "")
@@ -34,11 +38,13 @@ out = {
     "kernel": sel[0][col["Kernel Name"]],
     "command": cmd,
     "launches_captured": n,
+    "kernel_source_hash": bench.kernel_source_hash(),
+    "algorithmic_bytes_per_launch": (json.load(open(sys.argv[4]))["roofline"]["algorithmic"]["bytes_per_launch"] if len(sys.argv) > 4 else None),
     "dram_bytes_per_launch": sum(p["dram_read"] + p["dram_write"] for p in per) / n,
     "dram_read_bytes_per_launch": sum(p["dram_read"] for p in per) / n,
     "dram_write_bytes_per_launch": sum(p["dram_write"] for p in per) / n,
     "ms_per_launch_under_ncu": sum(p["ms"] for p in per) / n,
-    "per_launch": per,
+    "per_launch": per if n <= 12 else per[:12],
     "metrics_mean": {k: sum(val(r, k) for r in sel) / n for k in keep if k in col},
 }
 dst = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
