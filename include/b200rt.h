@@ -288,6 +288,26 @@ int b200rt_group_download_accum(b200rt_group *g, float *rgb_out);
 int b200rt_group_get_stats(b200rt_group *g, b200rt_stats *out);
 const char *b200rt_group_last_error(b200rt_group *g);
 
+/* ---- measurement cross-check ("N_* counted by the kernel and cross-checked against a CPU traversal of the
+ * same flattened BVH on a fixed ray set") ---------------------------------------------------------------------------
+ * Replaces nothing in the reference by itself: it exposes the traversal that replaces BVH::intersect_
+ * (hw8/src/include/bvh.h:111-142) to a checker.  b200rt_trace_rays runs the PRODUCTION closest-hit kernel (wf_extend,
+ * counting build) over n caller-supplied rays (host array, 6 floats each: origin xyz, direction xyz; t in (0, 1e4)) and
+ * returns per ray {t, u, v, bits} with bits = triangle index | inside << 31, or 0x7FFFFFFF for a miss, plus the number of
+ * child boxes and triangle records it tested.  b200rt_scene_bvh_layout / _download hand out the flattened tree exactly as
+ * it sits in device memory (32-byte sibling-pair records, 48-byte triangle records) so that
+ * oracle/pairs_traverse.c can walk the same records on the CPU.  glTF modes only. */
+typedef struct b200rt_bvh_layout {
+    uint64_t n_records, n_tris;
+    uint32_t root;            /* child word of the root (leaf flag 0x80000000 | count << 27 | first) */
+    int32_t  quant_bits;      /* 15 */
+    float    guard;           /* conservative guard band of the box test, in grid units */
+    float    base[3], scale[3], inv_scale[3];   /* world = base + q * scale */
+} b200rt_bvh_layout;
+int b200rt_trace_rays(b200rt_ctx *ctx, const float *rays, int32_t n, float *hits, uint64_t *node_tests, uint64_t *tri_tests);
+int b200rt_scene_bvh_layout(b200rt_ctx *ctx, b200rt_bvh_layout *out);
+int b200rt_scene_bvh_download(b200rt_ctx *ctx, void *records, void *tris);
+
 /* ---- no-allocation resolve ------------------------------------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -46,6 +46,13 @@ class Stats(ctypes.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class BvhLayout(ctypes.Structure):
+    """b200rt_bvh_layout (include/b200rt.h)."""
+    _fields_ = [("n_records", ctypes.c_uint64), ("n_tris", ctypes.c_uint64), ("root", ctypes.c_uint32),
+                ("quant_bits", ctypes.c_int32), ("guard", ctypes.c_float),
+                ("base", ctypes.c_float * 3), ("scale", ctypes.c_float * 3), ("inv_scale", ctypes.c_float * 3)]
+
+
 class SceneHeader(ctypes.Structure):
     """Leading scalar fields of b200rt_scene_desc (include/b200rt.h); pointers are not bound here."""
     _fields_ = [("mode", ctypes.c_int32), ("width", ctypes.c_int32), ("height", ctypes.c_int32),
@@ -130,6 +137,10 @@ def device_lib():
         L.b200rt_synchronize.argtypes = [ctypes.c_void_p]
         L.b200rt_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(Stats)]
         L.b200rt_stream.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        L.b200rt_trace_rays.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p,
+                                        ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
+        L.b200rt_scene_bvh_layout.argtypes = [ctypes.c_void_p, ctypes.POINTER(BvhLayout)]
+        L.b200rt_scene_bvh_download.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.b200rt_resolve_noalloc.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
         L.b200rt_resolve_peers.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_void_p]
@@ -161,6 +172,7 @@ DEVICE_SYMBOLS = ["b200rt_create", "b200rt_destroy", "b200rt_upload_scene", "b20
                   "b200rt_export_scene", "b200rt_import_scene_begin", "b200rt_import_scene_end", "b200rt_replicate_scene",
                   "b200rt_primary_ids", "b200rt_synchronize", "b200rt_get_stats", "b200rt_stream",
                   "b200rt_strerror", "b200rt_last_error", "b200rt_device_count",
+                  "b200rt_trace_rays", "b200rt_scene_bvh_layout", "b200rt_scene_bvh_download",
                   "b200rt_resolve_noalloc", "b200rt_resolve_peers", "b200rt_reduce_peers", "b200rt_enable_peer", "b200rt_accum_ipc_export",
                   "b200rt_ipc_open", "b200rt_ipc_close", "b200rt_group_create", "b200rt_group_destroy", "b200rt_group_size",
                   "b200rt_group_member", "b200rt_group_upload_scene", "b200rt_group_render", "b200rt_group_clear",
@@ -365,6 +377,26 @@ class Renderer:
 
     def ipc_close(self, ptr):
         self._ck(self._L.b200rt_ipc_close(self._ctx, ctypes.c_void_p(ptr)))
+
+    # measurement cross-check: the production traversal kernel on a caller's rays + the flattened tree
+    def trace_rays(self, rays):
+        """rays: (n, 6) float32 (origin, direction).  Returns (hits (n, 4) float32 {t, u, v, bits}, boxes tested,
+        triangles tested) from wf_extend's counting build."""
+        rays = np.ascontiguousarray(rays, np.float32)
+        hits = np.empty((rays.shape[0], 4), np.float32)
+        nb, nt = ctypes.c_uint64(), ctypes.c_uint64()
+        self._ck(self._L.b200rt_trace_rays(self._ctx, rays.ctypes.data_as(ctypes.c_void_p), rays.shape[0],
+                                           hits.ctypes.data_as(ctypes.c_void_p), ctypes.byref(nb), ctypes.byref(nt)))
+        return hits, nb.value, nt.value
+
+    def scene_bvh(self):
+        """(BvhLayout, records (n, 8) uint32, triangle records (n, 12) float32) exactly as they sit in device memory."""
+        lay = BvhLayout()
+        self._ck(self._L.b200rt_scene_bvh_layout(self._ctx, ctypes.byref(lay)))
+        rec = np.empty((lay.n_records, 8), np.uint32)
+        tri = np.empty((lay.n_tris, 12), np.float32)
+        self._ck(self._L.b200rt_scene_bvh_download(self._ctx, rec.ctypes.data_as(ctypes.c_void_p), tri.ctypes.data_as(ctypes.c_void_p)))
+        return lay, rec, tri
 
     def primary_ids(self):
         out = np.empty((self.height, self.width), np.int32)

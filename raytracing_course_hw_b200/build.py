@@ -119,6 +119,11 @@ def build_oracle(force=False):
     deps = srcs + [os.path.join(ORACLE, "port_common.h"), os.path.join(ORACLE, "port_figures.inl")] + _all_under(INC, (".h",))
     if force or _newer(deps, out):
         _run([GXX, "-O3", "-DNDEBUG", "-std=c++17", "-fopenmp", "-fPIC", "-shared", "-Wall", "-Wextra"] + srcs + ["-o", out])
+    # CPU walk of the flattened device BVH (SURVEY 8d counter cross-check): plain C, no FMA contraction
+    pt_src, pt_out = os.path.join(ORACLE, "pairs_traverse.c"), os.path.join(ref_out, "liboracle_pairs.so")
+    if force or _newer([pt_src], pt_out):
+        _run([os.environ.get("B200RT_CC", "/usr/bin/gcc"), "-O2", "-ffp-contract=off", "-std=c11", "-fPIC", "-shared", "-Wall", "-Wextra",
+              pt_src, "-lm", "-o", pt_out])
     _run(["bash", os.path.join(ORACLE, "build_ref.sh")])
     return out
 

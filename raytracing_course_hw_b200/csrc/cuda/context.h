@@ -30,6 +30,7 @@ struct b200rt_ctx {
     char *arena_dev = nullptr, *arena_pin = nullptr;
     size_t arena_cap = 0, arena_used = 0;     // arena_used / n_materials: what b200rt_export_scene hands out
     int n_materials = 0;
+    uint64_t n_pairs = 0, n_dtris = 0;        // records of the scene BVH / triangle records in the arena (b200rt_scene_bvh_*)
     float *lut_srgb = nullptr;
     RebuiltBvh own_bvh;                      // host scratch of the BVH rebuild (bvh_rebuild.h)
     std::vector<b200rt_triangle> own_tris;   // triangles in the rebuilt tree's order
@@ -106,3 +107,4 @@ void free_scene_memory(b200rt_ctx *c);
 // scheduler.cu
 void free_wave(b200rt_ctx *c);
 int ensure_buffers(b200rt_ctx *ctx, int w, int h, int n_slabs);
+int ensure_wave(b200rt_ctx *ctx, size_t slots);

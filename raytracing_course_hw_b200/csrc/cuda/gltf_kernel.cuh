@@ -83,7 +83,7 @@ struct QRay {
     uint32_t sx, sy, sz;   // PRMT selector of the NEAR plane of each axis (far = near ^ B200RT_SEL_FLIP)
 };
 __device__ __forceinline__ float safe_rcp(float d) {
-    const float r = 1.f / d;
+    const float r = __fdiv_rn(1.f, d);
     return fabsf(r) < 1e30f ? r : copysignf(1e30f, d);
 }
 // u16 -> float without the conversion pipe: one PRMT splices a half of the record word into a float.
@@ -102,20 +102,27 @@ __device__ __forceinline__ float q16(uint32_t w, uint32_t sel) { return __uint_a
 #define B200RT_SEL_FLIP 0x0022u
 __device__ __forceinline__ float q16(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.f; }
 #endif
+// Every operation is an explicitly rounded one (no FMA contraction left to the compiler): oracle/pairs_traverse.c
+// restates this function on the CPU and must get the same planes bit for bit (SURVEY 8d counter cross-check).
+__device__ __forceinline__ float qray_axis(float o, float d, float base, float scale, float inv_scale, float &bn, float &bf) {
+    const float oq = __fmul_rn(__fsub_rn(o, base), inv_scale);
+    const float ig = __fmul_rn(scale, safe_rcp(d));
+    const float c = -__fmul_rn(oq, ig);
+    const float g = __fmul_rn(B200RT_QEPS, fabsf(ig));
+    bn = __fsub_rn(c, g); bf = __fadd_rn(c, g);
+#if B200RT_QBITS == 15
+    const float off = __fmul_rn(32768.f, ig);      // exact (power of two)
+    bn = __fsub_rn(bn, off); bf = __fsub_rn(bf, off);
+    return __fmul_rn(65536.f, ig);
+#else
+    return ig;
+#endif
+}
 __device__ __forceinline__ QRay make_qray(const DQuant &q, const V3 o, const V3 d) {
     QRay r;
-    const V3 oq = mk((o.x - q.base[0]) * q.inv_scale[0], (o.y - q.base[1]) * q.inv_scale[1], (o.z - q.base[2]) * q.inv_scale[2]);
-    const V3 ig = mk(q.scale[0] * safe_rcp(d.x), q.scale[1] * safe_rcp(d.y), q.scale[2] * safe_rcp(d.z));
-    const V3 c = mk(-oq.x * ig.x, -oq.y * ig.y, -oq.z * ig.z);
-    const V3 g = mk(B200RT_QEPS * fabsf(ig.x), B200RT_QEPS * fabsf(ig.y), B200RT_QEPS * fabsf(ig.z));
-    r.bn = c - g; r.bf = c + g;
-#if B200RT_QBITS == 15
-    r.inv = 65536.f * ig;
-    const V3 off = 32768.f * ig;
-    r.bn = r.bn - off; r.bf = r.bf - off;
-#else
-    r.inv = ig;
-#endif
+    r.inv.x = qray_axis(o.x, d.x, q.base[0], q.scale[0], q.inv_scale[0], r.bn.x, r.bf.x);
+    r.inv.y = qray_axis(o.y, d.y, q.base[1], q.scale[1], q.inv_scale[1], r.bn.y, r.bf.y);
+    r.inv.z = qray_axis(o.z, d.z, q.base[2], q.scale[2], q.inv_scale[2], r.bn.z, r.bf.z);
     r.sx = d.x < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
     r.sy = d.y < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
     r.sz = d.z < 0.f ? B200RT_SEL_HI : B200RT_SEL_LO;
@@ -166,21 +173,27 @@ __device__ __forceinline__ void pair_test(const DPair *nodes, uint32_t idx, cons
 // -- three out of four at the leaves -- costs no reciprocal.  Accepts 0 <= u, 0 <= v, u + v <= 1, 0 < t < tmax
 // (intersectPlaneAndRay + the inside test of hw8/src/primitives.cpp:18-27, 85-108, up to rounding at the edges);
 // det = 0 or NaN rejects.  `det` keeps its sign: det > 0 means the ray runs along the reference's normal ("inside").
+// Every operation below is explicitly rounded / explicitly fused: the same bits come out of every kernel this is inlined
+// into (the compiler's own FMA contraction differed between kernels) and out of oracle/pairs_traverse.c on the CPU.
+__device__ __forceinline__ float dot_p(const V3 a, const V3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, __fmul_rn(a.x, b.x))); }
+__device__ __forceinline__ V3 cross_p(const V3 a, const V3 b) {
+    return mk(fmaf(a.y, b.z, -__fmul_rn(a.z, b.y)), fmaf(a.z, b.x, -__fmul_rn(a.x, b.z)), fmaf(a.x, b.y, -__fmul_rn(a.y, b.x)));
+}
 __device__ __forceinline__ bool tri_hit(const float4 v0, const float4 e1, const float4 e2, const V3 o, const V3 d, const float tmax,
                                         float &t, float &u, float &v, float &det) {
     const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-    const V3 pv = cross(d, E2);
-    det = dot(E1, pv);
-    const V3 tv = mk(o.x - v0.x, o.y - v0.y, o.z - v0.z);
-    const V3 qv = cross(tv, E1);
+    const V3 pv = cross_p(d, E2);
+    det = dot_p(E1, pv);
+    const V3 tv = mk(__fsub_rn(o.x, v0.x), __fsub_rn(o.y, v0.y), __fsub_rn(o.z, v0.z));
+    const V3 qv = cross_p(tv, E1);
     const uint32_t sb = __float_as_uint(det) & 0x80000000u;
     const float ad = fabsf(det);
-    const float un = __uint_as_float(__float_as_uint(dot(tv, pv)) ^ sb);
-    const float vn = __uint_as_float(__float_as_uint(dot(d, qv)) ^ sb);
-    const float tn = __uint_as_float(__float_as_uint(dot(E2, qv)) ^ sb);
-    if (!(un >= 0.f && vn >= 0.f && un + vn <= ad && tn > 0.f && tn < tmax * ad)) return false;
-    const float idet = 1.f / ad;
-    t = tn * idet; u = un * idet; v = vn * idet;
+    const float un = __uint_as_float(__float_as_uint(dot_p(tv, pv)) ^ sb);
+    const float vn = __uint_as_float(__float_as_uint(dot_p(d, qv)) ^ sb);
+    const float tn = __uint_as_float(__float_as_uint(dot_p(E2, qv)) ^ sb);
+    if (!(un >= 0.f && vn >= 0.f && __fadd_rn(un, vn) <= ad && tn > 0.f && tn < __fmul_rn(tmax, ad))) return false;
+    const float idet = __fdiv_rn(1.f, ad);
+    t = __fmul_rn(tn, idet); u = __fmul_rn(un, idet); v = __fmul_rn(vn, idet);
     return true;
 }
 
@@ -222,6 +235,28 @@ __device__ __forceinline__ void trace_closest(const DGltfScene &sc, const V3 o, 
     }
 }
 
+// One emitter's term of FiguresMix::getTotalPdf for a ray that hits it at parameter t with barycentrics (u, v):
+// pointProb * |x - y|^2 / |d . n_y|, n_y = the interpolated shading normal (hw8 distributions.h:140-145) or the geometric
+// normal (hw7 :145).  Written ONCE with explicitly rounded / fused operations: wf_light and the megakernel's
+// light_pdf_sum must add the same bits (their images are compared bit for bit).
+__device__ __forceinline__ float light_term(const DGltfScene &sc, uint32_t i, const float4 v0, const float4 e1, const float4 e2,
+                                            const V3 d, float t, float u, float v) {
+    V3 yn;
+    if (sc.hw8) {
+        const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);
+        const float4 n0 = __ldg(nq), n1 = __ldg(nq + 1), n2 = __ldg(nq + 2);
+        yn = mk(fmaf(v, __fsub_rn(n1.x, n2.x), fmaf(u, __fsub_rn(n0.x, n2.x), n2.x)),
+                fmaf(v, __fsub_rn(n1.y, n2.y), fmaf(u, __fsub_rn(n0.y, n2.y), n2.y)),
+                fmaf(v, __fsub_rn(n1.z, n2.z), fmaf(u, __fsub_rn(n0.z, n2.z), n2.z)));
+    } else {
+        yn = cross_p(mk(e2.x, e2.y, e2.z), mk(e1.x, e1.y, e1.z));
+    }
+    const float il = rsqrtf(dot_p(yn, yn));
+    yn = mk(__fmul_rn(il, yn.x), __fmul_rn(il, yn.y), __fmul_rn(il, yn.z));
+    const V3 td = mk(__fmul_rn(t, d.x), __fmul_rn(t, d.y), __fmul_rn(t, d.z));      // y - x
+    return __fdiv_rn(__fmul_rn(v0.w, dot_p(td, td)), fabsf(dot_p(d, yn)));
+}
+
 // FiguresMix::getTotalPdf (distributions.h:122-165): every emissive triangle whose box the ray
 // (x, d) pierces contributes pointProb * |x-y|^2 / |d . n_y|; NO distance pruning.
 template <bool COUNT>
@@ -257,22 +292,7 @@ __device__ __forceinline__ float light_pdf_sum(const DGltfScene &sc, const V3 o,
                 const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                 if (COUNT) tc.light_tri_tests++;
                 float t, u, v, det;
-                if (tri_hit(v0, e1, e2, o, d, B200RT_TMAX, t, u, v, det)) {
-                    const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-                    V3 yn;
-                    if (sc.hw8) {   // interpolated shading normal of the emitter (hw8 distributions.h:140-145)
-                        const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);
-                        const float4 n0 = __ldg(nq), n1 = __ldg(nq + 1), n2 = __ldg(nq + 2);
-                        yn = normalize(mk(n2.x + u * (n0.x - n2.x) + v * (n1.x - n2.x),
-                                          n2.y + u * (n0.y - n2.y) + v * (n1.y - n2.y),
-                                          n2.z + u * (n0.z - n2.z) + v * (n1.z - n2.z)));
-                    } else {        // geometric normal (hw7 distributions.h:145)
-                        yn = normalize(cross(E2, E1));
-                    }
-                    // |x - y|^2 with y = x + t d
-                    const V3 td = t * d;
-                    total += v0.w * len2(td) / fabsf(dot(d, yn));
-                }
+                if (tri_hit(v0, e1, e2, o, d, B200RT_TMAX, t, u, v, det)) total = __fadd_rn(total, light_term(sc, i, v0, e1, e2, d, t, u, v));
             }
         }
         if (sp == 0) break;

@@ -270,6 +270,81 @@ int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_be
     return B200RT_OK;
 }
 
+// ---- SURVEY 8(d) cross-check aid: the production closest-hit kernel on a caller-supplied ray set ----------------
+namespace {
+__global__ void load_rays_kernel(const float *__restrict__ rays, int n, const WaveBuffers wb) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *r = rays + (size_t)i * 6;
+    wb.ray_o[i] = make_float4(r[0], r[1], r[2], 0.f);
+    wb.ray_d[i] = make_float4(r[3], r[4], r[5], 0.f);
+    wb.queue[0][i] = i;
+    if (i == 0) wb.ctr[-1] = n;
+}
+__global__ void store_hits_kernel(float4 *__restrict__ out, int n, const WaveBuffers wb) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = wb.hit[i];
+}
+}  // namespace
+
+int b200rt_trace_rays(b200rt_ctx *ctx, const float *rays, int32_t n, float *hits, uint64_t *node_tests, uint64_t *tri_tests) {
+    if (!ctx || !rays || !hits || n <= 0) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "trace_rays before upload_scene");
+    if (ctx->desc.mode < B200RT_MODE_HW6) return fail(ctx, B200RT_ERR_UNSUPPORTED, "ray queries exist for the glTF modes only");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    int rc = ensure_wave(ctx, (size_t)n);
+    if (rc) return rc;
+    const WaveBuffers &wb = ctx->wave[0];
+    // device staging for the rays and the hits (a test / measurement entry point, not a hot path: plain cudaMalloc)
+    float *d_rays = nullptr;
+    float4 *d_hits = nullptr;
+    CK(cudaMalloc(&d_rays, (size_t)n * 6 * sizeof(float)));
+    if (cudaMalloc(&d_hits, (size_t)n * sizeof(float4)) != cudaSuccess) { cudaFree(d_rays); return fail(ctx, B200RT_ERR_CUDA, "cudaMalloc"); }
+    cudaStream_t st = ctx->stream;
+    auto done = [&](int code) { cudaFree(d_rays); cudaFree(d_hits); return code; };
+    if (cudaMemcpyAsync(d_rays, rays, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemsetAsync(ctx->counters, 0, sizeof(DCounters), st) != cudaSuccess ||
+        cudaMemsetAsync(wb.ctr - 4, 0, 4 * 66 * sizeof(int), st) != cudaSuccess)
+        return done(fail(ctx, B200RT_ERR_CUDA, "trace_rays staging"));
+    load_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rays, n, wb);
+    int nb = 0;
+    if (!ctx->num_sms) cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wf_extend<true>, 128, 0);
+    const int blocks = std::max(1, nb) * std::max(1, ctx->num_sms);
+    int *c = wb.ctr;
+    wf_extend<true><<<blocks, 128, 0, st>>>(ctx->gs, wb, wb.queue[0], c - 1, c + 0, ctx->counters, ctx->wf_batch, ctx->wf_leaf_t, 0, 0.f, 0.f, 0.f);
+    store_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_hits, n, wb);
+    DCounters cnt;
+    if (cudaGetLastError() != cudaSuccess ||
+        cudaMemcpyAsync(hits, d_hits, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaMemcpyAsync(&cnt, ctx->counters, sizeof(cnt), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess)
+        return done(fail(ctx, B200RT_ERR_CUDA, "trace_rays launch", cudaGetLastError()));
+    if (node_tests) *node_tests = cnt.node_tests;
+    if (tri_tests) *tri_tests = cnt.tri_tests;
+    return done(B200RT_OK);
+}
+
+int b200rt_scene_bvh_layout(b200rt_ctx *ctx, b200rt_bvh_layout *out) {
+    if (!ctx || !out) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene || ctx->desc.mode < B200RT_MODE_HW6) return fail(ctx, B200RT_ERR_NO_SCENE, "no glTF-mode scene uploaded");
+    out->n_records = ctx->n_pairs; out->n_tris = ctx->n_dtris; out->root = ctx->gs.root;
+    out->quant_bits = B200RT_QBITS; out->guard = B200RT_QEPS;
+    for (int k = 0; k < 3; k++) { out->base[k] = ctx->gs.q.base[k]; out->scale[k] = ctx->gs.q.scale[k]; out->inv_scale[k] = ctx->gs.q.inv_scale[k]; }
+    return B200RT_OK;
+}
+
+int b200rt_scene_bvh_download(b200rt_ctx *ctx, void *records, void *tris) {
+    if (!ctx || !records || !tris) return B200RT_ERR_INVALID;
+    if (!ctx->has_scene || ctx->desc.mode < B200RT_MODE_HW6) return fail(ctx, B200RT_ERR_NO_SCENE, "no glTF-mode scene uploaded");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(records, ctx->gs.nodes, ctx->n_pairs * sizeof(DPair), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(tris, ctx->gs.tris, ctx->n_dtris * sizeof(DTri), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return B200RT_OK;
+}
+
 int b200rt_get_stats(b200rt_ctx *ctx, b200rt_stats *out) {
     if (!ctx || !out) return B200RT_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));

@@ -451,6 +451,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     ctx->lut_srgb = reinterpret_cast<float *>(dev + o_lut);
     ctx->gs = g;
     ctx->arena_used = off; ctx->n_materials = (int)nm;
+    ctx->n_pairs = n_pairs; ctx->n_dtris = nt;
     lap("materials, lut, copy");
     return B200RT_OK;
 }
@@ -557,6 +558,7 @@ namespace {
 struct SceneImage {
     uint64_t magic, base, bytes, lut;
     int32_t n_materials, pad;
+    uint64_t n_pairs, n_dtris;
     DGltfScene gs;
     b200rt_scene_desc desc;      // scalars only (pointers nulled)
 };
@@ -584,6 +586,7 @@ int b200rt_export_scene(b200rt_ctx *ctx, b200rt_scene_image *hdr, void **device_
     SceneImage im{};
     im.magic = kSceneMagic; im.base = (uint64_t)(uintptr_t)ctx->arena_dev; im.bytes = ctx->arena_used;
     im.lut = (uint64_t)(uintptr_t)ctx->lut_srgb; im.n_materials = ctx->n_materials;
+    im.n_pairs = ctx->n_pairs; im.n_dtris = ctx->n_dtris;
     im.gs = ctx->gs; im.desc = ctx->desc;
     memcpy(hdr, &im, sizeof(im));
     *device_blob = ctx->arena_dev;
@@ -623,6 +626,7 @@ int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr) {
     ctx->gs = g;
     ctx->lut_srgb = reinterpret_cast<float *>(reinterpret_cast<char *>((uintptr_t)im.lut) + delta);
     ctx->arena_used = (size_t)im.bytes; ctx->n_materials = im.n_materials;
+    ctx->n_pairs = im.n_pairs; ctx->n_dtris = im.n_dtris;
     ctx->hw5_has_tris = false; ctx->hw5_n_lights = 0;
     ctx->desc = im.desc;
     ctx->has_scene = true;

@@ -463,21 +463,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                         const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                         if (COUNT) tri_tests++;
                         float t, u, v, det;
-                        if (tri_hit(v0, e1, e2, o, d, B200RT_TMAX, t, u, v, det)) {
-                            const V3 E1 = mk(e1.x, e1.y, e1.z), E2 = mk(e2.x, e2.y, e2.z);
-                            V3 yn;
-                            if (sc.hw8) {
-                                const float4 *nq = reinterpret_cast<const float4 *>(sc.light_normals + i);
-                                const float4 n0 = __ldg(nq), n1 = __ldg(nq + 1), n2 = __ldg(nq + 2);
-                                yn = normalize(mk(n2.x + u * (n0.x - n2.x) + v * (n1.x - n2.x),
-                                                  n2.y + u * (n0.y - n2.y) + v * (n1.y - n2.y),
-                                                  n2.z + u * (n0.z - n2.z) + v * (n1.z - n2.z)));
-                            } else {
-                                yn = normalize(cross(E2, E1));
-                            }
-                            const V3 td = t * d;
-                            total += v0.w * len2(td) / fabsf(dot(d, yn));
-                        }
+                        if (tri_hit(v0, e1, e2, o, d, B200RT_TMAX, t, u, v, det)) total = __fadd_rn(total, light_term(sc, i, v0, e1, e2, d, t, u, v));
                     }
                     pop = true;
                 }

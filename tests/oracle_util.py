@@ -39,6 +39,40 @@ def load_scene(path, **kw):
     return rt.load_scene(path, **kw)
 
 
+def room_scene(tris=20000):
+    """Textured, normal-mapped, emissive synthetic room of the bench scene's family (tools/make_scene.py, seed 1):
+    generated on demand (deterministic), never committed."""
+    import sys
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import make_scene
+    d = os.path.join(tempfile.gettempdir(), f"b200rt_test_room_{tris}_{os.getuid()}")
+    if not os.path.exists(os.path.join(d, "b200room.gltf")):
+        make_scene.build(d, tris, 1)
+    return os.path.join(d, "b200room.gltf")
+
+
+def room_digest(gltf_path):
+    """sha256 over the generated scene's geometry + the DECODED texels of its images (PNG compression may differ
+    between zlib builds; the texels may not)."""
+    import hashlib
+    import raytracing_course_hw_b200 as rt
+    h = hashlib.sha256()
+    d = os.path.dirname(gltf_path)
+    h.update(open(os.path.join(d, "b200room.bin"), "rb").read())
+    sc = rt.load_scene(gltf_path, width=4, height=4, samples=1)
+    desc = sc.desc
+    for i in range(desc.n_images):
+        im = desc.images[i]
+        h.update(ctypes.string_at(im.rgb, im.width * im.height * 3))
+    return h.hexdigest()
+
+
+def room_matches_golden(gltf_path):
+    p = os.path.join(GOLDEN, "hw8_room20k.sha")
+    return os.path.exists(p) and open(p).read().strip() == room_digest(gltf_path)
+
+
 def port_render(scene, rng_kind, seed=0, spp_begin=0, spp_end=None, want_counters=False):
     """rng_kind 0 = reference minstd stream, 1 = Philox stream of the CUDA kernels."""
     h, w = scene.height, scene.width
@@ -54,6 +88,32 @@ def port_render(scene, rng_kind, seed=0, spp_begin=0, spp_end=None, want_counter
                                   counters.ctypes.data_as(ctypes.c_void_p) if want_counters else None)
     assert rc == 0, f"oracle_render rc={rc}"
     return {"accum": accum, "rgb": rgb, "ids": ids, "counters": counters}
+
+
+_pairs = None
+
+
+def pairs_traverse(layout, records, tris, rays):
+    """CPU walk of the flattened device BVH (oracle/pairs_traverse.c).  Returns (hits (n, 4), per-ray (n, 2) uint32
+    {boxes, triangles tested}, total boxes, total triangles)."""
+    global _pairs
+    if _pairs is None:
+        path = os.path.join(REF_DIR, "liboracle_pairs.so")
+        if not os.path.exists(path):
+            from raytracing_course_hw_b200 import build
+            build.build_oracle()
+        _pairs = ctypes.CDLL(path)
+        _pairs.pairs_traverse.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int] + [ctypes.c_void_p] * 3
+    rays = np.ascontiguousarray(rays, np.float32)
+    n = rays.shape[0]
+    hits = np.empty((n, 4), np.float32)
+    per = np.zeros((n, 2), np.uint32)
+    counts = np.zeros(2, np.uint64)
+    rc = _pairs.pairs_traverse(ctypes.byref(layout), records.ctypes.data_as(ctypes.c_void_p), tris.ctypes.data_as(ctypes.c_void_p),
+                               rays.ctypes.data_as(ctypes.c_void_p), n, hits.ctypes.data_as(ctypes.c_void_p),
+                               per.ctypes.data_as(ctypes.c_void_p), counts.ctypes.data_as(ctypes.c_void_p))
+    assert rc == 0, f"pairs_traverse rc={rc}"
+    return hits, per, int(counts[0]), int(counts[1])
 
 
 def port_resolve(accum_sum, total_spp):

@@ -10,6 +10,7 @@
  * K5 resolve bytes against the port's resolve of the same float buffer;
  * size-independent properties at large sizes: sample ranges add up, determinism, seeds differ.
 """
+import ctypes
 import os
 
 import numpy as np
@@ -33,6 +34,62 @@ def renderer(request):
     r.megakernel = request.param == "megakernel"
     yield r
     r.close()
+
+
+BIG = os.path.join(ou.REF_DIR, "scenes")        # the reference's large example scenes (copied by oracle/build_ref.sh)
+
+
+def _scene_file(name):
+    """Fixture name -> path; None when an optional large scene is not on this machine."""
+    if name == "room20k":
+        return ou.room_scene(20000)
+    if name == "bench268k":
+        import sys
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import bench
+        return bench.scene_path(270000)
+    if name.startswith("big:"):
+        p = os.path.join(BIG, name[4:])
+        return p if os.path.exists(p) else None
+    return os.path.join(S, name)
+
+
+def _primary_material(sc):
+    """(H, W) material id of the primary hit through each pixel centre (-1 = miss), from the production traversal
+    kernel (b200rt_trace_rays) and the material ids stored in the device's triangle records."""
+    d, H, W = sc.desc, sc.height, sc.width
+    pos, right, up, fwd = (np.array(list(v), np.float32) for v in (d.cam_pos, d.cam_right, d.cam_up, d.cam_forward))
+    ty = np.tan(d.cam_fov / 2)
+    tx = ty * W / H
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float32)
+    nx, ny = tx * (2 * (xs + 0.5) / W - 1), ty * (2 * (ys + 0.5) / H - 1)
+    dirs = nx[..., None] * right - ny[..., None] * up + fwd
+    dirs /= np.linalg.norm(dirs, axis=2, keepdims=True)
+    rays = np.concatenate([np.broadcast_to(pos, dirs.shape), dirs], axis=2).reshape(-1, 6)
+    r = rt.Renderer()
+    r.upload(sc)
+    hits, _, _ = r.trace_rays(rays)
+    _, _, tri = r.scene_bvh()
+    r.close()
+    bits = hits[:, 3].view(np.uint32)
+    miss = bits == 0x7FFFFFFF
+    mat = tri[:, 3].view(np.int32)[np.where(miss, 0, bits & 0x7FFFFFFF)]
+    return np.where(miss, -1, mat).reshape(H, W)
+
+
+def _class_means_close(acc, port, mat, rel=0.02):
+    """Same Philox stream => the two images differ only where a path diverged at a tie (triangle edge, box plane);
+    those differences are unbiased noise.  A SYSTEMATIC error in the shading of one material class would shift that
+    class's mean: for every class covering >= 2 % of the frame the means agree within `rel` (+ a small floor)."""
+    bad = []
+    for m in np.unique(mat):
+        sel = mat == m
+        if sel.mean() < 0.02:
+            continue
+        a, b = float(acc[sel].mean()), float(port[sel].mean())
+        if abs(a - b) > rel * b + 1e-3 * float(port.mean()):
+            bad.append((int(m), float(sel.mean()), a, b))
+    return bad
 
 
 def _render(r, sc, b=0, e=None):
@@ -135,14 +192,20 @@ def test_hw4_box_light_matches_port_on_same_stream(renderer):
 
 
 @pytest.mark.parametrize("path,frac", [("hw8/sphere_emissive.gltf", 0.99), ("hw7/practice7_1.gltf", 0.85),
-                                       ("hw7/practice7_4.gltf", 0.90)])
+                                       ("hw7/practice7_4.gltf", 0.90), ("room20k", 0.85)])
 def test_gltf_matches_port_on_same_stream(renderer, path, frac):
-    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=16)
+    """Pixels of the two images are equal unless one of the pixel's ~80 ray queries diverged at a tie (the device hits
+    triangles with Moeller-Trumbore, the reference with its plane + projected 2x2 solve: different rounding at
+    edges), hence the pixel budget `frac`; what the budget could hide -- a systematic error on one material -- is
+    bounded per material class of the primary hit (room20k: all four texture kinds of hw8)."""
+    sc = ou.load_scene(_scene_file(path), width=128, height=96, samples=16)
     acc = _render(renderer, sc)
     port = ou.port_render(sc, 1, want_counters=True)
     ok, got = _mean_close(acc, port["accum"], 16, frac, rel=5e-2)
     assert ok, got
     assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean()
+    bad = _class_means_close(acc, port["accum"], _primary_material(sc))
+    assert not bad, bad
     st = renderer.stats()
     # same paths => (almost) the same number of closest-hit queries and light-pdf queries
     rays, rays_port = int(st["rays"]), int(port["counters"][0])
@@ -304,6 +367,7 @@ def _linear(img8):
     ("hw8_sphere_emissive_128x96", "hw8/sphere_emissive.gltf", "gltf"),
     ("hw7_practice7_1_128x96", "hw7/practice7_1.gltf", "gltf"),
     ("hw7_practice7_4_128x96", "hw7/practice7_4.gltf", "gltf"),
+    ("hw8_room20k_128x96", "room20k", "room"),
     ("hw6_practice7_1_128x96", "hw7/practice7_1.gltf", "gltf6"),
     ("hw6_practice7_1_glass_128x96", "hw6/practice7_1_glass.gltf", "gltf6"),
     ("hw4_p3_1", "hw4_p3_1_spp4096.txt", "text"),
@@ -316,7 +380,11 @@ def _linear(img8):
 ])
 def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind):
     spp = 64
-    if kind == "gltf":
+    if kind == "room":      # textured hw8 room: baseColor / metallicRoughness / normal-map / emissive textures
+        if not ou.has_golden(name + "_spp4096") or not ou.room_matches_golden(_scene_file(path)):
+            pytest.skip("room golden absent or rendered from a different generated scene")
+        sc = ou.load_scene(_scene_file(path), width=128, height=96, samples=spp)
+    elif kind == "gltf":
         sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=spp)
     elif kind == "gltf6":
         sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
@@ -369,15 +437,7 @@ def test_resolve_edge_values(renderer):
 
 
 def _room(tris=20000):
-    """Textured, normal-mapped, emissive synthetic room of the bench scene's family (tools/make_scene.py)."""
-    import sys
-    import tempfile
-    sys.path.insert(0, os.path.join(os.path.dirname(S), "..", "tools"))
-    import make_scene
-    d = os.path.join(tempfile.gettempdir(), f"b200rt_test_room_{tris}_{os.getuid()}")
-    if not os.path.exists(os.path.join(d, "b200room.gltf")):
-        make_scene.build(d, tris, 1)
-    return os.path.join(d, "b200room.gltf")
+    return ou.room_scene(tris)
 
 
 def test_every_build_renders_the_same_image():
@@ -592,3 +652,50 @@ def test_hw7_file_loads_under_hw8_rules_with_generated_attributes():
     d = np.abs(acc - p).max(axis=2) / 16
     assert (d <= 5e-2 * (np.abs(p).max(axis=2) / 16 + 1e-2)).mean() >= 0.9
     assert abs(acc.mean() - p.mean()) <= 2e-2 * p.mean()
+
+
+# ---- the counters the roofline is built from, checked against a CPU walk of the SAME flattened tree ----
+def _fixed_rays(sc, n_cam, n_rand, seed):
+    """Camera rays of the scene (coherent) + seeded random segments between points of the scene's box (incoherent)."""
+    d = sc.desc
+    pos, right, up, fwd = (np.array(list(v), np.float32) for v in (d.cam_pos, d.cam_right, d.cam_up, d.cam_forward))
+    rng = np.random.default_rng(seed)
+    ty = np.tan(d.cam_fov / 2)
+    tx = ty * sc.width / sc.height
+    uv = rng.random((n_cam, 2), dtype=np.float32) * 2 - 1
+    dirs = uv[:, :1] * tx * right - uv[:, 1:] * ty * up + fwd
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    cam = np.concatenate([np.broadcast_to(pos, dirs.shape), dirs], axis=1)
+    tris = np.frombuffer(ctypes.string_at(d.tris, d.n_tris * 148), np.uint8).reshape(d.n_tris, 148)[:, :36].copy().view(np.float32).reshape(-1, 3)
+    lo, hi = tris.min(axis=0), tris.max(axis=0)
+    a = lo + rng.random((n_rand, 3), dtype=np.float32) * (hi - lo)
+    b = lo + rng.random((n_rand, 3), dtype=np.float32) * (hi - lo)
+    dd = b - a
+    dd /= np.maximum(np.linalg.norm(dd, axis=1, keepdims=True), 1e-6)
+    return np.concatenate([cam, np.concatenate([a, dd], axis=1)]).astype(np.float32)
+
+
+@pytest.mark.parametrize("which", ["practice7_4", "room20k", "sphere"])
+def test_device_counters_equal_a_cpu_walk_of_the_same_flattened_bvh(which):
+    """b200rt_trace_rays runs the production wf_extend (counting build) on a fixed ray set; oracle/pairs_traverse.c walks
+    the records downloaded from the device with the same ordered traversal.  Box and triangle arithmetic are explicitly
+    rounded / fused on the device and restated with the same operations on the CPU: the hits (t, u, v, triangle, side)
+    are bit-identical and the counters EQUAL -- these are the counts bench.py's algorithmic bytes are built from."""
+    path = {"practice7_4": os.path.join(S, "hw7/practice7_4.gltf"), "sphere": os.path.join(S, "hw8/sphere_emissive.gltf"), "room20k": _room()}[which]
+    sc = rt.load_scene(path, width=160, height=96, samples=1)
+    r = rt.Renderer()
+    r.upload(sc)
+    rays = _fixed_rays(sc, 60000, 60000, 7)
+    hits, nb, nt = r.trace_rays(rays)
+    lay, rec, tri = r.scene_bvh()
+    r.close()
+    assert lay.n_tris == sc.desc.n_tris and lay.quant_bits == 15
+    chits, per, cb, ct = ou.pairs_traverse(lay, rec, tri, rays)
+    assert cb > 0 and ct > 0 and nb % 2 == 0
+    bits, cbits = hits[:, 3].view(np.uint32), chits[:, 3].view(np.uint32)
+    assert np.array_equal(bits, cbits), int((bits != cbits).sum())
+    hit = bits != 0x7FFFFFFF
+    assert hit.mean() > 0.3          # (a closed room has no misses at all)
+    assert np.array_equal(hits[hit, :3].view(np.uint32), chits[hit, :3].view(np.uint32))
+    assert (nb, nt) == (cb, ct), (nb, cb, nt, ct)
+    assert int(per[:, 0].sum()) == nb and per[:, 0].max() < 2000

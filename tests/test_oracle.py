@@ -129,3 +129,17 @@ def test_port_resolve_matches_port_render():
     sc = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=64, height=48, samples=4)
     o = ou.port_render(sc, 1)
     assert np.array_equal(ou.port_resolve(o["accum"], 4), o["rgb"])
+
+
+def test_port_hw8_textured_room_bytes_equal_reference():
+    """The only fixture with baseColor, metallicRoughness AND normal-map textures (hw8/src/scene.cpp:37-52, 107-146;
+    20 k-triangle room of tools/make_scene.py, regenerated here and pinned by tests/golden/hw8_room20k.sha):
+    port[minstd] reproduces the unmodified hw8 binary's PPM byte for byte -- texture wrap + bilinear taps, per-texel
+    sRGB decode, the TBN frame with the reference's negated cross, roughness clamp, emissive texture."""
+    room = ou.room_scene(20000)
+    if not ou.room_matches_golden(room):
+        pytest.skip("tools/make_scene.py generated a different scene than the one the golden was rendered from")
+    sc = ou.load_scene(room, width=128, height=96, samples=4)
+    assert sc.desc.n_images == 5 and sc.desc.n_light_tris > 0
+    o = ou.port_render(sc, 0)
+    assert np.array_equal(o["rgb"], ou.golden("hw8_room20k_128x96_spp4"))

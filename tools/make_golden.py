@@ -13,6 +13,9 @@ Fixtures:
   hw3_p3_{k}_spp{4,4096}.ppm.gz                   the hw3 binary on the same shrunk inputs (hw3 ships the same scenes)
   hw7_{name}_128x96_spp4.ppm.gz / _spp4096        hw7 binaries on practice7_1, practice7_4
   hw8_sphere_emissive_128x96_spp4.ppm.gz / _spp4096
+  hw8_room20k_128x96_spp{4,4096}.ppm.gz + .sha    hw8 binary on the 20 k-triangle room of tools/make_scene.py (seed 1): the only
+                                                  fixture with baseColor, metallicRoughness and normal-map textures; the
+                                                  .sha file pins the generated scene files (regenerated at test time)
   hw6_{name}_128x96_spp4.ppm.gz / _spp4096        hw6 binary on practice7_1 (mirrors + diffuse) and on
                                                   hw6/practice7_1_glass (same geometry, cube alpha 0.5 => dielectric)
 """
@@ -73,6 +76,14 @@ def main():
     env = os.path.join(SC, "hw8/sphere_emission.png")
     for spp in (4, 4096):
         run("hw8", [os.path.join(SC, "hw8/sphere_emissive.gltf"), "128", "96", str(spp), "@OUT", env], f"hw8_sphere_emissive_env_128x96_spp{spp}")
+    # textured room (tools/make_scene.py is deterministic: the scene is regenerated wherever the tests run)
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_util as ou
+    room = ou.room_scene(20000)
+    open(os.path.join(GOLD, "hw8_room20k.sha"), "w").write(ou.room_digest(room) + "\n")
+    for spp in (4, 4096):
+        run("hw8", [room, "128", "96", str(spp), "@OUT"], f"hw8_room20k_128x96_spp{spp}")
     for k in (1, 3, 4):  # slow (single-threaded reference): last
         run("hw4", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw4_p3_{k}_spp4096")
         run("hw3", [os.path.join(GOLD, f"hw4_p3_{k}_spp4096.txt"), "@OUT"], f"hw3_p3_{k}_spp4096")
