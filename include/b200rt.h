@@ -183,6 +183,11 @@ typedef struct b200rt_options {
 #define B200RT_FLAG_EXPLICIT_CAMERA_STATE 32 /* wavefront: wf_generate stores the whole state record of a camera path
                                        instead of the direction only (bit-identical image -- test aid) */
 
+#define B200RT_FLAG_NO_FIREFLY_CLAMP 64 /* hw7 / hw8: do not end a path when a bounce weight exceeds 6 in some channel (the
+                                       reference's DIRTY_DENOISE_HACK_BUBEN, hw8/src/scene.cpp:7,161 -- biased, darkens).  The
+                                       one-sample MIS estimator is then unbiased; NaN / inf weights still end the path.
+                                       Default (flag off) = the reference's image */
+
 typedef struct b200rt_stats {
     double   kernel_ms;        /* device time of the last b200rt_render (CUDA events) */
     uint64_t paths;            /* camera samples started                                */

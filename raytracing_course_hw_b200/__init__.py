@@ -19,6 +19,7 @@ MODE_HW1, MODE_HW2, MODE_HW3, MODE_HW4, MODE_HW5, MODE_HW6, MODE_HW7, MODE_HW8 =
 FLAG_COUNTERS = 1
 FLAG_MEGAKERNEL = 2   # glTF modes: per-path megakernel instead of the wavefront pipeline
 FLAG_REFERENCE_BVH = 8  # glTF modes: traverse the description's BVH instead of the library's rebuilt one
+FLAG_NO_FIREFLY_CLAMP = 64  # hw7 / hw8: unbiased estimator instead of the reference's weight clamp at 6
 FLAG_KEEP_DARK_RAYS = 16
 FLAG_EXPLICIT_CAMERA_STATE = 32
 FLAG_SERIAL_WAVES = 4  # wavefront: one wave in flight (stage times in stats() are then exclusive kernel times)

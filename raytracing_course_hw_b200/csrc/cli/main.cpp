@@ -7,7 +7,7 @@
 // Environment: B200RT_MODE=hw1..hw8 forces the semantics (default: inferred from the scene),
 // B200RT_GPUS=N renders with N GPUs (samples split; the buffers are combined by one peer-memory kernel on GPU 0),
 // output container by file name (.ppm / anything: binary P6 like the reference; .png; .pfm = float radiance),
-// B200RT_SEED, B200RT_STATS=1 (JSON with timings and ray counts on stderr).
+// B200RT_NO_CLAMP=1 (hw7 / hw8: unbiased estimator instead of the reference's firefly clamp), B200RT_SEED, B200RT_STATS=1 (JSON with timings and ray counts on stderr).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -70,6 +70,7 @@ int main(int argc, const char *argv[]) {
     // [g*S/G, (g+1)*S/G), and ONE fused peer reduce + resolve kernel on the first GPU (include/b200rt.h).
     b200rt_options opt{};
     opt.seed = getenv("B200RT_SEED") ? (uint32_t)strtoul(getenv("B200RT_SEED"), nullptr, 10) : 0u;
+    if (getenv("B200RT_NO_CLAMP") && atoi(getenv("B200RT_NO_CLAMP"))) opt.flags |= B200RT_FLAG_NO_FIREFLY_CLAMP;
     std::vector<int32_t> devices((size_t)n_gpus);
     for (int g = 0; g < n_gpus; g++) devices[(size_t)g] = g % avail;
     b200rt_group *grp = nullptr;

@@ -14,8 +14,32 @@ namespace b200rt {
 
 __constant__ DAnalyticScene g_scene;
 
+namespace {
+// Host restatement of Quaternion::operator* / transform with the reference's operation order (negated cross,
+// hw4/src/include/quaternion.h:36-48) -- the same float operations the kernels' qtransform performs.
+struct HQ { float x, y, z, w; };
+inline HQ hq_mul(const HQ &a, const HQ &b) {
+    return {(a.w * b.x + b.w * a.x) + (a.z * b.y - a.y * b.z), (a.w * b.y + b.w * a.y) + (a.x * b.z - a.z * b.x),
+            (a.w * b.z + b.w * a.z) + (a.y * b.x - a.x * b.y), a.w * b.w - (a.x * b.x + a.y * b.y + a.z * b.z)};
+}
+}  // namespace
+
 cudaError_t analytic_upload(const DAnalyticScene &scene, cudaStream_t stream) {
-    return cudaMemcpyToSymbolAsync(g_scene, &scene, sizeof(scene), 0, cudaMemcpyHostToDevice, stream);
+    static DAnalyticScene staged;       // a context is driven by one thread; pageable source: staged during the call
+    staged = scene;
+    for (int k = 0; k < staged.n_prims && k < B200RT_MAX_PRIMS; k++) {
+        const float *r = staged.prims[k].rotation;
+        const HQ q{r[0], r[1], r[2], r[3]}, qc{-1.f * r[0], -1.f * r[1], -1.f * r[2], r[3]};
+        float *m = staged.frame[k];
+        for (int c = 0; c < 3; c++) {       // column c = image of basis vector e_c
+            const HQ e{c == 0 ? 1.f : 0.f, c == 1 ? 1.f : 0.f, c == 2 ? 1.f : 0.f, 0.f};
+            const HQ t = hq_mul(hq_mul(q, e), qc);
+            m[0 + c] = t.x; m[3 + c] = t.y; m[6 + c] = t.z;
+        }
+        const bool ident = r[0] == 0.f && r[1] == 0.f && r[2] == 0.f && r[3] == 1.f;
+        m[9] = ident ? 1.f : 0.f; m[10] = m[11] = 0.f;
+    }
+    return cudaMemcpyToSymbolAsync(g_scene, &staged, sizeof(staged), 0, cudaMemcpyHostToDevice, stream);
 }
 
 namespace {
@@ -69,12 +93,46 @@ __device__ __forceinline__ bool box_slabs(V3 s, V3 o, V3 d, float &t, bool &insi
     return true;
 }
 
-// Figure::intersect of hw1..hw4.  WANT_N = false skips the normal (hw1 / shadow rays).
-template <bool WANT_N>
-__device__ __forceinline__ bool hit_prim(const b200rt_primitive &f, V3 o, V3 d, bool plane_tmax, AHit &h) {
+// World -> local of a ray for figure k.  FAST (Monte-Carlo modes): the precomputed 3x3 frame with explicit fused
+// multiply-adds (this file is compiled -fmad=false for hw1 / hw2), nothing at all for identity rotations; otherwise the
+// reference's two quaternion sandwiches in its own operation order (hw1 / hw2: bit-exact images).
+__device__ __forceinline__ V3 frame_apply(const float *m, V3 p) {
+    return mk(fmaf(m[2], p.z, fmaf(m[1], p.y, m[0] * p.x)), fmaf(m[5], p.z, fmaf(m[4], p.y, m[3] * p.x)), fmaf(m[8], p.z, fmaf(m[7], p.y, m[6] * p.x)));
+}
+__device__ __forceinline__ V3 frame_apply_t(const float *m, V3 p) {      // transpose: local -> world (up to the |q|^2 scale)
+    return mk(fmaf(m[6], p.z, fmaf(m[3], p.y, m[0] * p.x)), fmaf(m[7], p.z, fmaf(m[4], p.y, m[1] * p.x)), fmaf(m[8], p.z, fmaf(m[5], p.y, m[2] * p.x)));
+}
+template <bool FAST>
+__device__ __forceinline__ void to_local(int k, const b200rt_primitive &f, V3 o, V3 d, V3 &lo, V3 &ld) {
+    if (FAST) {
+        const float *m = g_scene.frame[k];
+        const V3 p = o - ld3(f.position);
+        if (m[9] != 0.f) { lo = p; ld = d; }
+        else { lo = frame_apply(m, p); ld = frame_apply(m, d); }
+    } else {
+        const Quat q{ld3(f.rotation), f.rotation[3]};
+        lo = qtransform(q, o - ld3(f.position));
+        ld = qtransform(q, d);
+    }
+}
+template <bool FAST>
+__device__ __forceinline__ V3 normal_to_world(int k, const b200rt_primitive &f, V3 n) {
+    if (FAST) {
+        const float *m = g_scene.frame[k];
+        const V3 w = m[9] != 0.f ? n : frame_apply_t(m, n);
+        return rsqrtf(fmaf(w.z, w.z, fmaf(w.y, w.y, w.x * w.x))) * w;
+    }
     const Quat q{ld3(f.rotation), f.rotation[3]};
-    const V3 lo = qtransform(q, o - ld3(f.position));
-    const V3 ld = qtransform(q, d);
+    return rnorm(qtransform(qconj(q), n));
+}
+
+// Figure::intersect of hw1..hw5 for figure k of the constant-memory scene.  WANT_N = false skips the normal (hw1,
+// shadow rays, and the candidates of the Monte-Carlo modes: there only the WINNER's normal is computed).
+template <bool WANT_N, bool FAST>
+__device__ __forceinline__ bool hit_prim(int k, V3 o, V3 d, bool plane_tmax, AHit &h) {
+    const b200rt_primitive &f = g_scene.prims[k];
+    V3 lo, ld;
+    to_local<FAST>(k, f, o, d, lo, ld);
     V3 n = mk(0, 0, 0);
     if (f.type == B200RT_PRIM_ELLIPSOID) {
         const V3 r = ld3(f.data);
@@ -87,7 +145,7 @@ __device__ __forceinline__ bool hit_prim(const b200rt_primitive &f, V3 o, V3 d, 
             const V3 point = lo + h.t * ld;
             n = point / (r * r);
             if (h.inside) n = -1.f * n;
-            n = rnorm(n);
+            if (!FAST) n = rnorm(n);       // (FAST normalises once, in world space)
         }
     } else if (f.type == B200RT_PRIM_PLANE) {
         const V3 pn = ld3(f.data);
@@ -108,7 +166,7 @@ __device__ __forceinline__ bool hit_prim(const b200rt_primitive &f, V3 o, V3 d, 
             if (h.inside) n = -1.f * n;
         }
     }
-    if (WANT_N) h.n = rnorm(qtransform(qconj(q), n));
+    if (WANT_N) h.n = normal_to_world<FAST>(k, f, n);
     return true;
 }
 
@@ -131,7 +189,7 @@ __global__ void cast_kernel(const DCamera cam, float *__restrict__ out, int32_t 
     for (int k = 0; k < g_scene.n_prims; k++) {
         AHit h;
         // hw1 planes have no T_MAX and the nearest test is `best == -1 || t < best` (scene.cpp:13)
-        if (hit_prim<false>(g_scene.prims[k], o, d, false, h) && (best == -1 || h.t < best)) {
+        if (hit_prim<false, false>(k, o, d, false, h) && (best == -1 || h.t < best)) {
             best = h.t; id = k; ans = ld3(g_scene.prims[k].color);
         }
     }
@@ -140,18 +198,29 @@ __global__ void cast_kernel(const DCamera cam, float *__restrict__ out, int32_t 
 }
 
 // ---- K2 ------------------------------------------------------------------------------------
+template <bool FAST>
 __device__ __forceinline__ int closest_prim(V3 o, V3 d, float tmax, bool plane_tmax, AHit &best) {
     int pos = -1;
+    if (FAST) {
+        // candidates without normals; the winner's normal afterwards (one more test of ONE figure instead of a
+        // local -> world transform + normalisation for every figure the ray pierces)
+        for (int k = 0; k < g_scene.n_prims; k++) {
+            AHit h;
+            if (hit_prim<false, true>(k, o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best.t = h.t; pos = k; }
+        }
+        if (pos >= 0) hit_prim<true, true>(pos, o, d, plane_tmax, best);
+        return pos;
+    }
     for (int k = 0; k < g_scene.n_prims; k++) {
         AHit h;
-        if (hit_prim<true>(g_scene.prims[k], o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best = h; pos = k; }
+        if (hit_prim<true, false>(k, o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best = h; pos = k; }
     }
     return pos;
 }
 __device__ __forceinline__ bool occluded(V3 o, V3 d, float tmax) {
     for (int k = 0; k < g_scene.n_prims; k++) {
         AHit h;
-        if (hit_prim<false>(g_scene.prims[k], o, d, false, h) && h.t <= tmax) return true;
+        if (hit_prim<false, false>(k, o, d, false, h) && h.t <= tmax) return true;
     }
     return false;
 }
@@ -182,7 +251,7 @@ __global__ void whitted_kernel(const DCamera cam, int ray_depth, float *__restri
         if (f.stage == 0) {
             if (f.depth == 0) { ret = mk(0.f, 0.f, 0.f); sp--; continue; }
             AHit h;
-            const int pos = closest_prim(f.o, f.d, INFINITY, false, h);
+            const int pos = closest_prim<false>(f.o, f.d, INFINITY, false, h);
             if (sp == 0) primary = pos;
             if (pos < 0) { ret = ld3(g_scene.bg); sp--; continue; }
             const b200rt_primitive &fig = g_scene.prims[pos];
@@ -264,7 +333,8 @@ __global__ void whitted_kernel(const DCamera cam, int ray_depth, float *__restri
 #define B200RT_PI_F 3.14159274f          /* const float PI = acos(-1) */
 #define B200RT_MAX_REJECTION 8           /* the reference loops unbounded */
 
-__device__ __forceinline__ float light_pdf_one(const b200rt_primitive &f, V3 x, V3 d, V3 y, V3 yn) {
+__device__ __forceinline__ float light_pdf_one(int k, V3 x, V3 d, V3 y, V3 yn) {
+    const b200rt_primitive &f = g_scene.prims[k];
     const V3 xy = x - y;
     if (f.type == B200RT_PRIM_BOX) {
         const float sx = f.data[0], sy = f.data[1], sz = f.data[2];
@@ -272,25 +342,27 @@ __device__ __forceinline__ float light_pdf_one(const b200rt_primitive &f, V3 x, 
         return dot(xy, xy) / (s_total * fabsf(dot(d, yn)));
     }
     const V3 r = ld3(f.data);
-    const Quat q{ld3(f.rotation), f.rotation[3]};
-    const V3 n = qtransform(q, y - ld3(f.position)) / r;
+    V3 ly, unused;
+    to_local<true>(k, f, y, mk(0, 0, 0), ly, unused);
+    const V3 n = ly / r;
     const V3 g = mk(n.x * r.y * r.z, r.x * n.y * r.z, r.x * r.y * n.z);
     const float point_prob = 1.f / (4 * B200RT_PI_F * sqrtf(dot(g, g)));
     return point_prob * dot(xy, xy) / fabsf(dot(d, yn));
 }
 // FigureLight::pdf (distributions.h:85-106): first hit plus the second hit from just behind it.
-__device__ __forceinline__ float light_pdf(const b200rt_primitive &f, V3 x, V3 d) {
+__device__ __forceinline__ float light_pdf(int k, V3 x, V3 d) {
     AHit h1;
-    if (!hit_prim<true>(f, x, d, true, h1)) return 0.f;
+    if (!hit_prim<true, true>(k, x, d, true, h1)) return 0.f;
     if (isnan(h1.t)) return INFINITY;
-    float ans = light_pdf_one(f, x, d, x + h1.t * d, h1.n);
+    float ans = light_pdf_one(k, x, d, x + h1.t * d, h1.n);
     AHit h2;
-    if (!hit_prim<true>(f, x + (h1.t + 0.0001f) * d, d, true, h2)) return ans;
-    return ans + light_pdf_one(f, x, d, x + (h1.t + 0.0001f + h2.t) * d, h2.n);
+    if (!hit_prim<true, true>(k, x + (h1.t + 0.0001f) * d, d, true, h2)) return ans;
+    return ans + light_pdf_one(k, x, d, x + (h1.t + 0.0001f + h2.t) * d, h2.n);
 }
 
-__device__ __forceinline__ V3 light_sample(const b200rt_primitive &f, V3 x, Rng &rng) {
-    const Quat q{ld3(f.rotation), f.rotation[3]};
+__device__ __forceinline__ V3 light_sample(int k, V3 x, Rng &rng) {
+    const b200rt_primitive &f = g_scene.prims[k];
+    const float *m = g_scene.frame[k];
     V3 dir = mk(0, 0, 1);
     for (int iter = 0; iter < B200RT_MAX_REJECTION; iter++) {
         V3 point;
@@ -309,10 +381,13 @@ __device__ __forceinline__ V3 light_sample(const b200rt_primitive &f, V3 x, Rng 
             const float u1 = rng.u(), u2 = rng.u();
             point = ld3(f.data) * sphere_dir(u1, u2);
         }
-        const V3 actual = qtransform(qconj(q), point) + ld3(f.position);
-        dir = rnorm(actual - x);
+        // local -> world: the transpose of the frame; for a non-unit quaternion both maps scale by |q|^2, so
+        // the transpose alone stands for q-conjugate's sandwich
+        const V3 actual = (m[9] != 0.f ? point : frame_apply_t(m, point)) + ld3(f.position);
+        const V3 ax = actual - x;
+        dir = rsqrtf(fmaf(ax.z, ax.z, fmaf(ax.y, ax.y, ax.x * ax.x))) * ax;
         AHit h;
-        if (hit_prim<false>(f, x, dir, true, h)) break;
+        if (hit_prim<false, true>(k, x, dir, true, h)) break;
     }
     return dir;
 }
@@ -357,7 +432,7 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                 for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
                     AHit h;
                     rays++;
-                    const int pos = closest_prim(o, d, INFINITY, !HW3, h);
+                    const int pos = closest_prim<true>(o, d, INFINITY, !HW3, h);
                     if (pos < 0) { L = L + T * ld3(g_scene.bg); break; }
                     rng.begin_bounce((uint32_t)bounce);
                     const b200rt_primitive &f = g_scene.prims[pos];
@@ -384,13 +459,13 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                             nd = (l <= 1e-9f || dot(c, h.n) <= 1e-9f || isnan(l)) ? h.n : (1.f / l) * c;
                         } else {
                             const int li = min((int)(rng.u() * n_lights), n_lights - 1);
-                            nd = light_sample(g_scene.prims[g_scene.light_prims[li]], xs, rng);
+                            nd = light_sample(g_scene.light_prims[li], xs, rng);
                         }
                         if (dot(nd, h.n) < 0) break;
                         float pdf = smax(0.f, dot(nd, h.n) / B200RT_PI_F);
                         if (n_lights > 0) {
                             float inner = 0;
-                            for (int li = 0; li < n_lights; li++) inner += light_pdf(g_scene.prims[g_scene.light_prims[li]], xs, nd);
+                            for (int li = 0; li < n_lights; li++) inner += light_pdf(g_scene.light_prims[li], xs, nd);
                             pdf = (pdf + inner / n_lights) / 2;
                         }
                         const float w = (1.f / (B200RT_PI_F * pdf)) * dot(nd, h.n);
@@ -492,7 +567,7 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                     // Scene::intersect: analytic figures by scan, triangles through the BVH, nearest wins
                     AHit h;
                     tc.rays++;
-                    const int pos = closest_prim(o, d, INFINITY, true, h);
+                    const int pos = closest_prim<true>(o, d, INFINITY, true, h);
                     TraceHit th;
                     th.tri = -1;
                     if (has_tris) trace_closest<false>(sc, o, d, th, tc);
@@ -535,7 +610,7 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                             const int li = min((int)(rng.u() * n_lights), n_lights - 1);
                             const int32_t e = __ldg(light_order + li);
                             if (e >= 0) {
-                                nd = light_sample(g_scene.prims[e], xs, rng);
+                                nd = light_sample(e, xs, rng);
                             } else {
                                 const float4 *lq = reinterpret_cast<const float4 *>(sc.light_sample_tris + ~e);
                                 const float4 a = __ldg(lq), b = __ldg(lq + 1), c = __ldg(lq + 2);
@@ -551,7 +626,7 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                             // FiguresMix::pdf: every emissive figure the ray pierces contributes (both hits for closed ones)
                             tc.light_queries++;
                             float inner = 0;
-                            for (int li = 0; li < g_scene.n_light_prims; li++) inner += light_pdf(g_scene.prims[g_scene.light_prims[li]], xs, nd);
+                            for (int li = 0; li < g_scene.n_light_prims; li++) inner += light_pdf(g_scene.light_prims[li], xs, nd);
                             if (sc.n_light_tris > 0) inner += light_pdf_sum<false>(sc, xs, nd, tc);
                             pdf = (pdf + inner / n_lights) / 2;
                         }

@@ -101,6 +101,7 @@ struct DGltfScene {
     uint32_t light_top_word[B200RT_LIGHT_TOP];
     int32_t light_top_start;
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
+    float weight_clamp;          // a bounce weight above this in any channel ends the path: 6 (reference), or FLT_MAX
     float bg[3];
     DTexels env;                 // null = absent
     int32_t env_w, env_h;
@@ -132,6 +133,11 @@ struct DAnalyticScene {
     int32_t n_light_prims;
     float bg[3], ambient[3];
     int32_t mode;
+    // Monte-Carlo modes (hw3 - hw5) only: the world -> local map p -> q p conj(q) of each figure as a row-major 3x3
+    // matrix (built at upload by applying the reference's quaternion arithmetic to the basis vectors: it carries the
+    // |q|^2 scale of non-unit quaternions), frame[k][9] != 0 marks an identity rotation (no transform at
+    // all).  hw1 / hw2 keep the two quaternion sandwiches per ray and figure: their images are bit-exact.
+    float frame[B200RT_MAX_PRIMS][12];
 };
 
 }  // namespace b200rt

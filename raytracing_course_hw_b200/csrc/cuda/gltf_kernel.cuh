@@ -583,15 +583,17 @@ __device__ __forceinline__ V3 surface_emission(const DGltfScene &sc, const float
 // Second part: mean of the component pdfs, path weight, firefly clamp (scene.cpp:158-163).
 // light_sum = FiguresMix::getTotalPdf for the ray (xo, nd); ignored when there are no emitters.
 __device__ __forceinline__ bool finish_bounce(const V3 brdf, float pdf_partial, float absdot, float light_sum,
-                                              int n_light_tris, V3 &T) {
+                                              int n_light_tris, V3 &T, const float clamp_at) {
     float pdf = pdf_partial;
     float k = 2.f;
     if (n_light_tris > 0) { pdf += light_sum / (float)n_light_tris; k = 3.f; }
     pdf /= k;
     const float w = (1.f / pdf) * absdot;
     const V3 mult = w * brdf;
-    // any channel > 6 or NaN ends the path
-    if (!(mult.x <= 6.f) || !(mult.y <= 6.f) || !(mult.z <= 6.f)) return false;
+    // any channel > 6 or NaN ends the path (the reference's DIRTY_DENOISE_HACK_BUBEN, hw8/src/scene.cpp:7,161: biased,
+    // darkens).  clamp_at = DGltfScene::weight_clamp: 6 by default; B200RT_FLAG_NO_FIREFLY_CLAMP raises it to FLT_MAX,
+    // which leaves the one-sample MIS estimator of Mix::pdf unbiased and still ends paths on NaN / inf weights.
+    if (!(mult.x <= clamp_at) || !(mult.y <= clamp_at) || !(mult.z <= clamp_at)) return false;
     T = T * mult;
     return true;
 }
@@ -609,7 +611,7 @@ __device__ __forceinline__ bool shade_bounce(const DGltfScene &sc, const float *
         tc.light_queries++;
         ls = light_pdf_sum<COUNT>(sc, bo.xo, bo.nd, tc);
     }
-    if (!finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, ls, sc.n_light_tris, T)) return false;
+    if (!finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, ls, sc.n_light_tris, T, sc.weight_clamp)) return false;
     o = bo.xo;
     d = bo.nd;
     return true;

@@ -253,6 +253,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
 
     DGltfScene g{};
     g.hw8 = s->mode == B200RT_MODE_HW8;
+    g.weight_clamp = (ctx->flags & B200RT_FLAG_NO_FIREFLY_CLAMP) ? 3.402823466e38f : 6.f;
     for (int k = 0; k < 3; k++) g.bg[k] = s->bg_color[k];
     int rc;
 #ifdef B200RT_DEV      // development builds only: per-phase times on stderr
@@ -623,6 +624,7 @@ int b200rt_import_scene_end(b200rt_ctx *ctx, const b200rt_scene_image *hdr) {
         rebase_materials_kernel<<<(im.n_materials + 63) / 64, 64, 0, ctx->stream>>>(const_cast<DMaterial *>(g.materials), im.n_materials, delta);
         CK(cudaGetLastError());
     }
+    g.weight_clamp = (ctx->flags & B200RT_FLAG_NO_FIREFLY_CLAMP) ? 3.402823466e38f : 6.f;      // a property of THIS context
     ctx->gs = g;
     ctx->lut_srgb = reinterpret_cast<float *>(reinterpret_cast<char *>((uintptr_t)im.lut) + delta);
     ctx->arena_used = (size_t)im.bytes; ctx->n_materials = im.n_materials;

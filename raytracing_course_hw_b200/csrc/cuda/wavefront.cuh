@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                 SurfRec rec;
                 load_surf_rec<HW8>(sc, (int)(bits & 0x7FFFFFFFu), rec);
                 cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, rec, (bits >> 31) != 0, L, T, rnd, tc, bo);
-                if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
+                if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T, sc.weight_clamp);
                 if (cont && has_lights && q_direct) {
                     // A ray that misses the boxes around the emitters has a light pdf of exactly 0
                     // (light_boxes_hit): the bounce is finished here and the path skips the light stage
@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                         if (COUNT) tc.light_node_tests++;
                         answered++;
                         direct = true;
-                        cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T);
+                        cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T, sc.weight_clamp);
                         bo.pdf_partial = 0.f;
                         // drop_dark (set when the NEXT bounce is the last one and the background is black): that
                         // bounce only adds the emission of what it hits, and a ray that misses the emitters' boxes
@@ -488,7 +488,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     V3 T = mk(th.x, th.y, th.z);
                     // drop_dark: see wf_shade.  total == 0 means the ray pierces no emissive triangle within T_MAX (every
                     // hit adds a positive term), so the last bounce would add nothing: the path ends here
-                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T) && !(drop_dark && total == 0.f)) {
+                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T, sc.weight_clamp) && !(drop_dark && total == 0.f)) {
                         st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, 0.f));
                         push_pending = true;
                         push_p = p;

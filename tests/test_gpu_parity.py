@@ -699,3 +699,22 @@ def test_device_counters_equal_a_cpu_walk_of_the_same_flattened_bvh(which):
     assert np.array_equal(hits[hit, :3].view(np.uint32), chits[hit, :3].view(np.uint32))
     assert (nb, nt) == (cb, ct), (nb, cb, nt, ct)
     assert int(per[:, 0].sum()) == nb and per[:, 0].max() < 2000
+
+
+def test_no_firefly_clamp_mode_only_adds_energy():
+    """B200RT_FLAG_NO_FIREFLY_CLAMP: the reference ends a path when a bounce weight exceeds 6 in some
+    channel (DIRTY_DENOISE_HACK_BUBEN, hw8/src/scene.cpp:161 -- biased).  Without the clamp the same paths continue:
+    every pixel's sum is >= the clamped one's (same Philox stream, radiance is non-negative), a visible share of pixels
+    gains energy, nothing is NaN / inf, and the flag changes nothing else (the default stays the reference's image)."""
+    sc = ou.load_scene(os.path.join(S, "hw7/practice7_4.gltf"), width=128, height=96, samples=32)
+    a, b = rt.Renderer(), rt.Renderer(flags=rt.FLAG_NO_FIREFLY_CLAMP)
+    clamped, free = _render(a, sc), _render(b, sc)
+    m = rt.Renderer(flags=rt.FLAG_NO_FIREFLY_CLAMP | rt.FLAG_MEGAKERNEL)
+    assert np.array_equal(_render(m, sc), free)                      # every scheduling honours the flag
+    for r in (a, b, m):
+        r.close()
+    assert np.isfinite(free).all()
+    assert (free >= clamped - 1e-6 * np.abs(clamped)).all()
+    gained = (free > clamped * 1.0001).any(axis=2).mean()
+    assert 0.001 < gained < 0.9, gained
+    assert free.mean() > clamped.mean()
