@@ -42,7 +42,7 @@ static void make_qray(const Layout *L, const float *o, const float *d, QRay *r) 
         const float oq = (o[a] - L->base[a]) * L->inv_scale[a];
         const float ig = L->scale[a] * safe_rcp(d[a]);
         const float c = -(oq * ig);
-        const float g = L->guard * fabsf(ig);
+        const float g = fmaf(fabsf(oq), 4.76837158203125e-7f, L->guard) * fabsf(ig);      /* see make_qray on the device */
         const float off = 32768.f * ig;
         r->bn[a] = (c - g) - off;
         r->bf[a] = (c + g) - off;

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <stdexcept>
 #include "analytic_kernels.h"
 #include "context.h"
 #include "resolve.cuh"
@@ -97,7 +98,14 @@ void b200rt_destroy(b200rt_ctx *ctx) {
     delete ctx;
 }
 
+static int upload_scene_impl(b200rt_ctx *ctx, const b200rt_scene_desc *s);
+// "Never throws" (include/b200rt.h): the flattener and the BVH rebuild allocate std::vectors
 int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
+    B200RT_TRY
+    return upload_scene_impl(ctx, s);
+    B200RT_CATCH(ctx)
+}
+static int upload_scene_impl(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
     if (!ctx || !s) return B200RT_ERR_INVALID;
     if (s->width <= 0 || s->height <= 0 || s->samples <= 0) return fail(ctx, B200RT_ERR_INVALID, "bad frame size / sample count");
     CK(cudaSetDevice(ctx->device));

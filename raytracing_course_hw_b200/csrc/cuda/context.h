@@ -3,6 +3,7 @@
 // multi_gpu.cu: groups, peer reduce).
 #pragma once
 #include <cuda_runtime.h>
+#include <new>
 #include <string>
 #include <vector>
 #include "b200rt.h"

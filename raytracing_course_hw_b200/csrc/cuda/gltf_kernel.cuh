@@ -108,7 +108,10 @@ __device__ __forceinline__ float qray_axis(float o, float d, float base, float s
     const float oq = __fmul_rn(__fsub_rn(o, base), inv_scale);
     const float ig = __fmul_rn(scale, safe_rcp(d));
     const float c = -__fmul_rn(oq, ig);
-    const float g = __fmul_rn(B200RT_QEPS, fabsf(ig));
+    // guard band: B200RT_QEPS grid units for the plane arithmetic + 2^-21 |o'| for the rounding of the origin's own
+    // transform, which grows with its distance from the grid (a ray origin far outside the LIGHT tree's small grid --
+    // a lamp in a large room -- would otherwise see boxes that are no longer conservative)
+    const float g = __fmul_rn(fmaf(fabsf(oq), 4.76837158203125e-7f, B200RT_QEPS), fabsf(ig));
     bn = __fsub_rn(c, g); bf = __fadd_rn(c, g);
 #if B200RT_QBITS == 15
     const float off = __fmul_rn(32768.f, ig);      // exact (power of two)

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include "analytic_kernels.h"
 #include "context.h"
 #include "gltf_kernel.cuh"
@@ -182,7 +183,13 @@ void camera_of(const b200rt_scene_desc &d, int w, int h, DCamera &c) {
 
 extern "C" {
 
+static int render_impl(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_begin, int32_t spp_end, int32_t ray_depth);
 int b200rt_render(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_begin, int32_t spp_end, int32_t ray_depth) {
+    B200RT_TRY                 // (the per-stage event pool is a std::vector)
+    return render_impl(ctx, width, height, spp_begin, spp_end, ray_depth);
+    B200RT_CATCH(ctx)
+}
+static int render_impl(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t spp_begin, int32_t spp_end, int32_t ray_depth) {
     if (!ctx) return B200RT_ERR_INVALID;
     if (!ctx->has_scene) return fail(ctx, B200RT_ERR_NO_SCENE, "render before upload_scene");
     const b200rt_scene_desc &d = ctx->desc;

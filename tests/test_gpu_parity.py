@@ -496,18 +496,25 @@ def test_full_size_frame_properties(renderer):
     assert img.shape == (2160, 3840, 3)
 
 
-def test_wave_of_two_to_the_26_slots():
-    """8192 x 8192 = 2^26 pixels: the largest wave whose slot index leaves no room for the light-cut mask in a queue
-    entry (the light stage then tests the cut boxes itself).  Same camera => same mean radiance as a small frame."""
-    small = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=256, height=256, samples=64)
-    big = ou.load_scene(os.path.join(S, "hw8/sphere_emissive.gltf"), width=8192, height=8192, samples=1)
+@pytest.mark.parametrize("height", [8192, 8200])
+def test_wave_of_two_to_the_26_slots_and_more(height):
+    """8192 x 8192 = 2^26 pixels is the first wave whose slot index leaves no room for the light-cut mask in a queue
+    entry (the light stage then tests the cut boxes itself); 8192 x 8200 has slots ABOVE 2^26 (its last eight rows) --
+    round 1 masked the queue entry to 26 bits there: those paths were dropped and the low slots they aliased onto
+    (the first eight rows) finished the wrong bounce.  Closed, lit room (every pixel carries indirect light): same
+    camera => same mean as a small frame, and the first / last eight rows look like the eight rows next to them."""
+    path = _room()
+    small = ou.load_scene(path, width=256, height=256, samples=64)
+    big = ou.load_scene(path, width=8192, height=height, samples=1)
     r = rt.Renderer()
-    ref = _render(r, small).mean() / 64
+    ref = (_render(r, small) / 64).mean()
     acc = _render(r, big)
     st = r.stats()
     r.close()
-    assert st["paths"] == 1 << 26 and np.isfinite(acc).all()
+    assert st["paths"] == 8192 * height and np.isfinite(acc).all()
     assert abs(acc.mean() - ref) <= 0.02 * ref, (acc.mean(), ref)
+    for a, b in ((acc[:8], acc[8:16]), (acc[-8:], acc[-16:-8])):
+        assert a.mean() > 0 and abs(a.mean() - b.mean()) <= 0.2 * b.mean(), (a.mean(), b.mean())
 
 
 @pytest.mark.parametrize("mode_lines,mode", [("", rt.MODE_HW1), ("AMBIENT_LIGHT 0.2 0.2 0.2\nRAY_DEPTH 3\n", rt.MODE_HW2),
