@@ -18,3 +18,24 @@ for path, kw, flags in cases:
     img = r.resolve(sc.samples)
     print(path, kw, flags, "mean", float(img.mean()), flush=True)
     r.close()
+
+# round 2: several contexts behind one group (fused peer reduce + resolve; 61 x 47 x 3 floats is not a multiple of
+# four: the scalar tail runs), the ray-set query of the production traversal kernel, the allocation-free resolve
+import numpy as np
+sc = rt.load_scene(os.path.join(S, "hw7/practice7_4.gltf"), width=61, height=47, samples=6)
+g = rt.Group([0, 0, 0])
+g.upload(sc)
+g.render(0, 6)
+print("group", float(g.resolve(6).mean()), float(g.download_accum().mean()), flush=True)
+g.close()
+r = rt.Renderer()
+r.upload(sc)
+rays = np.random.default_rng(1).standard_normal((5000, 6)).astype(np.float32)
+hits, nb, nt = r.trace_rays(rays)
+lay, rec, tri = r.scene_bvh()
+print("trace_rays", nb, nt, rec.shape, tri.shape, flush=True)
+r.render(0, 6)
+r.synchronize()
+ptr, _ = r.accum_device_ptr()
+print("noalloc", float(rt.resolve_noalloc(0, ptr, 61, 47, 6, sc.mode, stream=r.stream()).mean()), flush=True)
+r.close()
