@@ -209,3 +209,103 @@ def _stb_free_decode(path):
         prev = cur
     out = out.reshape(h, w, ch)
     return np.repeat(out, 3, axis=2) if ch == 1 else out[:, :, :3]
+
+
+def test_gltf_loader_survives_mutated_files(tmp_path):
+    """The reference reads missing JSON members through compiled-out asserts and indexes buffers unchecked
+    (hw8/src/sceneio.cpp:28-37, 82-98: undefined behaviour on malformed files); this loader promises an error code.
+    300 seeded mutations of practice7_4.gltf (byte flips, deletions, truncations, number edits; a truncated .bin;
+    index / count / offset values pushed out of range) are loaded in a SUBPROCESS: it must exit normally, every load
+    either fails with a B200rtError or yields a description whose counts are sane."""
+    import subprocess, sys, textwrap
+    src = os.path.join(S, "hw7/practice7_4.gltf")
+    text = open(src, "rb").read()
+    blob = open(os.path.join(S, "hw7/practice7_4.bin"), "rb").read()
+    rng = np.random.default_rng(11)
+    paths = []
+    for i in range(300):
+        t = bytearray(text)
+        kind = i % 6
+        if kind == 0:        # flip random bytes
+            for _ in range(int(rng.integers(1, 6))):
+                t[int(rng.integers(0, len(t)))] = int(rng.integers(32, 127))
+        elif kind == 1:      # delete a slice
+            a = int(rng.integers(0, len(t) - 1)); del t[a:a + int(rng.integers(1, 200))]
+        elif kind == 2:      # truncate
+            del t[int(rng.integers(1, len(t))):]
+        elif kind == 3:      # blow up some number
+            s = t.decode("latin1")
+            nums = [m for m in re.finditer(r"(?<=[:\[, ])\d+(?=[,\]\} \n])", s)]
+            m = nums[int(rng.integers(0, len(nums)))]
+            s = s[:m.start()] + str(int(rng.choice([0, 7, 99999999, 4294967295, 2 ** 40]))) + s[m.end():]
+            t = bytearray(s.encode("latin1"))
+        elif kind == 4:      # duplicate a slice somewhere else
+            a = int(rng.integers(0, len(t) - 50)); b = int(rng.integers(0, len(t)))
+            t[b:b] = t[a:a + int(rng.integers(1, 50))]
+        d = tmp_path / f"m{i}"
+        d.mkdir()
+        (d / "practice7_4.gltf").write_bytes(bytes(t))
+        (d / "practice7_4.bin").write_bytes(blob[:int(rng.integers(0, len(blob)))] if kind == 5 else blob)
+        paths.append(str(d / "practice7_4.gltf"))
+    (tmp_path / "list.txt").write_text("\n".join(paths))
+    code = textwrap.dedent(f"""
+        import sys
+        sys.path.insert(0, {ROOT!r})
+        import raytracing_course_hw_b200 as rt
+        ok = bad = 0
+        for p in open({str(tmp_path / 'list.txt')!r}).read().split("\\n"):
+            for mode in (0, 8):
+                try:
+                    sc = rt.load_scene(p, width=8, height=8, samples=1, mode=mode)
+                    d = sc.desc
+                    assert 0 <= d.n_tris < 1 << 27 and 0 <= d.n_light_tris <= d.n_tris and d.n_materials >= 0
+                    ok += 1
+                except rt.B200rtError:
+                    bad += 1
+        print("loaded", ok, "rejected", bad)
+    """)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-2000:])
+    ok, bad = (int(x) for x in re.findall(r"loaded (\d+) rejected (\d+)", r.stdout)[0])
+    assert ok + bad == 600 and bad > 100 and ok > 50, r.stdout       # both outcomes occur: the mutations are neither all fatal nor all harmless
+
+
+def test_png_decoder_survives_mutated_files(tmp_path):
+    """Same for the built-in PNG decoder (dynamic-Huffman deflate stream of the shipped texture): 120 seeded mutations /
+    truncations, decoded in a subprocess through b200rt_host_set_env_map; never a crash, never a partial image."""
+    import subprocess, sys, textwrap
+    data = open(os.path.join(S, "hw8/sphere_emission.png"), "rb").read()
+    rng = np.random.default_rng(5)
+    names = []
+    for i in range(120):
+        t = bytearray(data)
+        if i % 3 == 0:
+            del t[int(rng.integers(8, len(t))):]
+        elif i % 3 == 1:
+            for _ in range(int(rng.integers(1, 8))):
+                t[int(rng.integers(8, len(t)))] = int(rng.integers(0, 256))
+        else:
+            a = int(rng.integers(33, len(t) - 64)); del t[a:a + int(rng.integers(1, 64))]
+        (tmp_path / f"m{i}.png").write_bytes(bytes(t))
+        names.append(str(tmp_path / f"m{i}.png"))
+    (tmp_path / "list.txt").write_text("\n".join(names))
+    code = textwrap.dedent(f"""
+        import sys
+        sys.path.insert(0, {ROOT!r})
+        import raytracing_course_hw_b200 as rt
+        sc = rt.load_scene({os.path.join(S, 'hw8/sphere_emissive.gltf')!r}, width=8, height=8, samples=1)
+        ok = bad = 0
+        for p in open({str(tmp_path / 'list.txt')!r}).read().split("\\n"):
+            try:
+                sc.set_env_map(p)
+                e = sc.desc.env_map.contents
+                assert e.width == 2048 and e.height == 1024 or e.width > 0
+                ok += 1
+            except rt.B200rtError:
+                bad += 1
+        print("decoded", ok, "rejected", bad)
+    """)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-2000:])
+    ok, bad = (int(x) for x in re.findall(r"decoded (\d+) rejected (\d+)", r.stdout)[0])
+    assert ok + bad == 120 and bad >= 40, r.stdout
