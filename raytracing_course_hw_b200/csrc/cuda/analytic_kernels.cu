@@ -417,23 +417,37 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
             rng.pixel = (uint32_t)(py * W + px); rng.seed = rp.seed;
             const int n_lights = g_scene.n_light_prims;
             V3 sum = mk(0, 0, 0);
-            for (int s = s0; s < s1; s++) {
-                rng.begin_sample((uint32_t)s);
-                // hw4 camera: jitter only, no +0.5, fovX based, NOT normalised (scene.cpp:113-128)
-                const float fx = (float)px + rng.u();
-                const float fy = (float)py + rng.u();
-                // hw3: 2 * (x + 0.5) / width - 1 is evaluated in double (the 0.5 literal), then rounded
-                const float nx = HW3 ? rp.cam.tan_x * (float)(2 * ((double)fx + 0.5) / W - 1) : rp.cam.tan_x * (2 * fx / W - 1);
-                const float ny = HW3 ? rp.cam.tan_y * (float)(2 * ((double)fy + 0.5) / H - 1) : rp.cam.tan_y * (2 * fy / H - 1);
-                V3 o = ld3(rp.cam.pos);
-                V3 d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
-                V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
-                paths++;
-                for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
+            // Path regeneration: ONE loop over bounces; a lane whose path has ended starts its pixel's next sample in
+            // the same pass instead of idling until the longest path of the warp's 32 pixels is through (ncu: 14.6 of
+            // 32 lanes active with a loop over samples around a loop over bounces).  The counter-based generator makes
+            // every path independent of when it is traced, and each pixel still adds its samples in order.
+            int s = rp.ray_depth > 0 ? s0 : s1, bounce = 0;
+            bool alive = false;
+            V3 o = mk(0, 0, 0), d = mk(0, 0, 1), L = mk(0, 0, 0), T = mk(1, 1, 1);
+            while (true) {
+                if (!alive) {
+                    if (s >= s1) break;
+                    rng.begin_sample((uint32_t)s);
+                    // hw4 camera: jitter only, no +0.5, fovX based, NOT normalised (scene.cpp:113-128)
+                    const float fx = (float)px + rng.u();
+                    const float fy = (float)py + rng.u();
+                    // hw3: 2 * (x + 0.5) / width - 1 is evaluated in double (the 0.5 literal), then rounded
+                    const float nx = HW3 ? rp.cam.tan_x * (float)(2 * ((double)fx + 0.5) / W - 1) : rp.cam.tan_x * (2 * fx / W - 1);
+                    const float ny = HW3 ? rp.cam.tan_y * (float)(2 * ((double)fy + 0.5) / H - 1) : rp.cam.tan_y * (2 * fy / H - 1);
+                    o = ld3(rp.cam.pos);
+                    d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
+                    L = mk(0, 0, 0); T = mk(1, 1, 1);
+                    paths++;
+                    bounce = 0;
+                    alive = true;
+                }
+                // one bounce of this lane's current path; `end`: the path stops here
+                bool end = false;
+                do {
                     AHit h;
                     rays++;
                     const int pos = closest_prim<true>(o, d, INFINITY, !HW3, h);
-                    if (pos < 0) { L = L + T * ld3(g_scene.bg); break; }
+                    if (pos < 0) { L = L + T * ld3(g_scene.bg); end = true; break; }
                     rng.begin_bounce((uint32_t)bounce);
                     const b200rt_primitive &f = g_scene.prims[pos];
                     const V3 x = o + h.t * d;
@@ -461,7 +475,7 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                             const int li = min((int)(rng.u() * n_lights), n_lights - 1);
                             nd = light_sample(g_scene.light_prims[li], xs, rng);
                         }
-                        if (dot(nd, h.n) < 0) break;
+                        if (dot(nd, h.n) < 0) { end = true; break; }
                         float pdf = smax(0.f, dot(nd, h.n) / B200RT_PI_F);
                         if (n_lights > 0) {
                             float inner = 0;
@@ -503,8 +517,9 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
                         (void)reflect;
                         o = x + 0.0001f * nd; d = nd;
                     }
-                }
-                sum = sum + L;
+                } while (false);
+                if (++bounce >= rp.ray_depth) end = true;
+                if (end) { sum = sum + L; s++; alive = false; }
             }
             float *dst = rp.accum + ((size_t)chunk * W * H + (size_t)(py * W + px)) * 3;
             dst[0] = sum.x; dst[1] = sum.y; dst[2] = sum.z;
@@ -552,18 +567,28 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
             Rng rng;
             rng.pixel = (uint32_t)(py * W + px); rng.seed = rp.seed;
             V3 sum = mk(0, 0, 0);
-            for (int s = s0; s < s1; s++) {
-                rng.begin_sample((uint32_t)s);
-                // camera of hw4 / hw5: jitter only, fovX based, NOT normalised (hw5/src/scene.cpp:107-126)
-                const float fx = (float)px + rng.u();
-                const float fy = (float)py + rng.u();
-                const float nx = rp.cam.tan_x * (2 * fx / W - 1);
-                const float ny = rp.cam.tan_y * (2 * fy / H - 1);
-                V3 o = ld3(rp.cam.pos);
-                V3 d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
-                V3 L = mk(0, 0, 0), T = mk(1, 1, 1);
-                tc.paths++;
-                for (int bounce = 0; bounce < rp.ray_depth; bounce++) {
+            // path regeneration, as in pt_analytic_kernel: one loop over bounces, ended paths restart at once
+            int s = rp.ray_depth > 0 ? s0 : s1, bounce = 0;
+            bool alive = false;
+            V3 o = mk(0, 0, 0), d = mk(0, 0, 1), L = mk(0, 0, 0), T = mk(1, 1, 1);
+            while (true) {
+                if (!alive) {
+                    if (s >= s1) break;
+                    rng.begin_sample((uint32_t)s);
+                    // camera of hw4 / hw5: jitter only, fovX based, NOT normalised (hw5/src/scene.cpp:107-126)
+                    const float fx = (float)px + rng.u();
+                    const float fy = (float)py + rng.u();
+                    const float nx = rp.cam.tan_x * (2 * fx / W - 1);
+                    const float ny = rp.cam.tan_y * (2 * fy / H - 1);
+                    o = ld3(rp.cam.pos);
+                    d = (nx * ld3(rp.cam.right) - ny * ld3(rp.cam.up)) + ld3(rp.cam.forward);
+                    L = mk(0, 0, 0); T = mk(1, 1, 1);
+                    tc.paths++;
+                    bounce = 0;
+                    alive = true;
+                }
+                bool end = false;
+                do {
                     // Scene::intersect: analytic figures by scan, triangles through the BVH, nearest wins
                     AHit h;
                     tc.rays++;
@@ -572,7 +597,7 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                     th.tri = -1;
                     if (has_tris) trace_closest<false>(sc, o, d, th, tc);
                     const bool on_tri = th.tri >= 0 && (pos < 0 || th.t < h.t);
-                    if (pos < 0 && !on_tri) { L = L + T * ld3(sc.bg); break; }
+                    if (pos < 0 && !on_tri) { L = L + T * ld3(sc.bg); end = true; break; }
                     rng.begin_bounce((uint32_t)bounce);
                     V3 emission, color;
                     int material;
@@ -620,7 +645,7 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                                 nd = rnorm(point - xs);
                             }
                         }
-                        if (dot(nd, h.n) < 0) break;
+                        if (dot(nd, h.n) < 0) { end = true; break; }
                         float pdf = smax(0.f, dot(nd, h.n) / B200RT_PI_F);
                         if (n_lights > 0) {
                             // FiguresMix::pdf: every emissive figure the ray pierces contributes (both hits for closed ones)
@@ -659,8 +684,9 @@ __global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, cons
                         }
                         o = x + 0.0001f * nd; d = nd;
                     }
-                }
-                sum = sum + L;
+                } while (false);
+                if (++bounce >= rp.ray_depth) end = true;
+                if (end) { sum = sum + L; s++; alive = false; }
             }
             float *dst = rp.accum + ((size_t)chunk * W * H + (size_t)(py * W + px)) * 3;
             dst[0] = sum.x; dst[1] = sum.y; dst[2] = sum.z;

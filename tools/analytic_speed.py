@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Throughput of the analytic-scene kernels (K3 hw3 / hw4, K7 hw5, K2 hw2) on their BASELINE scenes: kernel time from the
+"""Throughput of the analytic-scene kernels (K3 hw3 / hw4, K7 hw5, K6 hw6, K2 hw2) on their BASELINE scenes: kernel time from the
 library's CUDA events.  Development / measurement tool (profiles/rNN_analytic_speed.log is a copy of its output)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -9,9 +9,13 @@ S = os.path.join(ROOT, "tests", "scenes")
 CASES = [("hw4 practice3_1", "hw4/practice3_1.txt", 0, 1920, 1080, 256), ("hw4 practice3_3", "hw4/practice3_3.txt", 0, 1920, 1080, 256),
          ("hw4 practice3_4", "hw4/practice3_4.txt", 0, 1920, 1080, 256), ("hw4 practice3_5", "hw4/practice3_5.txt", 0, 1920, 1080, 256),
          ("hw3 practice3_3", "hw4/practice3_3.txt", rt.MODE_HW3, 1920, 1080, 256), ("hw5 mixed", "hw5/mixed.txt", 0, 1920, 1080, 256),
+         ("hw6 glass", "hw6/practice7_1_glass.gltf", rt.MODE_HW6, 1920, 1080, 64),
          ("hw2 sample 4K", "hw2/sample.txt", 0, 3840, 2160, 1)]
+only = sys.argv[1:]      # optional: substrings of the case names to run
 r = rt.Renderer()
 for name, path, mode, w, h, spp in CASES:
+    if only and not any(o in name for o in only):
+        continue
     sc = rt.load_scene(os.path.join(S, path), width=w, height=h, samples=spp, mode=mode)
     r.upload(sc)
     r.render(0, spp)
