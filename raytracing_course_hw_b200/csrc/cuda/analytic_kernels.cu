@@ -395,8 +395,16 @@ __device__ __forceinline__ V3 light_sample(int k, V3 x, Rng &rng) {
 // HW3 = the uniform-hemisphere integrator of hw3 (hw3/src/scene.cpp:31-106): the diffuse bounce draws a uniform
 // direction on the hemisphere around the normal and weighs it by 2 (w . n) colour; planes have no T_MAX yet
 // (hw3/src/primitives.cpp:72); the camera adds 0.5 to the jittered pixel position (hw3/src/scene.cpp:103-104).
+// Resident blocks per SM asked of ptxas (profiles/r02_sweep_analytic_minb.log): these per-path kernels wait on their own
+// dependent arithmetic and loads, and more resident warps pay for the spills up to 64 registers (K3) / 42 (K7).
+#ifndef B200RT_K3_MINB
+#define B200RT_K3_MINB 8
+#endif
+#ifndef B200RT_K7_MINB
+#define B200RT_K7_MINB 12
+#endif
 template <bool HW3>
-__global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp) {
+__global__ void __launch_bounds__(128, B200RT_K3_MINB) pt_analytic_kernel(const DRenderParams rp) {
     const int W = rp.cam.width, H = rp.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
     const long long n_tiles = (long long)tiles_x * tiles_y;
@@ -546,7 +554,7 @@ __global__ void __launch_bounds__(128) pt_analytic_kernel(const DRenderParams rp
 // order: `light_order[i]` >= 0 names an analytic figure, < 0 the emissive triangle ~light_order[i].
 // Integrator = hw4's / hw6's (diffuse with Mix{Cosine, lights}, mirror, dielectric with the Fresnel coin first).
 // Stream layout = oracle/port_mc.cpp Hw5<RngPhilox>, draw for draw (sequential Rng view).
-__global__ void __launch_bounds__(128) hw5_path_kernel(const DGltfScene sc, const DRenderParams rp, const int32_t *__restrict__ light_order,
+__global__ void __launch_bounds__(128, B200RT_K7_MINB) hw5_path_kernel(const DGltfScene sc, const DRenderParams rp, const int32_t *__restrict__ light_order,
                                                        const int n_lights, const int has_tris) {
     const int W = rp.cam.width, H = rp.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;

@@ -13,8 +13,11 @@ namespace b200rt {
 
 #define B200RT_PI_F6 3.14159274f          /* const float PI = acos(-1) (distributions.h:11) */
 
+#ifndef B200RT_K6_MINB
+#define B200RT_K6_MINB 8        /* resident blocks per SM asked of ptxas (profiles/r02_sweep_analytic_minb.log: 3.01 -> 3.20 Gpaths/s) */
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(128) hw6_path_kernel(const DGltfScene sc, const DRenderParams rp) {
+__global__ void __launch_bounds__(128, B200RT_K6_MINB) hw6_path_kernel(const DGltfScene sc, const DRenderParams rp) {
     const int W = rp.cam.width, H = rp.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2;
     const long long n_tiles = (long long)tiles_x * tiles_y;
