@@ -60,12 +60,14 @@ def build_cuda(force=False, verbose=False):
     if verbose:
         common += ["-Xptxas", "-v"]
     objs = []
-    # analytic kernels: no FMA contraction (bit-exact hw1/hw2); path tracer: default FMA
-    units = (("b200rt.cu", []), ("upload.cu", []), ("scheduler.cu", []), ("multi_gpu.cu", []), ("noalloc.cu", []),
-             ("analytic_kernels.cu", ["-fmad=false"]))
+    # analytic kernels: hw1 / hw2 without FMA contraction (bit-exact), the Monte-Carlo modes of the same file as a
+    # second unit with the default contraction; path tracer: default FMA
+    units = (("b200rt.cu", [], None), ("upload.cu", [], None), ("scheduler.cu", [], None), ("multi_gpu.cu", [], None),
+             ("noalloc.cu", [], None), ("analytic_kernels.cu", ["-fmad=false"], None),
+             ("analytic_kernels.cu", ["-DB200RT_ANALYTIC_MC_UNIT"], "analytic_mc.o"))
     procs = []
-    for src, extra in units:        # the units compile concurrently (scheduler.cu holds the big kernels)
-        obj = os.path.join(LIB, src.replace(".cu", ".o"))
+    for src, extra, obj_name in units:        # the units compile concurrently (scheduler.cu holds the big kernels)
+        obj = os.path.join(LIB, obj_name or src.replace(".cu", ".o"))
         cmd = common + extra + ["-c", os.path.join(cu, src), "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)

@@ -1,7 +1,11 @@
 // K1 (hw1 primary cast), K2 (hw2 Whitted), K3 (hw3 / hw4 analytic path tracers), K7 (hw5 mixed figures) for sm_100a.
-// Compiled with -fmad=false: every float operation below is written in the reference's own
-// order and with its float/double promotions, so that the deterministic configs (hw1, hw2)
-// reproduce primary-hit indices and radiance bit for bit (north_star).
+// This file is compiled TWICE (build.py):
+//   * with -fmad=false: K1, K2 and the scene upload.  Every float operation is written in the reference's own order
+//     and with its float/double promotions, so that the deterministic configs (hw1, hw2) reproduce primary-hit
+//     indices and radiance bit for bit (north_star);
+//   * with -DB200RT_ANALYTIC_MC_UNIT and the compiler's default FMA contraction: K3 and K7, the Monte-Carlo modes,
+//     whose parity is statistical -- a third of their arithmetic fuses.  Each unit has its own __constant__ copy of
+//     the scene; analytic_upload fills both.
 //   hw1: hw1/src/scene.cpp:7-30, hw1/src/primitives.cpp:24-91
 //   hw2: hw2/src/scene.cpp:8-99, hw2/src/primitives.cpp:25-137, hw2/src/light_source.cpp:9-23
 //   hw4: hw4/src/scene.cpp:10-128, hw4/src/include/distributions.h:46-205, hw4/src/primitives.cpp:9-118
@@ -12,7 +16,14 @@
 
 namespace b200rt {
 
-__constant__ DAnalyticScene g_scene;
+static __constant__ DAnalyticScene g_scene;
+
+#ifdef B200RT_ANALYTIC_MC_UNIT
+cudaError_t analytic_mc_upload(const DAnalyticScene &staged, cudaStream_t stream) {
+    return cudaMemcpyToSymbolAsync(g_scene, &staged, sizeof(staged), 0, cudaMemcpyHostToDevice, stream);
+}
+#else
+cudaError_t analytic_mc_upload(const DAnalyticScene &staged, cudaStream_t stream);
 
 namespace {
 // Host restatement of Quaternion::operator* / transform with the reference's operation order (negated cross,
@@ -37,10 +48,13 @@ cudaError_t analytic_upload(const DAnalyticScene &scene, cudaStream_t stream) {
             m[0 + c] = t.x; m[3 + c] = t.y; m[6 + c] = t.z;
         }
         const bool ident = r[0] == 0.f && r[1] == 0.f && r[2] == 0.f && r[3] == 1.f;
-        m[9] = ident ? 1.f : 0.f; m[10] = m[11] = 0.f;
+        m[9] = ident ? 1.f : 0.f; m[10] = m[11] = m[15] = 0.f;
+        for (int c = 0; c < 3; c++) m[12 + c] = 1.f / staged.prims[k].data[c];
     }
-    return cudaMemcpyToSymbolAsync(g_scene, &staged, sizeof(staged), 0, cudaMemcpyHostToDevice, stream);
+    const cudaError_t e = cudaMemcpyToSymbolAsync(g_scene, &staged, sizeof(staged), 0, cudaMemcpyHostToDevice, stream);
+    return e != cudaSuccess ? e : analytic_mc_upload(staged, stream);
 }
+#endif
 
 namespace {
 
@@ -93,6 +107,35 @@ __device__ __forceinline__ bool box_slabs(V3 s, V3 o, V3 d, float &t, bool &insi
     return true;
 }
 
+// Monte-Carlo modes (FAST): the same tests with one approximate reciprocal (MUFU.RCP, 1 ulp) where the reference
+// divides -- an IEEE division is ~10 instructions, and an ellipsoid test had eight of them.  Their parity is
+// statistical; hw1 / hw2 never come here.
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ bool quadratic_fast(float a, float b, float c, float &t, bool &inside) {
+    const float d = b * b - 4 * a * c;
+    if (d <= 0) return false;
+    const float sq = sqrt_fast(d), inv = rcp_fast(2 * a);
+    float x1 = (-b - sq) * inv, x2 = (-b + sq) * inv;
+    if (x1 > x2) { const float s = x1; x1 = x2; x2 = s; }
+    if (x2 < 0) return false;
+    if (x1 < 0) { t = x2; inside = true; } else { t = x1; inside = false; }
+    return true;
+}
+__device__ __forceinline__ bool box_slabs_fast(V3 s, V3 o, V3 d, float &t, bool &inside) {
+    const V3 inv = mk(rcp_fast(d.x), rcp_fast(d.y), rcp_fast(d.z));
+    const V3 ts1 = (-1.f * s - o) * inv;
+    const V3 ts2 = (s - o) * inv;
+    const float t1x = smin(ts1.x, ts2.x), t2x = smax(ts1.x, ts2.x);
+    const float t1y = smin(ts1.y, ts2.y), t2y = smax(ts1.y, ts2.y);
+    const float t1z = smin(ts1.z, ts2.z), t2z = smax(ts1.z, ts2.z);
+    const float t1 = smax(smax(t1x, t1y), t1z);
+    const float t2 = smin(smin(t2x, t2y), t2z);
+    if (t1 > t2 || t2 < 0) return false;
+    if (t1 < 0) { inside = true; t = t2; } else { inside = false; t = t1; }
+    return true;
+}
+
 // World -> local of a ray for figure k.  FAST (Monte-Carlo modes): the precomputed 3x3 frame with explicit fused
 // multiply-adds (this file is compiled -fmad=false for hw1 / hw2), nothing at all for identity rotations; otherwise the
 // reference's two quaternion sandwiches in its own operation order (hw1 / hw2: bit-exact images).
@@ -135,6 +178,15 @@ __device__ __forceinline__ bool hit_prim(int k, V3 o, V3 d, bool plane_tmax, AHi
     to_local<FAST>(k, f, o, d, lo, ld);
     V3 n = mk(0, 0, 0);
     if (f.type == B200RT_PRIM_ELLIPSOID) {
+        if constexpr (FAST) {
+            const V3 ir = ld3(g_scene.frame[k] + 12);
+            const V3 orr = lo * ir, dr = ld * ir;
+            if (!quadratic_fast(dot(dr, dr), 2.f * dot(orr, dr), dot(orr, orr) - 1, h.t, h.inside)) return false;
+            if (WANT_N) {
+                n = (lo + h.t * ld) * (ir * ir);      // (normalised once, in world space)
+                if (h.inside) n = -1.f * n;
+            }
+        } else {
         const V3 r = ld3(f.data);
         const V3 orr = lo / r, dr = ld / r;
         const float c = dot(orr, orr) - 1;
@@ -145,20 +197,21 @@ __device__ __forceinline__ bool hit_prim(int k, V3 o, V3 d, bool plane_tmax, AHi
             const V3 point = lo + h.t * ld;
             n = point / (r * r);
             if (h.inside) n = -1.f * n;
-            if (!FAST) n = rnorm(n);       // (FAST normalises once, in world space)
+            n = rnorm(n);
+        }
         }
     } else if (f.type == B200RT_PRIM_PLANE) {
         const V3 pn = ld3(f.data);
-        const float t = -dot(lo, pn) / dot(ld, pn);
+        const float t = FAST ? -dot(lo, pn) * rcp_fast(dot(ld, pn)) : -dot(lo, pn) / dot(ld, pn);
         if (!(t > 0 && (!plane_tmax || t < 1e4f))) return false;
         h.t = t;
         if (dot(ld, pn) > 0) { n = -1.f * pn; h.inside = true; } else { n = pn; h.inside = false; }
     } else {
         const V3 s = ld3(f.data);
-        if (!box_slabs(s, lo, ld, h.t, h.inside)) return false;
+        if (!(FAST ? box_slabs_fast(s, lo, ld, h.t, h.inside) : box_slabs(s, lo, ld, h.t, h.inside))) return false;
         if (WANT_N) {
             const V3 p = lo + h.t * ld;
-            n = p / s;
+            n = FAST ? p * ld3(g_scene.frame[k] + 12) : p / s;
             const float mx = smax(smax(fabsf(n.x), fabsf(n.y)), fabsf(n.z));
             if (fabsf(n.x) != mx) n.x = 0;
             if (fabsf(n.y) != mx) n.y = 0;
@@ -170,6 +223,7 @@ __device__ __forceinline__ bool hit_prim(int k, V3 o, V3 d, bool plane_tmax, AHi
     return true;
 }
 
+#ifndef B200RT_ANALYTIC_MC_UNIT
 // Camera of hw1/hw2 (pixel centre +0.5, evaluated in double: hw1/src/scene.cpp:26-27).
 __device__ __forceinline__ V3 camera_dir_center(const DCamera &c, int x, int y) {
     const float nx = (float)((double)c.tan_x * (2 * (x + 0.5) / c.width - 1));
@@ -197,11 +251,12 @@ __global__ void cast_kernel(const DCamera cam, float *__restrict__ out, int32_t 
     ids[i] = id;
 }
 
+#endif
 // ---- K2 ------------------------------------------------------------------------------------
 template <bool FAST>
 __device__ __forceinline__ int closest_prim(V3 o, V3 d, float tmax, bool plane_tmax, AHit &best) {
     int pos = -1;
-    if (FAST) {
+    if constexpr (FAST) {
         // candidates without normals; the winner's normal afterwards (one more test of ONE figure instead of a
         // local -> world transform + normalisation for every figure the ray pierces)
         for (int k = 0; k < g_scene.n_prims; k++) {
@@ -209,14 +264,15 @@ __device__ __forceinline__ int closest_prim(V3 o, V3 d, float tmax, bool plane_t
             if (hit_prim<false, true>(k, o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best.t = h.t; pos = k; }
         }
         if (pos >= 0) hit_prim<true, true>(pos, o, d, plane_tmax, best);
-        return pos;
-    }
-    for (int k = 0; k < g_scene.n_prims; k++) {
-        AHit h;
-        if (hit_prim<true, false>(k, o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best = h; pos = k; }
+    } else {
+        for (int k = 0; k < g_scene.n_prims; k++) {
+            AHit h;
+            if (hit_prim<true, false>(k, o, d, plane_tmax, h) && h.t <= tmax && (pos == -1 || h.t < best.t)) { best = h; pos = k; }
+        }
     }
     return pos;
 }
+#ifndef B200RT_ANALYTIC_MC_UNIT
 __device__ __forceinline__ bool occluded(V3 o, V3 d, float tmax) {
     for (int k = 0; k < g_scene.n_prims; k++) {
         AHit h;
@@ -325,6 +381,7 @@ __global__ void whitted_kernel(const DCamera cam, int ray_depth, float *__restri
     ids[i] = primary;
 }
 
+#else      // B200RT_ANALYTIC_MC_UNIT
 // ---- K3: hw4 Monte-Carlo path tracer over analytic primitives ---------------------------------
 // Iterative form of Scene::getColor (hw4/src/scene.cpp:50-108): L += T * emission per hit,
 // T *= bounce weight.  Sampling = Mix{Cosine, Mix{BoxLight | EllipsoidLight ...}}
@@ -333,31 +390,65 @@ __global__ void whitted_kernel(const DCamera cam, int ray_depth, float *__restri
 #define B200RT_PI_F 3.14159274f          /* const float PI = acos(-1) */
 #define B200RT_MAX_REJECTION 8           /* the reference loops unbounded */
 
-__device__ __forceinline__ float light_pdf_one(int k, V3 x, V3 d, V3 y, V3 yn) {
-    const b200rt_primitive &f = g_scene.prims[k];
-    const V3 xy = x - y;
-    if (f.type == B200RT_PRIM_BOX) {
-        const float sx = f.data[0], sy = f.data[1], sz = f.data[2];
-        const float s_total = 8 * (sy * sz + sx * sz + sx * sy);
-        return dot(xy, xy) / (s_total * fabsf(dot(d, yn)));
-    }
-    const V3 r = ld3(f.data);
-    V3 ly, unused;
-    to_local<true>(k, f, y, mk(0, 0, 0), ly, unused);
-    const V3 n = ly / r;
-    const V3 g = mk(n.x * r.y * r.z, r.x * n.y * r.z, r.x * r.y * n.z);
-    const float point_prob = 1.f / (4 * B200RT_PI_F * sqrtf(dot(g, g)));
-    return point_prob * dot(xy, xy) / fabsf(dot(d, yn));
-}
-// FigureLight::pdf (distributions.h:85-106): first hit plus the second hit from just behind it.
+// FigureLight::pdf (distributions.h:85-106) = the density of the first hit plus that of the second hit, found from
+// just behind the first.  Boxes and ellipsoids are convex: the two hits are the entry and the exit of ONE test (the
+// exit counts when it lies at least 1e-4 behind the entry, which is when the reference's second test finds it; an
+// origin inside the figure sees the exit only).  One world -> local transform and one root solve per emitter instead
+// of two of each plus a world -> local transform of every hit point.
 __device__ __forceinline__ float light_pdf(int k, V3 x, V3 d) {
-    AHit h1;
-    if (!hit_prim<true, true>(k, x, d, true, h1)) return 0.f;
-    if (isnan(h1.t)) return INFINITY;
-    float ans = light_pdf_one(k, x, d, x + h1.t * d, h1.n);
-    AHit h2;
-    if (!hit_prim<true, true>(k, x + (h1.t + 0.0001f) * d, d, true, h2)) return ans;
-    return ans + light_pdf_one(k, x, d, x + (h1.t + 0.0001f + h2.t) * d, h2.n);
+    const b200rt_primitive &f = g_scene.prims[k];
+    const float *m = g_scene.frame[k];
+    const V3 ir = ld3(m + 12);
+    V3 lo, ld;
+    to_local<true>(k, f, x, d, lo, ld);
+    const bool box = f.type == B200RT_PRIM_BOX;
+    float t1, t2;
+    if (box) {
+        const V3 s = ld3(f.data);
+        const V3 inv = mk(rcp_fast(ld.x), rcp_fast(ld.y), rcp_fast(ld.z));
+        const V3 ts1 = (-1.f * s - lo) * inv, ts2 = (s - lo) * inv;
+        t1 = smax(smax(smin(ts1.x, ts2.x), smin(ts1.y, ts2.y)), smin(ts1.z, ts2.z));
+        t2 = smin(smin(smax(ts1.x, ts2.x), smax(ts1.y, ts2.y)), smax(ts1.z, ts2.z));
+        if (t1 > t2 || t2 < 0) return 0.f;
+    } else {
+        const V3 orr = lo * ir, dr = ld * ir;
+        const float qa = dot(dr, dr), qb = 2.f * dot(orr, dr), qc = dot(orr, orr) - 1;
+        const float disc = qb * qb - 4 * qa * qc;
+        if (disc <= 0) return 0.f;
+        const float sq = sqrt_fast(disc), inv = rcp_fast(2 * qa);
+        t1 = (-qb - sq) * inv; t2 = (-qb + sq) * inv;
+        if (t1 > t2) { const float sw = t1; t1 = t2; t2 = sw; }
+        if (t2 < 0) return 0.f;
+    }
+    const bool inside = t1 < 0;
+    const float first = inside ? t2 : t1;
+    if (isnan(first)) return INFINITY;
+    const float dd = dot(d, d);
+    float s_total = 0.f;
+    if (box) { const float sx = f.data[0], sy = f.data[1], sz = f.data[2]; s_total = 8 * (sy * sz + sx * sz + sx * sy); }
+    // density of the hit at ray parameter t: |x - y|^2 / (area density^-1 * |d . n_y|)
+    auto term = [&](float t) {
+        const V3 lp = lo + t * ld;
+        V3 n = lp * ir;                    // box: p / s;  ellipsoid: p / r
+        float point_prob_inv;
+        if (box) {
+            const float mx = smax(smax(fabsf(n.x), fabsf(n.y)), fabsf(n.z));
+            if (fabsf(n.x) != mx) n.x = 0;
+            if (fabsf(n.y) != mx) n.y = 0;
+            if (fabsf(n.z) != mx) n.z = 0;
+            point_prob_inv = s_total;
+        } else {
+            const V3 r = ld3(f.data);
+            const V3 g = mk(n.x * r.y * r.z, r.x * n.y * r.z, r.x * r.y * n.z);
+            point_prob_inv = 4 * B200RT_PI_F * sqrt_fast(dot(g, g));
+            n = n * ir;                    // gradient direction p / r^2
+        }
+        const V3 yn = normal_to_world<true>(k, f, n);
+        return t * t * dd * rcp_fast(point_prob_inv * fabsf(dot(d, yn)));
+    };
+    float ans = term(first);
+    if (!inside && t2 - (t1 + 0.0001f) >= 0) ans += term(t2);
+    return ans;
 }
 
 __device__ __forceinline__ V3 light_sample(int k, V3 x, Rng &rng) {
@@ -703,8 +794,11 @@ __global__ void __launch_bounds__(128, B200RT_K7_MINB) hw5_path_kernel(const DGl
     flush_counters(rp.counters, tc);
 }
 
+#endif     // B200RT_ANALYTIC_MC_UNIT
+
 }  // namespace
 
+#ifndef B200RT_ANALYTIC_MC_UNIT
 cudaError_t launch_cast(const DCamera &cam, float *out, int32_t *ids, cudaStream_t stream) {
     const int n = cam.width * cam.height;
     cast_kernel<<<(n + 127) / 128, 128, 0, stream>>>(cam, out, ids);
@@ -717,7 +811,7 @@ cudaError_t launch_whitted(const DCamera &cam, int ray_depth, float *out, int32_
     whitted_kernel<<<(n + 63) / 64, 64, 0, stream>>>(cam, ray_depth, out, ids);
     return cudaGetLastError();
 }
-
+#else
 cudaError_t launch_pt_analytic(const DRenderParams &rp, bool hw3, cudaStream_t stream) {
     const long long tiles = (long long)((rp.cam.width + 7) / 8) * ((rp.cam.height + 3) / 4);
     const long long warps = tiles * rp.n_chunks;
@@ -734,5 +828,6 @@ cudaError_t launch_hw5(const DGltfScene &sc, const DRenderParams &rp, const int3
     hw5_path_kernel<<<(unsigned)blocks, 128, 0, stream>>>(sc, rp, light_order, n_lights, has_tris ? 1 : 0);
     return cudaGetLastError();
 }
+#endif
 
 }  // namespace b200rt

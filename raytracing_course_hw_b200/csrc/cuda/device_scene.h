@@ -136,8 +136,9 @@ struct DAnalyticScene {
     // Monte-Carlo modes (hw3 - hw5) only: the world -> local map p -> q p conj(q) of each figure as a row-major 3x3
     // matrix (built at upload by applying the reference's quaternion arithmetic to the basis vectors: it carries the
     // |q|^2 scale of non-unit quaternions), frame[k][9] != 0 marks an identity rotation (no transform at
-    // all).  hw1 / hw2 keep the two quaternion sandwiches per ray and figure: their images are bit-exact.
-    float frame[B200RT_MAX_PRIMS][12];
+    // all); frame[k][12..14] = 1 / data[0..2] (ellipsoid radii, box half sizes): the Monte-Carlo modes multiply where
+    // the reference divides.  hw1 / hw2 keep the two quaternion sandwiches per ray and figure: their images are bit-exact.
+    float frame[B200RT_MAX_PRIMS][16];
 };
 
 }  // namespace b200rt
