@@ -170,7 +170,7 @@ typedef struct b200rt_options {
 } b200rt_options;
 
 #define B200RT_FLAG_COUNTERS   1  /* also count node fetches / triangle tests / texture lookups */
-#define B200RT_FLAG_MEGAKERNEL 2  /* glTF modes: one-kernel-per-path variant instead of the wavefront pipeline */
+#define B200RT_FLAG_MEGAKERNEL 2  /* glTF modes (hw6 - hw8): one-kernel-per-path variant instead of the wavefront pipeline */
 #define B200RT_FLAG_REFERENCE_BVH 8 /* glTF modes: traverse the scene BVH exactly as given in the description (the reference's
                                       SAH tree) instead of the binned-SAH tree the library builds over the same triangles;
                                       results are identical up to closest-hit ties, the rebuilt tree tests ~20 % fewer boxes.
@@ -182,6 +182,12 @@ typedef struct b200rt_options {
                                        emitter (black background only; the image is bit-identical either way -- test aid) */
 #define B200RT_FLAG_EXPLICIT_CAMERA_STATE 32 /* wavefront: wf_generate stores the whole state record of a camera path
                                        instead of the direction only (bit-identical image -- test aid) */
+
+#define B200RT_FLAG_WAVEFRONT 128 /* hw6: always the wavefront pipeline.  By default hw6 scenes of up to
+                                       B200RT_HW6_PIXEL_KERNEL_MAX_TRIS triangles run the one-thread-per-pixel kernel (faster on
+                                       a handful of triangles: no path state to stream), larger ones the wavefront pipeline
+                                       (2x on the reference's practice6_2); both trace the same paths */
+#define B200RT_HW6_PIXEL_KERNEL_MAX_TRIS 2048
 
 #define B200RT_FLAG_NO_FIREFLY_CLAMP 64 /* hw7 / hw8: do not end a path when a bounce weight exceeds 6 in some channel (the
                                        reference's DIRTY_DENOISE_HACK_BUBEN, hw8/src/scene.cpp:7,161 -- biased, darkens).  The

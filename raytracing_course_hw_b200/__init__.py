@@ -21,6 +21,7 @@ FLAG_MEGAKERNEL = 2   # glTF modes: per-path megakernel instead of the wavefront
 FLAG_REFERENCE_BVH = 8  # glTF modes: traverse the description's BVH instead of the library's rebuilt one
 FLAG_NO_FIREFLY_CLAMP = 64  # hw7 / hw8: unbiased estimator instead of the reference's weight clamp at 6
 FLAG_KEEP_DARK_RAYS = 16
+FLAG_WAVEFRONT = 128  # hw6: the wavefront pipeline even for scenes small enough for the per-pixel kernel
 FLAG_EXPLICIT_CAMERA_STATE = 32
 FLAG_SERIAL_WAVES = 4  # wavefront: one wave in flight (stage times in stats() are then exclusive kernel times)
 

@@ -101,6 +101,7 @@ struct DGltfScene {
     uint32_t light_top_word[B200RT_LIGHT_TOP];
     int32_t light_top_start;
     int32_t hw8;                 // 1 = hw8 semantics (textures, shading-normal pdf), 0 = hw7
+    int32_t hw6;                 // 1 = hw6: the hw5 integrator (diffuse / mirror / dielectric) on these triangles (hw6_kernel.cuh)
     float weight_clamp;          // a bounce weight above this in any channel ends the path: 6 (reference), or FLT_MAX
     float bg[3];
     DTexels env;                 // null = absent

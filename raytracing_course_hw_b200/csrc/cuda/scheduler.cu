@@ -68,7 +68,7 @@ int ensure_wave(b200rt_ctx *ctx, size_t slots) {
 }
 
 // Wavefront render of sample indices [spp_begin, spp_end): waves of (all pixels) x S_w samples.
-template <bool HW8, bool COUNT>
+template <bool HW8, bool COUNT, bool HW6 = false>
 int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
     const int W = rp.cam.width, H = rp.cam.height;
     WaveParams wp{};
@@ -103,6 +103,9 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         ctx->blocks_light[COUNT] = std::max(1, nb) * ctx->num_sms;
     }
     const bool lights = ctx->gs.n_light_tris > 0;
+    // paths that need no light-pdf query skip the light stage; hw6's mirror / dielectric bounces never have one, so
+    // there the shortcut is not optional
+    const bool direct_on = ctx->wf_direct || HW6;
     // a light-queue entry carries the light-cut mask above bit 26: waves of 2^26 slots or more (frames above 67 M
     // pixels) leave it out and the light stage tests the cut boxes itself
     const int pack_mask = per * s_w < (1ll << B200RT_WF_MASK_SHIFT) ? 1 : 0;
@@ -122,7 +125,7 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
         CK(cudaMemsetAsync(wb.ctr - 4, 0, 4 * (B200RT_MAX_DEPTH + 2) * sizeof(int), st));
         // camera paths carry implicit state through their first extend / shade unless the path is one bounce long
         const int first_implicit = (rp.ray_depth > 1 && ctx->wf_first_implicit) ? 1 : 0;
-        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters, W % 8 == 0 && H % 4 == 0, !first_implicit);
+        wf_generate<<<flat_blocks, 128, 0, st>>>(wp, wb, ctx->counters, W % 8 == 0 && H % 4 == 0, !first_implicit, !HW6);
         (*launches)++;
         int *qa = wb.queue[0], *qb = wb.queue[2];
         for (int b = 0; b < rp.ray_depth; b++) {
@@ -137,17 +140,17 @@ int render_wavefront(b200rt_ctx *ctx, const DRenderParams &rp, int *launches) {
                               ctx->gs.bg[0] == 0.f && ctx->gs.bg[1] == 0.f && ctx->gs.bg[2] == 0.f) ? 1 : 0;
             if (lights && !last) {
                 ctx->stamp(true, 1, st);
-                wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, ctx->wf_direct ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop, first, pack_mask);
+                wf_shade<HW8, COUNT, false, HW6><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, wb.queue[1], c + 2, direct_on ? qb : nullptr, c + 3, b, ctx->lut_srgb, ctx->counters, drop, first, pack_mask);
                 ctx->stamp(false, 1, st);
                 ctx->stamp(true, 2, st);
-                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, ctx->wf_direct && pack_mask, drop);
+                wf_light<COUNT><<<ctx->blocks_light[COUNT], 128, 0, st>>>(ctx->gs, wb, wb.queue[1], c + 2, c + 1, qb, c + 3, ctx->counters, ctx->wf_batch_light, ctx->wf_leaf_t_light, direct_on && pack_mask, drop);
                 ctx->stamp(false, 2, st);
                 (*launches) += 3;
             } else {
                 // last bounce: the next ray is never traced (recLimit == 0), so its pdf is not needed
                 ctx->stamp(true, 1, st);
-                if (last) wf_shade<HW8, COUNT, true><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
-                else wf_shade<HW8, COUNT><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
+                if (last) wf_shade<HW8, COUNT, true, HW6><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
+                else wf_shade<HW8, COUNT, false, HW6><<<flat_blocks, 128, 0, st>>>(ctx->gs, wb, wp, qa, c - 1, qb, lights ? c + 2 : c + 3, nullptr, nullptr, b, ctx->lut_srgb, ctx->counters, 0, first);
                 ctx->stamp(false, 1, st);
                 (*launches) += 2;
             }
@@ -230,7 +233,17 @@ static int render_impl(b200rt_ctx *ctx, int32_t width, int32_t height, int32_t s
         CK(launch_hw5(ctx->gs, rp, ctx->hw5_light_order, ctx->hw5_n_lights, ctx->hw5_has_tris, ctx->stream));
         launches++;
     }
-    else if (d.mode == B200RT_MODE_HW6) {
+    else if (d.mode == B200RT_MODE_HW6 && !(ctx->flags & B200RT_FLAG_MEGAKERNEL) &&
+             ((ctx->flags & B200RT_FLAG_WAVEFRONT) || ctx->n_dtris > B200RT_HW6_PIXEL_KERNEL_MAX_TRIS)) {
+        // the hw6 integrator as the shade stage of the wavefront pipeline (persistent traversal kernels of hw7 / hw8):
+        // practice6_1 (17 k triangles) 1.78 -> 2.68, practice6_2 (145 k) 0.55 -> 1.13 Gpaths/s; a scene of a few dozen
+        // triangles is 15 % faster in the per-pixel kernel (profiles/r02_hw6_wavefront.log), hence the size rule
+        const int wrc = (ctx->flags & B200RT_FLAG_COUNTERS) ? render_wavefront<false, true, true>(ctx, rp, &launches)
+                                                             : render_wavefront<false, false, true>(ctx, rp, &launches);
+        if (wrc) return wrc;
+        n_chunks = 0;
+    }
+    else if (d.mode == B200RT_MODE_HW6) {      // one thread per pixel (K6): small scenes, and B200RT_FLAG_MEGAKERNEL
         const long long warps = (long long)((width + 7) / 8) * ((height + 3) / 4) * n_chunks;
         const long long blocks = (warps * 32 + 127) / 128;
         if (blocks > 0x7fffffffll) return fail(ctx, B200RT_ERR_INVALID, "grid too large");

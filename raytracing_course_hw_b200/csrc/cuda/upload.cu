@@ -253,6 +253,7 @@ int upload_gltf(b200rt_ctx *ctx, const b200rt_scene_desc *s) {
 
     DGltfScene g{};
     g.hw8 = s->mode == B200RT_MODE_HW8;
+    g.hw6 = s->mode == B200RT_MODE_HW6;
     g.weight_clamp = (ctx->flags & B200RT_FLAG_NO_FIREFLY_CLAMP) ? 3.402823466e38f : 6.f;
     for (int k = 0; k < 3; k++) g.bg[k] = s->bg_color[k];
     int rc;

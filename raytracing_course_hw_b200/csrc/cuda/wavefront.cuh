@@ -17,6 +17,7 @@
 // distributions.h:122-165).
 #pragma once
 #include "gltf_kernel.cuh"
+#include "hw6_kernel.cuh"      // hw6_surface / hw6_finish: the hw6 integrator as a shade stage
 #include "wave_state.h"
 
 namespace b200rt {
@@ -96,7 +97,7 @@ struct TravStack {
 
 // full = 0: only the ray direction is stored -- the first extend / shade of the wave (`first`) know the rest of a
 // camera path's state without reading it (origin = camera, throughput 1, radiance 0, Philox key / counter from the slot).
-__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters, const bool dense, const bool full) {
+__global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters *counters, const bool dense, const bool full, const bool unit_dir = true) {
     const int n_slots = wp.n_tiles * 32 * wp.s_count;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -112,7 +113,8 @@ __global__ void wf_generate(const WaveParams wp, const WaveBuffers wb, DCounters
             const float fx = (float)px + u01(j.x), fy = (float)py + u01(j.y);
             const float nx = wp.cam.tan_x * (2.f * fx / (float)wp.cam.width - 1.f);
             const float ny = wp.cam.tan_y * (2.f * fy / (float)wp.cam.height - 1.f);
-            const V3 d = normalize(nx * cright - ny * cup + cfwd);
+            const V3 dv = nx * cright - ny * cup + cfwd;
+            const V3 d = unit_dir ? normalize(dv) : dv;      // hw6's camera does not normalise (hw6/src/scene.cpp:107-126)
             st_state(&wb.ray_d[slot], make_float4(d.x, d.y, d.z, 0.f));
             if (full) {
             st_state(&wb.ray_o[slot], make_float4(cpos.x, cpos.y, cpos.z, __uint_as_float(pixel)));
@@ -279,7 +281,9 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 // L1 and pushes the 128-register build into spills), and prefetch.global.L2 of the next items' state records and hit
 // records (+8 % / +24 %).
 // LAST = the path's final bounce: only the emission of the hit is added (surface_emission), nothing continues.
-template <bool HW8, bool COUNT, bool LAST = false>
+// HW6 = hw6's integrator (hw6_kernel.cuh) instead of the metallic-roughness surface: a diffuse hit goes on to the light
+// stage like every hw7 / hw8 hit, a mirror / dielectric hit has its weight already and joins the next bounce directly.
+template <bool HW8, bool COUNT, bool LAST = false, bool HW6 = false>
 __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(const DGltfScene sc, const WaveBuffers wb, const WaveParams wp, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *q_out, int *n_out, int *q_direct, int *n_direct, int bounce,
                                                 const float *__restrict__ lut_srgb_g, DCounters *counters, const int drop_dark = 0, const int first = 0,
@@ -336,11 +340,18 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                 // key = pixel, counter = (global sample index, block of this bounce); both ride in spare state lanes
                 const uint4 rnd = philox4x32_10(__float_as_uint(ra.w), 16u * (uint32_t)(bounce + 1), __float_as_uint(ro.w), wp.seed);
                 BounceOut bo;
-                SurfRec rec;
-                load_surf_rec<HW8>(sc, (int)(bits & 0x7FFFFFFFu), rec);
-                cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, rec, (bits >> 31) != 0, L, T, rnd, tc, bo);
-                if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T, sc.weight_clamp);
-                if (cont && has_lights && q_direct) {
+                bool specular = false;
+                if constexpr (HW6) {
+                    cont = hw6_surface<COUNT>(sc, o, d, h.x, (int)(bits & 0x7FFFFFFFu), (bits >> 31) != 0, rnd, L, T, tc, bo, specular);
+                    if (cont && specular && q_direct) direct = true;      // (without emitters q_out IS the next bounce's queue)
+                    if (cont && !specular && !has_lights) hw6_finish(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T);
+                } else {
+                    SurfRec rec;
+                    load_surf_rec<HW8>(sc, (int)(bits & 0x7FFFFFFFu), rec);
+                    cont = shade_surface<HW8, COUNT>(sc, lut_srgb, lut_lin, o, d, h.x, h.y, h.z, rec, (bits >> 31) != 0, L, T, rnd, tc, bo);
+                    if (cont && !has_lights) cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, 0, T, sc.weight_clamp);
+                }
+                if (cont && !specular && has_lights && q_direct) {
                     // A ray that misses the boxes around the emitters has a light pdf of exactly 0
                     // (light_boxes_hit): the bounce is finished here and the path skips the light stage
                     // (its queue entry, bsdf round trip and refill slot).
@@ -349,7 +360,8 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
                         if (COUNT) tc.light_node_tests++;
                         answered++;
                         direct = true;
-                        cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T, sc.weight_clamp);
+                        if constexpr (HW6) hw6_finish(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T);
+                        else cont = finish_bounce(bo.brdf, bo.pdf_partial, bo.absdot, 0.f, sc.n_light_tris, T, sc.weight_clamp);
                         bo.pdf_partial = 0.f;
                         // drop_dark (set when the NEXT bounce is the last one and the background is black): that
                         // bounce only adds the emission of what it hits, and a ray that misses the emitters' boxes
@@ -488,7 +500,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScen
                     V3 T = mk(th.x, th.y, th.z);
                     // drop_dark: see wf_shade.  total == 0 means the ray pierces no emissive triangle within T_MAX (every
                     // hit adds a positive term), so the last bounce would add nothing: the path ends here
-                    if (finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T, sc.weight_clamp) && !(drop_dark && total == 0.f)) {
+                    bool go;
+                    if (sc.hw6) { hw6_finish(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T); go = true; }
+                    else go = finish_bounce(mk(bs.x, bs.y, bs.z), th.w, ld_state(&wb.ray_d[p]).w, total, sc.n_light_tris, T, sc.weight_clamp);
+                    if (go && !(drop_dark && total == 0.f)) {
                         st_state(&wb.thr[p], make_float4(T.x, T.y, T.z, 0.f));
                         push_pending = true;
                         push_p = p;

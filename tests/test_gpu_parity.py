@@ -358,6 +358,67 @@ def test_hw6_matches_port_on_same_stream(renderer, path, frac):
     assert st["paths"] == 128 * 96 * 16
 
 
+@pytest.mark.parametrize("path", ["hw6/practice7_1_glass.gltf", "hw7/practice7_1.gltf"])
+def test_hw6_wavefront_and_per_pixel_kernel_trace_the_same_paths(path):
+    """hw6 runs through the wavefront pipeline (hw6_surface / hw6_finish as its shade stage; the default above
+    B200RT_HW6_PIXEL_KERNEL_MAX_TRIS triangles) and through the one-thread-per-pixel kernel K6 (small scenes,
+    FLAG_MEGAKERNEL): the same two device functions on the same Philox stream.  The
+    wavefront drops rays that provably add nothing (FLAG_KEEP_DARK_RAYS turns that off), so with the flag the ray
+    counts are EQUAL; the images agree to float rounding (different kernels, different FMA contraction) on
+    all but the few pixels where a rounding flips a hit at a triangle edge."""
+    sc = ou.load_scene(os.path.join(S, path), width=160, height=120, samples=8, mode=6)
+    out = {}
+    W = rt.FLAG_WAVEFRONT       # (these scenes are small enough for the per-pixel kernel to be the default)
+    for name, flags in (("wave", W | rt.FLAG_KEEP_DARK_RAYS), ("wave-default", W), ("wave-counting", W | rt.FLAG_KEEP_DARK_RAYS | rt.FLAG_COUNTERS),
+                        ("pixel", rt.FLAG_MEGAKERNEL)):
+        r = rt.Renderer(flags=flags)
+        try:
+            out[name] = (_render(r, sc, 0, 8), r.stats())
+        finally:
+            r.close()
+    a, b = out["wave"][0], out["pixel"][0]
+    assert out["wave"][1]["paths"] == out["pixel"][1]["paths"] == 160 * 120 * 8
+    assert abs(int(out["wave"][1]["rays"]) - int(out["pixel"][1]["rays"])) <= 1e-3 * int(out["pixel"][1]["rays"])
+    # (the per-pixel kernel also makes the last bounce's light-pdf query, whose weight multiplies a ray that is never traced)
+    assert 0.7 * int(out["pixel"][1]["light_queries"]) <= int(out["wave"][1]["light_queries"]) <= 1.001 * int(out["pixel"][1]["light_queries"])
+    close = np.abs(a - b).max(axis=2) <= 1e-3 * (np.abs(b).max(axis=2) + 1e-2)
+    assert close.mean() >= 0.99, close.mean()
+    assert abs(a.mean() - b.mean()) <= 2e-3 * b.mean()
+    # dropping dark rays and counting change nothing in the image
+    assert np.array_equal(out["wave-default"][0], a) and np.array_equal(out["wave-counting"][0], a)
+    assert out["wave-default"][1]["rays"] <= out["wave"][1]["rays"]
+
+
+@pytest.mark.parametrize("name,mode,frac", [("big:hw7/practice7_2.gltf", 0, 0.99), ("big:hw7/practice7_3.gltf", 0, 0.99),
+                                            ("big:hw6/practice6_1.gltf", 6, 0.97), ("big:hw6/practice6_2.gltf", 6, 0.97),
+                                            ("bench268k", 0, 0.98)])
+def test_large_scenes_match_port_on_same_stream(name, mode, frac):
+    """The sizes the headline is quoted on (the reference's large example scenes, copied next to its binaries by
+    oracle/build_ref.sh, and the 268 k-triangle bench scene) at a small frame: the product's default scheduling for the
+    scene against the port on the same Philox stream -- image, mean, and with FLAG_KEEP_DARK_RAYS the ray and
+    light-query counts.  hw6 scenes of this size run the wavefront pipeline."""
+    path = _scene_file(name)
+    if path is None:
+        pytest.skip("the reference's example scenes are not on this machine (oracle/build_ref.sh copies them)")
+    sc = ou.load_scene(path, width=96, height=64, samples=8, **({"mode": mode} if mode else {}))
+    r = rt.Renderer(flags=rt.FLAG_KEEP_DARK_RAYS)
+    try:
+        acc = _render(r, sc)
+        st = r.stats()
+    finally:
+        r.close()
+    port = ou.port_render(sc, 1, want_counters=True)
+    ok, got = _mean_close(acc, port["accum"], 8, frac, rel=5e-2)
+    assert ok, got
+    assert abs(acc.mean() - port["accum"].mean()) <= 2e-2 * port["accum"].mean()
+    rays, rays_port = int(st["rays"]), int(port["counters"][0])
+    assert abs(rays - rays_port) <= 1e-3 * rays_port, (rays, rays_port)
+    lq, lq_port = int(st["light_queries"]), int(port["counters"][3])
+    assert 0.7 * lq_port <= lq <= 1.005 * lq_port, (lq, lq_port)
+    assert st["paths"] == 96 * 64 * 8
+    print(f"{name}: pixels within 5 % {got:.4f}, rays {rays} vs {rays_port}, light queries {lq} vs {lq_port}")
+
+
 # ---------------------------------------------------------------- MC: north_star statistical bar
 def _linear(img8):
     return ou.inv_display(img8)
