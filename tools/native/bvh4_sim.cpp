@@ -34,7 +34,8 @@ static bool tri_hit(const b200rt_triangle &T, const Ray &r, float tmax, float &t
     t = (e2[0] * qv[0] + e2[1] * qv[1] + e2[2] * qv[2]) * id;
     return u >= 0 && v >= 0 && u + v <= 1 && t > 0 && t < tmax;
 }
-struct Q4 { int n; uint32_t child[4]; };   // child = node id of the binary tree (leaf or inner)
+#define MAX_WIDE 16
+struct Q4 { int n; uint32_t child[MAX_WIDE]; };   // child = node id of the binary tree (leaf or inner)
 int main(int argc, char **argv) {
     if (argc < 2) return 2;
     b200rt_host_scene *hs = nullptr;
@@ -47,6 +48,7 @@ int main(int argc, char **argv) {
     for (int i = 0; i < d->n_tris; i++) tris[i] = d->tris[bvh.order[i]];
     auto area = [&](uint32_t i) { float x = N[i].aabb_max[0] - N[i].aabb_min[0], y = N[i].aabb_max[1] - N[i].aabb_min[1], z = N[i].aabb_max[2] - N[i].aabb_min[2]; return x * y + y * z + x * z; };
     const int wide = argc > 2 ? atoi(argv[2]) : 4;
+    if (wide < 2 || wide > MAX_WIDE) { fprintf(stderr, "width must be 2 .. %d\n", MAX_WIDE); return 2; }
     std::vector<Q4> q4(N.size());
     for (uint32_t i = 0; i < N.size(); i++) {
         Q4 &q = q4[i]; q.n = 0;
@@ -104,7 +106,7 @@ int main(int argc, char **argv) {
                 if (N[cur].left) {
                     const Q4 &q = q4[cur];
                     steps4++; boxes4 += wide;
-                    float t[8]; bool h[8]; int best = -1;
+                    float t[MAX_WIDE]; bool h[MAX_WIDE]; int best = -1;
                     for (int k = 0; k < q.n; k++) { h[k] = slab(N[q.child[k]].aabb_min, N[q.child[k]].aabb_max, r, tb4, t[k]); if (h[k] && (best < 0 || t[k] < t[best])) best = k; }
                     if (best >= 0) {
                         for (int k = q.n - 1; k >= 0; k--) if (h[k] && k != best) { st[sp++] = q.child[k]; push4++; }
