@@ -23,7 +23,10 @@
 namespace b200rt {
 
 #ifndef B200RT_EXT_MINB
-#define B200RT_EXT_MINB 9        /* min resident blocks per SM asked of ptxas for extend / light (sweep: profiles/r01_sweep_quantised_nodes.log) */
+#define B200RT_EXT_MINB 10       /* min resident blocks per SM asked of ptxas for extend (48 registers; profiles/r02_sweep_hit_on_accept.log) */
+#endif
+#ifndef B200RT_LIGHT_MINB
+#define B200RT_LIGHT_MINB 9      /* ... and for light (56 registers; sweep: profiles/r01_sweep_quantised_nodes.log) */
 #endif
 #ifndef B200RT_SHADE_MINB
 #define B200RT_SHADE_MINB 4
@@ -161,8 +164,8 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
     int p = 0;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
     QRay qr = {};
-    float tbest = 0.f, hu = 0.f, hv = 0.f, hdet = 0.f;
-    uint32_t htri = B200RT_WF_MISS, cur = 0;
+    float tbest = 0.f;
+    uint32_t cur = 0;
     unsigned node_tests = 0, tri_tests = 0;
 #ifdef B200RT_DBG_PHASE
     unsigned long long dbg[8] = {};
@@ -190,7 +193,7 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
 #endif
                     d = mk(rd.x, rd.y, rd.z);
                     qr = make_qray(sc.q, o, d);
-                    tbest = B200RT_TMAX; htri = B200RT_WF_MISS; hu = hv = hdet = 0.f;
+                    tbest = B200RT_TMAX;
                     sp = 0;
                     cur = sc.root;
                     active = true;
@@ -211,13 +214,14 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
             if (inner_mask == 0 || __popc(leaf_mask) >= leaf_t) { DBG_PHASE(2, 1); DBG_PHASE(3, __popc(leaf_mask)); }
             else { DBG_PHASE(0, 1); DBG_PHASE(1, __popc(inner_mask)); DBG_PHASE(6, __popc(leaf_mask)); DBG_PHASE(7, 32 - __popc(leaf_mask | inner_mask)); }
 #endif
-            // end of a subtree: next stacked node, or the ray is finished
+            // end of a subtree: next stacked node, or the ray is finished.  The hit record is written whenever a closer
+            // hit is accepted, not carried to the end of the ray: four registers less through the box steps, which is
+            // what lets the kernel run 10 blocks per SM at 48 registers without spills (a miss is written here)
             auto do_pop = [&]() {
                 bool got = false;
                 if (sp > 0) { cur = stack.pop(sp); got = true; }
                 if (!got) {
-                    const uint32_t bits = htri == B200RT_WF_MISS ? B200RT_WF_MISS : (htri | (hdet > 0.f ? 0x80000000u : 0u));
-                    st_state(&wb.hit[p], make_float4(tbest, hu, hv, __uint_as_float(bits)));
+                    if (tbest == B200RT_TMAX) st_state(&wb.hit[p], make_float4(B200RT_TMAX, 0.f, 0.f, __uint_as_float(B200RT_WF_MISS)));
                     active = false;
                 }
             };
@@ -229,7 +233,10 @@ __global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_extend(const DGltfSce
                         const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
                         if (COUNT) tri_tests++;
                         float t, u, v, det;
-                        if (tri_hit(v0, e1, e2, o, d, tbest, t, u, v, det)) { tbest = t; hu = u; hv = v; htri = i; hdet = det; }
+                        if (tri_hit(v0, e1, e2, o, d, tbest, t, u, v, det)) {
+                            tbest = t;
+                            st_state(&wb.hit[p], make_float4(t, u, v, __uint_as_float(i | (det > 0.f ? 0x80000000u : 0u))));
+                        }
                     }
                     do_pop();
                 }
@@ -391,7 +398,7 @@ __global__ void __launch_bounds__(128, COUNT ? 3 : B200RT_SHADE_MINB) wf_shade(c
 
 // ---- persistent light-pdf traversal + end of the bounce ---------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(128, B200RT_EXT_MINB) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
+__global__ void __launch_bounds__(128, B200RT_LIGHT_MINB) wf_light(const DGltfScene sc, const WaveBuffers wb, const int *__restrict__ q_in,
                                                 const int *__restrict__ n_in, int *cursor, int *q_out, int *n_out, DCounters *counters,
                                                 const int batch, const int leaf_t, const bool filtered, const int drop_dark = 0) {
     const int n = *n_in;
