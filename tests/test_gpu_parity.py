@@ -476,6 +476,32 @@ def test_rmse_and_luminance_against_4096spp_reference(renderer, name, path, kind
     assert abs(lum - truth.mean()) <= 0.01 * truth.mean(), (lum, truth.mean())
 
 
+@pytest.mark.parametrize("name,path", [("hw6_practice7_1_128x96", "hw7/practice7_1.gltf"), ("hw6_practice7_1_glass_128x96", "hw6/practice7_1_glass.gltf")])
+def test_hw6_wavefront_rmse_and_luminance_against_4096spp_reference(name, path):
+    """The north_star statistical bar for hw6 through the WAVEFRONT pipeline (the fixtures are small enough for the
+    per-pixel kernel to be the default, which the parametrised test above covers): RMSE against the hw6 binary's
+    4096-spp image no worse than the binary's own at equal spp, mean luminance within 1 %."""
+    spp = 64
+    sc = ou.load_scene(os.path.join(S, path), width=128, height=96, samples=spp, mode=6)
+    truth = _linear(ou.golden(name + "_spp4096"))
+    r = rt.Renderer(flags=rt.FLAG_WAVEFRONT)
+    try:
+        r.upload(sc)
+        r.render(0, spp)
+        gpu = _linear(r.resolve(spp))
+        r.clear()
+        r.render(0, 1024)
+        lum = _linear(r.resolve(1024)).mean()
+    finally:
+        r.close()
+    ref_equal_spp = _linear(ou.port_render(sc, 0)["rgb"])
+    rmse_gpu = np.sqrt(((gpu - truth) ** 2).mean())
+    rmse_ref = np.sqrt(((ref_equal_spp - truth) ** 2).mean())
+    shared = np.sqrt((1 + spp / 4096) / (1 - spp / 4096))      # (see the test above)
+    assert rmse_gpu <= 1.05 * shared * rmse_ref + 1e-4, (rmse_gpu, rmse_ref, shared)
+    assert abs(lum - truth.mean()) <= 0.01 * truth.mean(), (lum, truth.mean())
+
+
 # ---------------------------------------------------------------- K5 resolve
 @pytest.mark.parametrize("path", ["hw8/sphere_emissive.gltf", "hw7/practice7_4.gltf"])
 def test_resolve_bytes_match_port(renderer, path):
