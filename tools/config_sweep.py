@@ -112,6 +112,9 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--cpu-budget", type=float, default=4.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--grid", action="store_true",
+                    help="the resolution x spp grids of SURVEY 8d instead of the config list (GPU only: C3 = the five hw4 scenes at "
+                         "512^2 / 1080p x 64 .. 4096 spp, C5 = sphere_emissive and the bench scene at 1080p / 4K x 64 .. 1024 spp)")
     a = ap.parse_args()
     q = a.quick
     room = bench.scene_path(270000)
@@ -143,6 +146,16 @@ def main():
     C.append(("C5", "b200room (tools/make_scene.py --tris 270000)", 8, room, False, 8, 3840, 2160, 64 if not q else 4, (320, 180, 4)))
     C.append(("C5", "b200room (tools/make_scene.py --tris 270000)", 8, room, False, 8, 1920, 1080, 256 if not q else 4, None))
 
+    if a.grid:
+        C = []
+        for k in (1, 2, 3, 4, 5):
+            for w, h in ((512, 512), (1920, 1080)):
+                for spp in (64, 256, 1024, 4096):
+                    C.append(("C3", f"hw4/practice3_{k}.txt", 4, os.path.join(SC, f"hw4/practice3_{k}.txt"), True, 0, w, h, spp, None))
+        for label, scene in (("hw8/sphere_emissive.gltf", os.path.join(SC, "hw8/sphere_emissive.gltf")), ("b200room (tools/make_scene.py --tris 270000)", room)):
+            for w, h in ((1920, 1080), (3840, 2160)):
+                for spp in (64, 256, 1024):
+                    C.append(("C5", label, 8, scene, False, 8, w, h, spp, None))
     r = rt.Renderer()
     cpu_cache = {}
     for cfg, label, hw, scene, is_text, mode, w, h, spp, cpu in C:
@@ -150,7 +163,7 @@ def main():
             w, h = w // 4, h // 4
             spp = min(spp, 4) if spp else spp
         try:
-            g = gpu_rate(r, scene, w, h, spp, mode, 2)
+            g = gpu_rate(r, scene, w, h, spp, mode, 1 if a.grid else 2)
         except Exception as e:
             g = {"error": str(e)}
         row = {"config": cfg, "scene": label, "reference_binary": f"hw{hw}", "gpu": g}
