@@ -419,6 +419,31 @@ def test_large_scenes_match_port_on_same_stream(name, mode, frac):
     print(f"{name}: pixels within 5 % {got:.4f}, rays {rays} vs {rays_port}, light queries {lq} vs {lq_port}")
 
 
+def test_hw6_without_light_sampling_in_both_schedulings():
+    """hw6 rules on a description whose emitter list is empty (Mix = Cosine alone, k = 1) over a bright background: the
+    branch of the wavefront shade stage that finishes diffuse bounces itself and sends every ray -- diffuse, mirror,
+    dielectric -- straight to the next bounce, against the per-pixel kernel and the port on the same stream."""
+    sc = ou.load_scene(os.path.join(S, "hw6/practice7_1_glass.gltf"), width=128, height=96, samples=8, mode=6)
+    sc.desc.n_light_tris = 0
+    sc.desc.n_light_nodes = 0
+    sc.desc.bg_color[0], sc.desc.bg_color[1], sc.desc.bg_color[2] = 0.6, 0.7, 0.9
+    out = {}
+    for name, flags in (("wave", rt.FLAG_WAVEFRONT), ("pixel", rt.FLAG_MEGAKERNEL)):
+        r = rt.Renderer(flags=flags)
+        try:
+            out[name] = (_render(r, sc, 0, 8), r.stats())
+        finally:
+            r.close()
+    port = ou.port_render(sc, 1, want_counters=True)
+    for name, (acc, st) in out.items():
+        ok, got = _mean_close(acc, port["accum"], 8, 0.97, rel=5e-2)
+        assert ok, (name, got)
+        assert abs(acc.mean() - port["accum"].mean()) <= 1e-2 * port["accum"].mean(), name
+        assert abs(int(st["rays"]) - int(port["counters"][0])) <= 2e-3 * int(port["counters"][0]), name
+        assert int(st["light_queries"]) == 0, name
+    assert acc.mean() > 0.3      # the background is seen
+
+
 # ---------------------------------------------------------------- MC: north_star statistical bar
 def _linear(img8):
     return ou.inv_display(img8)
