@@ -728,6 +728,32 @@ def test_group_text_scene_and_deterministic_modes():
     one.close(); g.close()
 
 
+def test_group_hw6_large_scene_takes_the_wavefront_on_every_member():
+    """An hw6 scene above the per-pixel kernel's size limit, replicated to a second member: the replica keeps the
+    triangle count (the scheduling rule reads it), so both members run the wavefront pipeline and the frame equals the
+    one-context frame up to float summation order -- and is bit-identical to a forced-wavefront single context when the
+    group has one member."""
+    path = _scene_file("big:hw6/practice6_1.gltf")
+    if path is None:
+        pytest.skip("the reference's example scenes are not on this machine (oracle/build_ref.sh copies them)")
+    sc = ou.load_scene(path, width=96, height=64, samples=8, mode=6)
+    one = rt.Renderer(flags=rt.FLAG_WAVEFRONT)
+    one.upload(sc); one.render(0, 8)
+    single = one.download_accum()
+    for members in (1, 2):
+        g = rt.Group([0] * members)
+        g.upload(sc); g.render(0, 8)
+        total = g.download_accum()
+        if members == 1:
+            assert np.array_equal(total, single)
+        else:
+            assert np.allclose(total, single, rtol=1e-5, atol=1e-6)
+            assert all(g.member_accum(i).max() > 0 for i in range(members))
+        assert g.stats()["paths"] == 96 * 64 * 8
+        g.close()
+    one.close()
+
+
 # ---- the product's default load: no trees in the description ----------------------------------------------------
 @pytest.mark.parametrize("path,mode", [("hw7/practice7_4.gltf", 0), ("hw8/sphere_emissive.gltf", 0), ("hw7/practice7_1.gltf", 6)])
 def test_default_load_without_trees_matches_port_on_same_stream(path, mode):
